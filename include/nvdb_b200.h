@@ -1,0 +1,133 @@
+/*
+ * nvdb_b200.h — C ABI of the B200-native flat-scan top-k + exact-refine path.
+ *
+ * This is the drop-in boundary for ONE hot path of ntnu-yjyjames/nano-vectordb (citations into that repo):
+ *   - nvdb::FlatIndex{,OMP,Async,Pool}::search_topk_dot(q, k)       include/nvdb/flat_index.h:13,
+ *                                                                   src/flat_index.cpp:16-48 (+_omp/_async/_pool)
+ *   - the bench-side batched scan                                   apps/nvdb_bench.cpp:47-159,161-251
+ *   - nvdb::cuda_l2_topk_batch(...)                                 include/nvdb/cuda_refine.h:25-38,
+ *                                                                   src/cuda_refine.cu:839-1173
+ * Plain pointers and sizes only; no C++/torch types; every function returns an int status (0 = OK) and never
+ * exits or throws across the boundary (the reference's CUDA library calls exit(); src/cuda_refine.cu:18-23).
+ * There is no CPU fallback behind these symbols: without a CUDA device they return NVDB_B200_ERR_CUDA.
+ *
+ * dtype codes are the vecbin codes (include/nvdb/vecbin_format.h:10-14): 1 = f32, 2 = f16, 3 = i8 (+ one f32
+ * scale per row). Result order is canonical: score descending, then id ascending (flat scan); distance
+ * ascending, then id ascending (refine). See DESIGN.md "Parity contract".
+ *
+ * Thread-safety: calls on different index handles are independent; calls on ONE handle serialise on its
+ * stream (same contract as FlatIndexPool / cuda_l2_topk_batch: one query batch in flight per index).
+ */
+#ifndef NVDB_B200_H
+#define NVDB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NVDB_B200_VERSION 100
+
+enum {
+  NVDB_B200_OK = 0,
+  NVDB_B200_ERR_ARG = 1,      /* null pointer / bad dtype / bad shape */
+  NVDB_B200_ERR_EMPTY = 2,    /* "Empty base" (src/flat_index.cpp:17) */
+  NVDB_B200_ERR_CUDA = 3,     /* CUDA runtime / driver error; see nvdb_b200_last_error */
+  NVDB_B200_ERR_OOM = 4,      /* device allocation failed */
+  NVDB_B200_ERR_UNSUPPORTED = 5
+};
+
+enum { NVDB_B200_F32 = 1, NVDB_B200_F16 = 2, NVDB_B200_I8 = 3 };
+
+/* which scan kernel family nvdb_b200_search* uses */
+enum {
+  NVDB_B200_PATH_AUTO = 0, /* GEMV for small batches, tensor-core GEMM above the crossover */
+  NVDB_B200_PATH_GEMV = 1, /* bit-exact FP32-FMA streaming scan (all dtypes) */
+  NVDB_B200_PATH_MMA = 2   /* tcgen05 tensor-core scan (f16 / i8), tolerance-mode parity */
+};
+
+typedef struct nvdb_b200_index nvdb_b200_index;
+
+/* mirrors nvdb::CudaRefineTiming's first four fields (include/nvdb/cuda_refine.h:7-8) */
+typedef struct nvdb_b200_timing {
+  float h2d_ms;
+  float kernel_ms;
+  float d2h_ms;
+  float total_ms;
+  uint32_t kernel_launches; /* kernels of this library launched by the call */
+  uint32_t path;            /* NVDB_B200_PATH_* actually used */
+} nvdb_b200_timing;
+
+int nvdb_b200_version(void);
+const char* nvdb_b200_status_string(int status);
+/* last error text; idx may be NULL for errors raised before a handle existed (thread-local). */
+const char* nvdb_b200_last_error(const nvdb_b200_index* idx);
+int nvdb_b200_device_count(int* out_count);
+
+/* ---- index lifecycle --------------------------------------------------------------------------------------
+ * Replaces: `FlatIndex(const VectorDataset* base)` (non-owning view of the mmap; include/nvdb/flat_index.h:11)
+ * and the hidden process-global device cache of the refine library (src/cuda_refine.cu:179-204).
+ * payload_host: n*dim elements, row-major (the vecbin payload, e.g. the mmap); copied to `device` through a
+ * chunked pinned double buffer. scales_host: n floats (i8 only, else NULL). row_offset is added to local row
+ * ids in results (row-sharded multi-GPU indices). */
+int nvdb_b200_index_create(const void* payload_host, const float* scales_host, uint32_t dtype, uint64_t n,
+                           uint32_t dim, int device, uint64_t row_offset, nvdb_b200_index** out);
+/* Non-owning view over rows already resident in device memory (16-byte aligned). */
+int nvdb_b200_index_create_device(const void* payload_dev, const float* scales_dev, uint32_t dtype, uint64_t n,
+                                  uint32_t dim, int device, uint64_t row_offset, nvdb_b200_index** out);
+/* Synthetic base generated on the device: global rows [first_row, first_row+n) of the counter-based
+ * generator restated in oracle/nvdb_oracle.c (orc_synth_*), converted with the reference converters'
+ * semantics (tools/nvdb_convert_f16.cpp, apps/nvdb_quantize_i8.cpp). */
+int nvdb_b200_index_create_synthetic(uint32_t dtype, uint64_t n, uint32_t dim, uint64_t seed, uint64_t first_row,
+                                     int device, uint64_t row_offset, nvdb_b200_index** out);
+int nvdb_b200_index_destroy(nvdb_b200_index* idx);
+int nvdb_b200_index_info(const nvdb_b200_index* idx, uint64_t* n, uint32_t* dim, uint32_t* dtype, int* device,
+                         uint64_t* row_offset, const void** payload_dev, const float** scales_dev);
+int nvdb_b200_index_set_path(nvdb_b200_index* idx, int path);
+/* Copy rows [row0,row0+nrows) of the device-resident payload (and scales) back to the host. */
+int nvdb_b200_index_read_rows(const nvdb_b200_index* idx, uint64_t row0, uint64_t nrows, void* payload_host,
+                              float* scales_host);
+
+/* ---- flat scan ----------------------------------------------------------------------------------------------
+ * Replaces FlatIndex::search_topk_dot (nq == 1) and batched_scan_* (nq > 1). queries: nq*dim f32.
+ * out_ids / out_scores: nq*k, score-descending; when k > n the tail is padded with id = UINT64_MAX,
+ * score = -inf (the reference clamps k to n, src/flat_index.cpp:24). k == 0 or nq == 0 is a no-op. */
+int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, uint32_t k, uint64_t* out_ids,
+                     float* out_scores, nvdb_b200_timing* timing);
+/* Same, all buffers in device memory, asynchronous on `stream` (a cudaStream_t; NULL = the index's stream). */
+int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
+                            uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+/* Merge `nlists` per-shard results (each [nq][k], laid out list-major: [nlists][nq][k]) into one [nq][k]
+ * under (score desc, id asc). Device buffers; asynchronous on `stream`. This is the step after the all-gather
+ * of a row-sharded index. */
+int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float* scores_dev, uint32_t nlists,
+                                uint32_t nq, uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev,
+                                void* stream);
+
+/* ---- exact refine -------------------------------------------------------------------------------------------
+ * Replaces nvdb::cuda_l2_topk_batch: for each of Q queries, squared-L2 distance to its R candidate rows
+ * (ids >= n, incl. 0xFFFFFFFF, are skipped), K smallest in ascending order; unfilled slots are
+ * id = 0xFFFFFFFF, dist = 1e30f (src/cuda_refine.cu:891-894). out_dist may be NULL (CUDA_RETURN_DIST=0). */
+int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const uint32_t* cand_ids_host,
+                        uint32_t Q, uint32_t R, uint32_t K, uint32_t* out_ids, float* out_dist,
+                        nvdb_b200_timing* timing);
+int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, const uint32_t* cand_ids_dev,
+                               uint32_t Q, uint32_t R, uint32_t K, uint32_t* out_ids_dev, float* out_dist_dev,
+                               void* stream);
+
+/* ---- synthetic data on the device ----------------------------------------------------------------------------
+ * Fill caller-owned device buffers with global rows [first_row, first_row+n) of the synthetic generator in
+ * `dtype` (payload n*dim elements; scales n floats for i8, else NULL). Asynchronous on `stream`. */
+int nvdb_b200_synth_fill_device(int device, uint32_t dtype, uint64_t n, uint32_t dim, uint64_t seed,
+                                uint64_t first_row, void* payload_dev, float* scales_dev, void* stream);
+
+/* ---- introspection for the harness ------------------------------------------------------------------------ */
+/* kernels launched by this library in this process so far (bench.py's gpu_launches). */
+uint64_t nvdb_b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NVDB_B200_H */

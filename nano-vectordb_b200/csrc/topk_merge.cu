@@ -1,0 +1,119 @@
+// topk_merge.cu — reductions of per-CTA / per-shard top-k lists.
+//
+// Replaces the serial merges of the reference (src/flat_index_omp.cpp:67-75, src/flat_index_pool.cpp:212-214,
+// include/nvdb/topK.h:41-49): one CTA per query; candidates are streamed through a shared-memory buffer,
+// block-bitonic-sorted, and the best k are carried to the next round.
+#include <math.h>
+
+#include "common.cuh"
+#include "scan.h"
+
+namespace nvdb_b200 {
+namespace {
+
+constexpr int kMergeThreads = 512;
+
+// partial: [nq][nlists][k] ordered keys (0 = empty). out: ids = row_offset + row, scores; padded with
+// UINT64_MAX / -inf when fewer than k candidates exist (k > n).
+__global__ void __launch_bounds__(kMergeThreads)
+merge_partials_kernel(const uint64_t* __restrict__ partial, uint32_t nlists, uint32_t k, uint32_t bufn,
+                      uint64_t row_offset, uint64_t* __restrict__ out_ids, float* __restrict__ out_scores) {
+  extern __shared__ uint64_t buf[];
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  const uint64_t* in = partial + (size_t)q * nlists * k;
+  const uint32_t total = nlists * k;
+  auto sync = [] { __syncthreads(); };
+  uint32_t kept = 0, pos = 0;
+  while (pos < total) {
+    const uint32_t take = min(bufn - kept, total - pos);
+    for (uint32_t i = tid; i < bufn - kept; i += kMergeThreads) buf[kept + i] = (i < take) ? in[pos + i] : 0ull;
+    __syncthreads();
+    bitonic_sort_desc(buf, bufn, tid, kMergeThreads, sync);
+    kept = k;
+    pos += take;
+  }
+  for (uint32_t j = tid; j < k; j += kMergeThreads) {
+    const uint64_t key = (total > 0) ? buf[j] : 0ull;
+    const bool ok = key != 0ull;
+    out_ids[(size_t)q * k + j] = ok ? row_offset + (uint64_t)key_row(key) : ~0ull;
+    out_scores[(size_t)q * k + j] = ok ? key_score(key) : -INFINITY;
+  }
+}
+
+// Cross-shard merge: ids are 64-bit global ids, so rank by pairwise comparison instead of packed keys.
+// L = nlists*k entries per query; entry e lands at position rank(e) = #{f better than e}.
+__device__ __forceinline__ bool better(uint32_t sa, uint64_t ia, uint32_t pa, uint32_t sb, uint64_t ib, uint32_t pb) {
+  if (sa != sb) return sa > sb;
+  if (ia != ib) return ia < ib;
+  return pa < pb;
+}
+
+__global__ void __launch_bounds__(256)
+merge_lists_kernel(const uint64_t* __restrict__ ids, const float* __restrict__ scores, uint32_t nlists, uint32_t nq,
+                   uint32_t k, uint64_t* __restrict__ out_ids, float* __restrict__ out_scores) {
+  extern __shared__ uint64_t sm[];
+  const uint32_t L = nlists * k;
+  uint64_t* sid = sm;                                      // [L]
+  uint32_t* ssc = reinterpret_cast<uint32_t*>(sm + L);     // [L] ordered scores (0 = empty)
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  for (uint32_t e = tid; e < L; e += blockDim.x) {
+    const uint32_t l = e / k, j = e - l * k;
+    const size_t src = ((size_t)l * nq + q) * k + j;
+    const uint64_t id = ids[src];
+    sid[e] = id;
+    ssc[e] = (id == ~0ull) ? 0u : float_to_ordered(scores[src]);
+  }
+  for (uint32_t j = tid; j < k; j += blockDim.x) {
+    out_ids[(size_t)q * k + j] = ~0ull;
+    out_scores[(size_t)q * k + j] = -INFINITY;
+  }
+  __syncthreads();
+  for (uint32_t e = tid; e < L; e += blockDim.x) {
+    const uint32_t s = ssc[e];
+    if (s == 0u) continue;
+    const uint64_t id = sid[e];
+    uint32_t rank = 0;
+    for (uint32_t f = 0; f < L && rank < k; ++f) rank += better(ssc[f], sid[f], f, s, id, e) ? 1u : 0u;
+    if (rank < k) {
+      out_ids[(size_t)q * k + rank] = id;
+      out_scores[(size_t)q * k + rank] = ordered_to_float(s);
+    }
+  }
+}
+
+}  // namespace
+
+cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
+                                  uint64_t row_offset, uint64_t* out_ids, float* out_scores, cudaStream_t stream) {
+  if (nq == 0 || k == 0) return cudaSuccess;
+  // buffer: at least 2k (so every round makes progress), ideally everything in one round, capped at 16384 keys
+  uint32_t bufn = next_pow2(nlists * k);
+  if (bufn > 16384u) bufn = 16384u;
+  const uint32_t min_buf = next_pow2(2u * k);
+  if (bufn < min_buf) bufn = min_buf;
+  if (bufn < 2u) bufn = 2u;
+  const size_t smem = (size_t)bufn * 8u;
+  if (smem > 48u * 1024u) {
+    cudaError_t e = cudaFuncSetAttribute(merge_partials_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, nlists, k, bufn, row_offset, out_ids, out_scores);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, uint32_t nlists, uint32_t nq, uint32_t k,
+                               uint64_t* out_ids, float* out_scores, cudaStream_t stream) {
+  if (nq == 0 || k == 0) return cudaSuccess;
+  const size_t smem = (size_t)nlists * k * 12u + 8u;
+  if (smem > 200u * 1024u) return cudaErrorInvalidValue;
+  if (smem > 48u * 1024u) {
+    cudaError_t e = cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  merge_lists_kernel<<<nq, 256, smem, stream>>>(ids, scores, nlists, nq, k, out_ids, out_scores);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace nvdb_b200

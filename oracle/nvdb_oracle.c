@@ -101,14 +101,19 @@ static inline float hsum8(const float a[8]) {
 }
 
 /* src/simd_dot.cpp:26-49 (dot_avx2_fma): one 8-lane accumulator, FMA per 8 elements in ascending order,
- * hsum, then a sequential tail `out += a[i]*b[i]` (GCC contracts it to an FMA inside target("fma")
- * functions at -O3; pinned against the compiled reference in tests/test_oracle.py). */
+ * hsum, then a sequential tail `out += a[i]*b[i]` (see the note at the tail). */
 float orc_dot_f32(const float* a, const float* b, uint32_t dim) {
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   uint32_t i = 0;
   for (; i + 8 <= dim; i += 8)
     for (int j = 0; j < 8; ++j) acc[j] = fmaf(a[i + j], b[i + j], acc[j]);
   float out = hsum8(acc);
+  /* tail (:47): as compiled by GCC 13 -O3 in target("avx2,fma") — a group of 4 is vectorised as an unfused
+   * multiply followed by in-order adds, the remaining <=3 elements are contracted to FMAs. Compiler artefact,
+   * pinned empirically against oracle/_ref; irrelevant for the reference's own dims (384, 768). */
+  if (dim - i >= 4) {
+    for (int j = 0; j < 4; ++j, ++i) out = out + a[i] * b[i];
+  }
   for (; i < dim; ++i) out = fmaf(a[i], b[i], out);
   return out;
 }
@@ -120,7 +125,7 @@ float orc_dot_f16(const float* q, const uint16_t* x, uint32_t dim) {
   for (; i + 8 <= dim; i += 8)
     for (int j = 0; j < 8; ++j) acc[j] = fmaf(q[i + j], orc_f16_to_f32(x[i + j]), acc[j]);
   float out = hsum8(acc);
-  for (; i < dim; ++i) out = fmaf(q[i], orc_f16_to_f32(x[i]), out);
+  for (; i < dim; ++i) out = out + q[i] * orc_f16_to_f32(x[i]); /* :122 — compiled unfused (scalar decode call) */
   return out;
 }
 
@@ -134,7 +139,7 @@ float orc_dot_i8(const float* q, const int8_t* x, uint32_t dim, float scale) {
     for (int j = 0; j < 8; ++j) acc[j] = fmaf(q[i + 8 + j], (float)x[i + 8 + j], acc[j]);
   }
   float out = hsum8(acc);
-  for (; i < dim; ++i) out = fmaf(q[i], (float)x[i], out);
+  for (; i < dim; ++i) out = out + q[i] * (float)x[i]; /* :196 — compiled unfused */
   return out * scale;
 }
 
