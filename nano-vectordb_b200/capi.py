@@ -1,0 +1,187 @@
+"""ctypes binding of include/nvdb_b200.h. No compute here; every call lands in the CUDA library.
+
+`FlatIndexCuda` mirrors the reference's index classes (reference include/nvdb/flat_index.h:9-20):
+`search_topk_dot(q, k)` -> (ids, scores) sorted by score descending; plus the bench-side batched search
+(reference apps/nvdb_bench.cpp:47-159) as `search_topk_dot_batch`, and `refine_l2` for
+nvdb::cuda_l2_topk_batch (reference include/nvdb/cuda_refine.h:25-38).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+F32, F16, I8 = 1, 2, 3
+PATH_AUTO, PATH_GEMV, PATH_MMA = 0, 1, 2
+_NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
+
+lib_path = Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"
+if not lib_path.exists():
+    raise ImportError(f"{lib_path} is not built (run `make lib` or __graft_entry__.build()); "
+                      "there is no CPU fallback for this path")
+lib = C.CDLL(str(lib_path))
+
+
+class Timing(C.Structure):
+    _fields_ = [("h2d_ms", C.c_float), ("kernel_ms", C.c_float), ("d2h_ms", C.c_float), ("total_ms", C.c_float),
+                ("kernel_launches", C.c_uint32), ("path", C.c_uint32)]
+
+
+class NvdbError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"nvdb_b200 status {status}: {msg}")
+        self.status = status
+        self.msg = msg
+
+
+_vp, _u32, _u64, _i = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+_sig = {
+    "nvdb_b200_version": (C.c_int, []),
+    "nvdb_b200_status_string": (C.c_char_p, [_i]),
+    "nvdb_b200_last_error": (C.c_char_p, [_vp]),
+    "nvdb_b200_device_count": (_i, [C.POINTER(_i)]),
+    "nvdb_b200_index_create": (_i, [_vp, _vp, _u32, _u64, _u32, _i, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_index_create_device": (_i, [_vp, _vp, _u32, _u64, _u32, _i, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_index_create_synthetic": (_i, [_u32, _u64, _u32, _u64, _u64, _i, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_index_destroy": (_i, [_vp]),
+    "nvdb_b200_index_info": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_i),
+                                  C.POINTER(_u64), C.POINTER(_vp), C.POINTER(_vp)]),
+    "nvdb_b200_index_set_path": (_i, [_vp, _i]),
+    "nvdb_b200_index_read_rows": (_i, [_vp, _u64, _u64, _vp, _vp]),
+    "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
+    "nvdb_b200_search_device": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_merge_topk_device": (_i, [_i, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
+    "nvdb_b200_refine_l2_device": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_synth_fill_device": (_i, [_i, _u32, _u64, _u32, _u64, _u64, _vp, _vp, _vp]),
+    "nvdb_b200_launch_count": (_u64, []),
+}
+for _name, (_res, _args) in _sig.items():
+    _f = getattr(lib, _name)
+    _f.restype = _res
+    _f.argtypes = _args
+EXPORTED_SYMBOLS = tuple(_sig)
+
+
+def _check(status, handle=None):
+    if status != 0:
+        msg = lib.nvdb_b200_last_error(handle)
+        raise NvdbError(status, (msg or b"").decode() or lib.nvdb_b200_status_string(status).decode())
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def launch_count() -> int:
+    return int(lib.nvdb_b200_launch_count())
+
+
+def synth_fill_device(device, dtype, n, dim, seed, first_row, payload_ptr, scales_ptr=None, stream=None):
+    _check(lib.nvdb_b200_synth_fill_device(device, dtype, n, dim, seed, first_row, payload_ptr, scales_ptr, stream))
+
+
+def merge_topk_device(device, ids_ptr, scores_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
+    _check(lib.nvdb_b200_merge_topk_device(device, ids_ptr, scores_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr,
+                                           stream))
+
+
+class FlatIndexCuda:
+    """Device-resident flat index. Host arrays in, host arrays out (the *_device methods take raw pointers)."""
+
+    def __init__(self, handle, keepalive=None):
+        self._h = handle
+        self._keep = keepalive
+        n, dim, dt, dev, off = _u64(), _u32(), _u32(), _i(), _u64()
+        pp, sp = _vp(), _vp()
+        _check(lib.nvdb_b200_index_info(self._h, C.byref(n), C.byref(dim), C.byref(dt), C.byref(dev), C.byref(off),
+                                        C.byref(pp), C.byref(sp)))
+        self.count, self.dim, self.dtype, self.device, self.row_offset = n.value, dim.value, dt.value, dev.value, off.value
+        self.payload_ptr, self.scales_ptr = pp.value, sp.value
+
+    # ---- constructors
+    @classmethod
+    def from_host(cls, payload: np.ndarray, scales: np.ndarray | None, dtype: int, device=0, row_offset=0):
+        payload = np.ascontiguousarray(payload, _NP[dtype])
+        n, dim = payload.shape
+        if scales is not None:
+            scales = np.ascontiguousarray(scales, np.float32)
+        h = _vp()
+        _check(lib.nvdb_b200_index_create(_ptr(payload), _ptr(scales), dtype, n, dim, device, row_offset, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_device(cls, payload_ptr, scales_ptr, dtype, n, dim, device=0, row_offset=0, keepalive=None):
+        h = _vp()
+        _check(lib.nvdb_b200_index_create_device(payload_ptr, scales_ptr, dtype, n, dim, device, row_offset, C.byref(h)))
+        return cls(h, keepalive)
+
+    @classmethod
+    def synthetic(cls, dtype, n, dim, seed, first_row=0, device=0, row_offset=0):
+        h = _vp()
+        _check(lib.nvdb_b200_index_create_synthetic(dtype, n, dim, seed, first_row, device, row_offset, C.byref(h)))
+        return cls(h)
+
+    def close(self):
+        if self._h:
+            lib.nvdb_b200_index_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_path(self, path):
+        _check(lib.nvdb_b200_index_set_path(self._h, path), self._h)
+
+    def read_rows(self, row0, nrows):
+        payload = np.empty((nrows, self.dim), _NP[self.dtype])
+        scales = np.empty(nrows, np.float32) if self.dtype == I8 else None
+        _check(lib.nvdb_b200_index_read_rows(self._h, row0, nrows, _ptr(payload), _ptr(scales)), self._h)
+        return payload, scales
+
+    # ---- search (mirrors FlatIndex::search_topk_dot / batched_scan_*)
+    def search_topk_dot(self, q, k, timing: Timing | None = None):
+        ids, sc = self.search_topk_dot_batch(np.asarray(q, np.float32).reshape(1, -1), k, timing)
+        kk = min(k, self.count)  # the reference clamps k to n (src/flat_index.cpp:24)
+        return ids[0, :kk], sc[0, :kk]
+
+    def search_topk_dot_batch(self, queries, k, timing: Timing | None = None):
+        if queries is None:
+            raise NvdbError(1, "Null query")
+        queries = np.ascontiguousarray(queries, np.float32)
+        if queries.ndim != 2 or queries.shape[1] != self.dim:
+            raise NvdbError(1, f"Dim mismatch: base.dim={self.dim}, query.dim={queries.shape[-1]}")
+        nq = queries.shape[0]
+        ids = np.empty((nq, k), np.uint64)
+        sc = np.empty((nq, k), np.float32)
+        _check(lib.nvdb_b200_search(self._h, _ptr(queries), nq, k, _ptr(ids), _ptr(sc),
+                                    C.byref(timing) if timing is not None else None), self._h)
+        return ids, sc
+
+    def search_device(self, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
+        _check(lib.nvdb_b200_search_device(self._h, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream), self._h)
+
+    # ---- refine (mirrors nvdb::cuda_l2_topk_batch)
+    def refine_l2(self, queries, cand_ids, K, want_dist=True, timing: Timing | None = None):
+        queries = np.ascontiguousarray(queries, np.float32)
+        cand_ids = np.ascontiguousarray(cand_ids, np.uint32)
+        Q, R = cand_ids.shape
+        ids = np.full((Q, K), 0xFFFFFFFF, np.uint32)
+        dist = np.full((Q, K), 1e30, np.float32) if want_dist else None
+        _check(lib.nvdb_b200_refine_l2(self._h, _ptr(queries), _ptr(cand_ids), Q, R, K, _ptr(ids), _ptr(dist),
+                                       C.byref(timing) if timing is not None else None), self._h)
+        return ids, dist
+
+    def refine_l2_device(self, queries_ptr, cand_ptr, Q, R, K, out_ids_ptr, out_dist_ptr, stream=None):
+        _check(lib.nvdb_b200_refine_l2_device(self._h, queries_ptr, cand_ptr, Q, R, K, out_ids_ptr, out_dist_ptr,
+                                              stream), self._h)

@@ -1,0 +1,592 @@
+// capi.cu — the C ABI (include/nvdb_b200.h): index handle, uploads, search / refine orchestration.
+// No CPU compute path lives here: every result is produced by the kernels in this directory.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "../../include/nvdb_b200.h"
+#include "common.cuh"
+#include "scan.h"
+
+using namespace nvdb_b200;
+
+namespace nvdb_b200 {
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(uint32_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+}  // namespace nvdb_b200
+
+struct nvdb_b200_index {
+  int device = 0;
+  uint32_t dtype = 0;
+  uint64_t n = 0;
+  uint32_t dim = 0;
+  uint64_t row_offset = 0;
+  void* payload = nullptr;
+  float* scales = nullptr;
+  bool owns = false;
+  int path = NVDB_B200_PATH_AUTO;
+  int num_sms = 148;
+  int max_smem = 227 * 1024;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  bool tma_ok = false;
+  CUtensorMap tmap;
+  // grow-only workspaces
+  void* d_ws[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t d_ws_bytes[6] = {0, 0, 0, 0, 0, 0};
+  void* h_pin[2] = {nullptr, nullptr};
+  size_t h_pin_bytes[2] = {0, 0};
+  std::mutex mu;
+  mutable std::string err;
+};
+
+namespace {
+
+thread_local std::string t_err;
+enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5 };
+
+int fail(const nvdb_b200_index* idx, int code, const std::string& msg) {
+  t_err = msg;
+  if (idx) idx->err = msg;
+  return code;
+}
+int fail_cuda(const nvdb_b200_index* idx, cudaError_t e, const char* what) {
+  return fail(idx, e == cudaErrorMemoryAllocation ? NVDB_B200_ERR_OOM : NVDB_B200_ERR_CUDA,
+              std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call, what)                                   \
+  do {                                                   \
+    cudaError_t _e = (call);                             \
+    if (_e != cudaSuccess) return fail_cuda(idx, _e, what); \
+  } while (0)
+
+size_t elem_size(uint32_t dtype) { return dtype == kDtF32 ? 4 : dtype == kDtF16 ? 2 : dtype == kDtI8 ? 1 : 0; }
+
+int ensure_ws(nvdb_b200_index* idx, int which, size_t bytes) {
+  if (bytes <= idx->d_ws_bytes[which]) return NVDB_B200_OK;
+  if (idx->d_ws[which]) {
+    CK(cudaStreamSynchronize(idx->stream), "sync before workspace grow");
+    cudaFree(idx->d_ws[which]);
+    idx->d_ws[which] = nullptr;
+    idx->d_ws_bytes[which] = 0;
+  }
+  size_t cap = 4096;
+  while (cap < bytes) cap <<= 1;
+  CK(cudaMalloc(&idx->d_ws[which], cap), "cudaMalloc workspace");
+  idx->d_ws_bytes[which] = cap;
+  return NVDB_B200_OK;
+}
+int ensure_pin(nvdb_b200_index* idx, int which, size_t bytes) {
+  if (bytes <= idx->h_pin_bytes[which]) return NVDB_B200_OK;
+  if (idx->h_pin[which]) {
+    CK(cudaStreamSynchronize(idx->stream), "sync before pinned grow");
+    cudaFreeHost(idx->h_pin[which]);
+    idx->h_pin[which] = nullptr;
+    idx->h_pin_bytes[which] = 0;
+  }
+  size_t cap = 4096;
+  while (cap < bytes) cap <<= 1;
+  CK(cudaMallocHost(&idx->h_pin[which], cap), "cudaMallocHost");
+  idx->h_pin_bytes[which] = cap;
+  return NVDB_B200_OK;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess) return (EncodeTiledFn) nullptr;
+    if (qres != cudaDriverEntryPointSuccess) return (EncodeTiledFn) nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// The streaming scan needs: whole 8-chains only (no scalar tail), 16-byte row pitch, 16-byte aligned base.
+bool tma_eligible(const nvdb_b200_index* idx) {
+  const uint32_t step = idx->dtype == kDtI8 ? 16u : 8u;
+  if (idx->dim % step) return false;
+  if ((idx->dim * elem_size(idx->dtype)) % 16) return false;
+  if (reinterpret_cast<uintptr_t>(idx->payload) % 16) return false;
+  if (idx->n > 0x7FFFFF00ull) return false;
+  return true;
+}
+
+int build_tmap(nvdb_b200_index* idx) {
+  idx->tma_ok = false;
+  if (!tma_eligible(idx)) return NVDB_B200_OK;
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail(idx, NVDB_B200_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const size_t es = elem_size(idx->dtype);
+  const CUtensorMapDataType dt = idx->dtype == kDtF32   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : idx->dtype == kDtF16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                        : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  cuuint64_t gdim[2] = {idx->dim, idx->n};
+  cuuint64_t gstride[1] = {(cuuint64_t)idx->dim * es};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / es), (cuuint32_t)kScanRowsPerTile};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(&idx->tmap, dt, 2, idx->payload, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(idx, NVDB_B200_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
+  idx->tma_ok = true;
+  return NVDB_B200_OK;
+}
+
+int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t row_offset, nvdb_b200_index** out) {
+  const nvdb_b200_index* idx = nullptr;
+  if (!out) return fail(nullptr, NVDB_B200_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  if (elem_size(dtype) == 0) return fail(nullptr, NVDB_B200_ERR_ARG, "Unsupported base dtype (Float32/Float16/Int8 only)");
+  if (n == 0 || dim == 0) return fail(nullptr, NVDB_B200_ERR_EMPTY, "Empty base");
+  if (n > 0xFFFFFFF0ull) return fail(nullptr, NVDB_B200_ERR_UNSUPPORTED, "more than 2^32 rows per device shard");
+  CK(cudaSetDevice(device), "cudaSetDevice");
+  auto* h = new nvdb_b200_index();
+  h->device = device;
+  h->dtype = dtype;
+  h->n = n;
+  h->dim = dim;
+  h->row_offset = row_offset;
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e == cudaSuccess) {
+    h->num_sms = prop.multiProcessorCount;
+    h->max_smem = (int)prop.sharedMemPerBlockOptin;
+  }
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+  if (e != cudaSuccess) {
+    delete h;
+    return fail_cuda(nullptr, e, "index init");
+  }
+  *out = h;
+  return NVDB_B200_OK;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// lifecycle
+// =====================================================================================================
+extern "C" {
+
+int nvdb_b200_version(void) { return NVDB_B200_VERSION; }
+
+const char* nvdb_b200_status_string(int s) {
+  switch (s) {
+    case NVDB_B200_OK: return "ok";
+    case NVDB_B200_ERR_ARG: return "invalid argument";
+    case NVDB_B200_ERR_EMPTY: return "Empty base";
+    case NVDB_B200_ERR_CUDA: return "CUDA error";
+    case NVDB_B200_ERR_OOM: return "out of device memory";
+    case NVDB_B200_ERR_UNSUPPORTED: return "unsupported";
+    default: return "unknown status";
+  }
+}
+
+const char* nvdb_b200_last_error(const nvdb_b200_index* idx) { return idx ? idx->err.c_str() : t_err.c_str(); }
+
+int nvdb_b200_device_count(int* out_count) {
+  const nvdb_b200_index* idx = nullptr;
+  if (!out_count) return fail(nullptr, NVDB_B200_ERR_ARG, "out_count is NULL");
+  *out_count = 0;
+  CK(cudaGetDeviceCount(out_count), "cudaGetDeviceCount");
+  return NVDB_B200_OK;
+}
+
+uint64_t nvdb_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int nvdb_b200_index_destroy(nvdb_b200_index* idx) {
+  if (!idx) return NVDB_B200_OK;
+  cudaSetDevice(idx->device);
+  if (idx->stream) cudaStreamSynchronize(idx->stream);
+  if (idx->owns) {
+    if (idx->payload) cudaFree(idx->payload);
+    if (idx->scales) cudaFree(idx->scales);
+  }
+  for (auto& p : idx->d_ws)
+    if (p) cudaFree(p);
+  for (auto& p : idx->h_pin)
+    if (p) cudaFreeHost(p);
+  for (auto& e : idx->ev)
+    if (e) cudaEventDestroy(e);
+  if (idx->stream) cudaStreamDestroy(idx->stream);
+  delete idx;
+  return NVDB_B200_OK;
+}
+
+static int alloc_base(nvdb_b200_index* idx) {
+  const size_t bytes = (size_t)idx->n * idx->dim * elem_size(idx->dtype);
+  CK(cudaMalloc(&idx->payload, bytes), "cudaMalloc base payload");
+  idx->owns = true;
+  if (idx->dtype == kDtI8) CK(cudaMalloc((void**)&idx->scales, (size_t)idx->n * 4), "cudaMalloc scales");
+  return NVDB_B200_OK;
+}
+
+// Upload path: host (typically the mmap of a vecbin file) -> two pinned staging buffers -> cudaMemcpyAsync,
+// the memcpy of chunk i+1 overlapping the DMA of chunk i. The reference does one synchronous pageable
+// cudaMemcpy of the whole base (src/cuda_refine.cu:198).
+static int upload(nvdb_b200_index* idx, void* dst, const void* src, size_t bytes) {
+  const size_t chunk = (size_t)64 << 20;
+  int rc;
+  if ((rc = ensure_pin(idx, 0, bytes < chunk ? bytes : chunk))) return rc;
+  if (bytes > chunk && (rc = ensure_pin(idx, 1, chunk))) return rc;
+  cudaEvent_t done[2] = {idx->ev[0], idx->ev[1]};
+  bool used[2] = {false, false};
+  size_t off = 0;
+  int b = 0;
+  while (off < bytes) {
+    const size_t take = bytes - off < chunk ? bytes - off : chunk;
+    if (used[b]) CK(cudaEventSynchronize(done[b]), "upload event sync");
+    std::memcpy(idx->h_pin[b], (const char*)src + off, take);
+    CK(cudaMemcpyAsync((char*)dst + off, idx->h_pin[b], take, cudaMemcpyHostToDevice, idx->stream), "H2D base chunk");
+    CK(cudaEventRecord(done[b], idx->stream), "upload event record");
+    used[b] = true;
+    off += take;
+    b ^= 1;
+  }
+  CK(cudaStreamSynchronize(idx->stream), "upload sync");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_create(const void* payload_host, const float* scales_host, uint32_t dtype, uint64_t n,
+                           uint32_t dim, int device, uint64_t row_offset, nvdb_b200_index** out) {
+  if (!payload_host) return fail(nullptr, NVDB_B200_ERR_ARG, "payload is NULL");
+  if (dtype == kDtI8 && !scales_host) return fail(nullptr, NVDB_B200_ERR_ARG, "Dataset is not int8 (scales missing)");
+  int rc = new_handle(dtype, n, dim, device, row_offset, out);
+  if (rc) return rc;
+  nvdb_b200_index* idx = *out;
+  rc = alloc_base(idx);
+  if (!rc) rc = upload(idx, idx->payload, payload_host, (size_t)n * dim * elem_size(dtype));
+  if (!rc && dtype == kDtI8) rc = upload(idx, idx->scales, scales_host, (size_t)n * 4);
+  if (!rc) rc = build_tmap(idx);
+  if (rc) {
+    t_err = idx->err;
+    nvdb_b200_index_destroy(idx);
+    *out = nullptr;
+  }
+  return rc;
+}
+
+int nvdb_b200_index_create_device(const void* payload_dev, const float* scales_dev, uint32_t dtype, uint64_t n,
+                                  uint32_t dim, int device, uint64_t row_offset, nvdb_b200_index** out) {
+  if (!payload_dev) return fail(nullptr, NVDB_B200_ERR_ARG, "payload is NULL");
+  if (dtype == kDtI8 && !scales_dev) return fail(nullptr, NVDB_B200_ERR_ARG, "Dataset is not int8 (scales missing)");
+  int rc = new_handle(dtype, n, dim, device, row_offset, out);
+  if (rc) return rc;
+  nvdb_b200_index* idx = *out;
+  idx->payload = const_cast<void*>(payload_dev);
+  idx->scales = const_cast<float*>(scales_dev);
+  idx->owns = false;
+  rc = build_tmap(idx);
+  if (rc) {
+    t_err = idx->err;
+    nvdb_b200_index_destroy(idx);
+    *out = nullptr;
+  }
+  return rc;
+}
+
+int nvdb_b200_synth_fill_device(int device, uint32_t dtype, uint64_t n, uint32_t dim, uint64_t seed,
+                                uint64_t first_row, void* payload_dev, float* scales_dev, void* stream) {
+  const nvdb_b200_index* idx = nullptr;
+  if (!payload_dev || elem_size(dtype) == 0 || (dtype == kDtI8 && !scales_dev))
+    return fail(nullptr, NVDB_B200_ERR_ARG, "synth_fill: bad arguments");
+  CK(cudaSetDevice(device), "cudaSetDevice");
+  CK(synth_fill_launch((int)dtype, n, dim, seed, first_row, payload_dev, scales_dev, (cudaStream_t)stream), "synth_fill");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_create_synthetic(uint32_t dtype, uint64_t n, uint32_t dim, uint64_t seed, uint64_t first_row,
+                                     int device, uint64_t row_offset, nvdb_b200_index** out) {
+  int rc = new_handle(dtype, n, dim, device, row_offset, out);
+  if (rc) return rc;
+  nvdb_b200_index* idx = *out;
+  rc = alloc_base(idx);
+  if (!rc) {
+    cudaError_t e = synth_fill_launch((int)dtype, n, dim, seed, first_row, idx->payload, idx->scales, idx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
+    if (e != cudaSuccess) rc = fail_cuda(idx, e, "synthetic fill");
+  }
+  if (!rc) rc = build_tmap(idx);
+  if (rc) {
+    t_err = idx->err;
+    nvdb_b200_index_destroy(idx);
+    *out = nullptr;
+  }
+  return rc;
+}
+
+int nvdb_b200_index_info(const nvdb_b200_index* idx, uint64_t* n, uint32_t* dim, uint32_t* dtype, int* device,
+                         uint64_t* row_offset, const void** payload_dev, const float** scales_dev) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (n) *n = idx->n;
+  if (dim) *dim = idx->dim;
+  if (dtype) *dtype = idx->dtype;
+  if (device) *device = idx->device;
+  if (row_offset) *row_offset = idx->row_offset;
+  if (payload_dev) *payload_dev = idx->payload;
+  if (scales_dev) *scales_dev = idx->scales;
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_set_path(nvdb_b200_index* idx, int path) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (path < NVDB_B200_PATH_AUTO || path > NVDB_B200_PATH_MMA) return fail(idx, NVDB_B200_ERR_ARG, "bad path");
+  idx->path = path;
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_read_rows(const nvdb_b200_index* idx, uint64_t row0, uint64_t nrows, void* payload_host,
+                              float* scales_host) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (row0 + nrows > idx->n) return fail(idx, NVDB_B200_ERR_ARG, "Index out of range");
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  CK(cudaStreamSynchronize(idx->stream), "sync");
+  const size_t rb = (size_t)idx->dim * elem_size(idx->dtype);
+  if (payload_host && nrows)
+    CK(cudaMemcpy(payload_host, (const char*)idx->payload + row0 * rb, nrows * rb, cudaMemcpyDeviceToHost), "D2H rows");
+  if (scales_host && idx->scales && nrows)
+    CK(cudaMemcpy(scales_host, idx->scales + row0, nrows * 4, cudaMemcpyDeviceToHost), "D2H scales");
+  return NVDB_B200_OK;
+}
+
+}  // extern "C"
+
+// =====================================================================================================
+// flat scan
+// =====================================================================================================
+namespace {
+
+struct ScanPlan {
+  int nq_template = 1;
+  int stages = 4;
+  uint32_t cap = 512;
+  int grid = 1;
+};
+
+// Queries per pass: as many as fit next to >= 3 ring stages (each 32 KB) in shared memory, at most 8.
+int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) {
+  const uint64_t need = (uint64_t)k + kScanRowsPerTile;
+  if (need > 8192) return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "k too large for the fused selector (k <= 7936)");
+  p->cap = next_pow2((uint32_t)need);
+  if (p->cap < 512) p->cap = 512;
+  const uint32_t tiles = (uint32_t)((idx->n + kScanRowsPerTile - 1) / kScanRowsPerTile);
+  p->grid = (int)(tiles < (uint32_t)idx->num_sms ? tiles : (uint32_t)idx->num_sms);
+  int want = nq >= 8 ? 8 : nq >= 4 ? 4 : nq >= 2 ? 2 : 1;
+  if (nq == 3) want = 4;
+  if (nq > 4 && nq < 8) want = 8;
+  for (int t = want; t >= 1; t >>= 1) {
+    if (!idx->tma_ok) {
+      if (scan_gemv_smem_bytes(false, 0, t, idx->dim, p->cap) <= (uint32_t)idx->max_smem) {
+        p->nq_template = t;
+        p->stages = 0;
+        return NVDB_B200_OK;
+      }
+      continue;
+    }
+    const uint32_t fixed = scan_gemv_smem_bytes(true, 0, t, idx->dim, p->cap);
+    if (fixed + 3u * 32768u > (uint32_t)idx->max_smem) continue;
+    int st = (int)(((uint32_t)idx->max_smem - fixed) / (32768u + 16u));
+    if (st > 6) st = 6;
+    while (st > 3 && scan_gemv_smem_bytes(true, st, t, idx->dim, p->cap) > (uint32_t)idx->max_smem) --st;
+    p->nq_template = t;
+    p->stages = st;
+    return NVDB_B200_OK;
+  }
+  return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "dim / k too large for shared memory");
+}
+
+int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                       float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
+  ScanPlan plan;
+  int rc = plan_scan(idx, nq, k, &plan);
+  if (rc) return rc;
+  if ((rc = ensure_ws(idx, WS_PARTIAL, (size_t)nq * plan.grid * k * 8))) return rc;
+  uint64_t* partial = (uint64_t*)idx->d_ws[WS_PARTIAL];
+
+  ScanLaunch L;
+  L.dtype = (int)idx->dtype;
+  L.use_tma = idx->tma_ok;
+  L.tmap = &idx->tmap;
+  L.grid = plan.grid;
+  L.stream = stream;
+  ScanArgs a;
+  a.scales = idx->scales;
+  a.base = idx->payload;
+  a.n_rows = (uint32_t)idx->n;
+  a.dim = idx->dim;
+  a.k = k;
+  a.cap = plan.cap;
+  a.num_tiles = (uint32_t)((idx->n + kScanRowsPerTile - 1) / kScanRowsPerTile);
+  a.kchunks = (uint32_t)(((size_t)idx->dim * elem_size(idx->dtype) + 127) / 128);
+  a.stages = plan.stages;
+  for (uint32_t q0 = 0; q0 < nq; q0 += (uint32_t)plan.nq_template) {
+    const uint32_t left = nq - q0;
+    // shrink the template for the remainder so a tail of 1-2 queries does not pay for 8
+    int t = plan.nq_template;
+    while (t > 1 && (uint32_t)(t / 2) >= left) t >>= 1;
+    a.nq = left < (uint32_t)t ? left : (uint32_t)t;
+    a.queries = d_queries + (size_t)q0 * idx->dim;
+    a.partial = partial + (size_t)q0 * plan.grid * k;
+    CK(scan_gemv_launch(L, a, t), "scan_gemv launch");
+    count_launch();
+    if (launches) ++*launches;
+  }
+  CK(merge_partials_launch(partial, (uint32_t)plan.grid, nq, k, idx->row_offset, d_out_ids, d_out_scores, stream),
+     "merge_partials launch");
+  if (launches) ++*launches;
+  return NVDB_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
+                            uint64_t* out_ids_dev, float* out_scores_dev, void* stream) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!queries_dev) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if (!out_ids_dev || !out_scores_dev) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  return search_device_impl(idx, queries_dev, nq, k, out_ids_dev, out_scores_dev,
+                            stream ? (cudaStream_t)stream : idx->stream, nullptr);
+}
+
+int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, uint32_t k, uint64_t* out_ids,
+                     float* out_scores, nvdb_b200_timing* timing) {
+  if (timing) *timing = nvdb_b200_timing{};
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!queries_host) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if (!out_ids || !out_scores) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  const size_t qbytes = (size_t)nq * idx->dim * 4, ibytes = (size_t)nq * k * 8, sbytes = (size_t)nq * k * 4;
+  int rc;
+  if ((rc = ensure_ws(idx, WS_QUERIES, qbytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_IDS, ibytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_SCORES, sbytes))) return rc;
+  if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
+  if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
+  cudaStream_t s = idx->stream;
+  std::memcpy(idx->h_pin[0], queries_host, qbytes);
+  CK(cudaEventRecord(idx->ev[0], s), "event");
+  CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
+  CK(cudaEventRecord(idx->ev[1], s), "event");
+  uint32_t launches = 0;
+  rc = search_device_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, (uint64_t*)idx->d_ws[WS_OUT_IDS],
+                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches);
+  if (rc) return rc;
+  CK(cudaEventRecord(idx->ev[2], s), "event");
+  char* hp = (char*)idx->h_pin[1];
+  CK(cudaMemcpyAsync(hp, idx->d_ws[WS_OUT_IDS], ibytes, cudaMemcpyDeviceToHost, s), "D2H ids");
+  CK(cudaMemcpyAsync(hp + ibytes, idx->d_ws[WS_OUT_SCORES], sbytes, cudaMemcpyDeviceToHost, s), "D2H scores");
+  CK(cudaEventRecord(idx->ev[3], s), "event");
+  CK(cudaEventSynchronize(idx->ev[3]), "search sync");
+  std::memcpy(out_ids, hp, ibytes);
+  std::memcpy(out_scores, hp + ibytes, sbytes);
+  if (timing) {
+    cudaEventElapsedTime(&timing->h2d_ms, idx->ev[0], idx->ev[1]);
+    cudaEventElapsedTime(&timing->kernel_ms, idx->ev[1], idx->ev[2]);
+    cudaEventElapsedTime(&timing->d2h_ms, idx->ev[2], idx->ev[3]);
+    cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
+    timing->kernel_launches = launches;
+    timing->path = NVDB_B200_PATH_GEMV;
+  }
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float* scores_dev, uint32_t nlists,
+                                uint32_t nq, uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev,
+                                void* stream) {
+  const nvdb_b200_index* idx = nullptr;
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!ids_dev || !scores_dev || !out_ids_dev || !out_scores_dev || nlists == 0)
+    return fail(nullptr, NVDB_B200_ERR_ARG, "merge_topk: bad arguments");
+  CK(cudaSetDevice(device), "cudaSetDevice");
+  CK(merge_lists_launch(ids_dev, scores_dev, nlists, nq, k, out_ids_dev, out_scores_dev, (cudaStream_t)stream),
+     "merge_lists launch");
+  return NVDB_B200_OK;
+}
+
+// =====================================================================================================
+// refine
+// =====================================================================================================
+static int refine_check(const nvdb_b200_index* idx) {
+  if ((idx->dim * elem_size(idx->dtype)) % 16)
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "refine needs a 16-byte row pitch (dim*elem_size % 16 == 0)");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, const uint32_t* cand_ids_dev,
+                               uint32_t Q, uint32_t R, uint32_t K, uint32_t* out_ids_dev, float* out_dist_dev,
+                               void* stream) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (Q == 0 || R == 0 || K == 0) return NVDB_B200_OK;  // src/cuda_refine.cu:853-857
+  if (!queries_dev || !cand_ids_dev || !out_ids_dev) return fail(idx, NVDB_B200_ERR_ARG, "refine: NULL buffer");
+  int rc = refine_check(idx);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  CK(refine_l2_launch((int)idx->dtype, idx->payload, idx->scales, idx->n, idx->dim, queries_dev, cand_ids_dev, Q, R, K,
+                      out_ids_dev, out_dist_dev, stream ? (cudaStream_t)stream : idx->stream),
+     "refine launch");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const uint32_t* cand_ids_host, uint32_t Q,
+                        uint32_t R, uint32_t K, uint32_t* out_ids, float* out_dist, nvdb_b200_timing* timing) {
+  if (timing) *timing = nvdb_b200_timing{};
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (Q == 0 || R == 0 || K == 0) return NVDB_B200_OK;
+  if (!queries_host || !cand_ids_host || !out_ids) return fail(idx, NVDB_B200_ERR_ARG, "refine: NULL buffer");
+  int rc = refine_check(idx);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  const size_t qb = (size_t)Q * idx->dim * 4, cb = (size_t)Q * R * 4, ob = (size_t)Q * K * 4;
+  if ((rc = ensure_ws(idx, WS_QUERIES, qb))) return rc;
+  if ((rc = ensure_ws(idx, WS_CAND, cb))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_IDS32, ob))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_SCORES, ob))) return rc;
+  if ((rc = ensure_pin(idx, 0, qb + cb))) return rc;
+  if ((rc = ensure_pin(idx, 1, 2 * ob))) return rc;
+  cudaStream_t s = idx->stream;
+  char* hin = (char*)idx->h_pin[0];
+  std::memcpy(hin, queries_host, qb);
+  std::memcpy(hin + qb, cand_ids_host, cb);
+  CK(cudaEventRecord(idx->ev[0], s), "event");
+  CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], hin, qb, cudaMemcpyHostToDevice, s), "H2D queries");
+  CK(cudaMemcpyAsync(idx->d_ws[WS_CAND], hin + qb, cb, cudaMemcpyHostToDevice, s), "H2D candidates");
+  CK(cudaEventRecord(idx->ev[1], s), "event");
+  CK(refine_l2_launch((int)idx->dtype, idx->payload, idx->scales, idx->n, idx->dim, (const float*)idx->d_ws[WS_QUERIES],
+                      (const uint32_t*)idx->d_ws[WS_CAND], Q, R, K, (uint32_t*)idx->d_ws[WS_OUT_IDS32],
+                      (float*)idx->d_ws[WS_OUT_SCORES], s),
+     "refine launch");
+  CK(cudaEventRecord(idx->ev[2], s), "event");
+  char* hout = (char*)idx->h_pin[1];
+  CK(cudaMemcpyAsync(hout, idx->d_ws[WS_OUT_IDS32], ob, cudaMemcpyDeviceToHost, s), "D2H ids");
+  if (out_dist) CK(cudaMemcpyAsync(hout + ob, idx->d_ws[WS_OUT_SCORES], ob, cudaMemcpyDeviceToHost, s), "D2H dist");
+  CK(cudaEventRecord(idx->ev[3], s), "event");
+  CK(cudaEventSynchronize(idx->ev[3]), "refine sync");
+  std::memcpy(out_ids, hout, ob);
+  if (out_dist) std::memcpy(out_dist, hout + ob, ob);
+  if (timing) {
+    cudaEventElapsedTime(&timing->h2d_ms, idx->ev[0], idx->ev[1]);
+    cudaEventElapsedTime(&timing->kernel_ms, idx->ev[1], idx->ev[2]);
+    cudaEventElapsedTime(&timing->d2h_ms, idx->ev[2], idx->ev[3]);
+    cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
+    timing->kernel_launches = 1;
+  }
+  return NVDB_B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,114 @@
+"""GPU parity: the CUDA flat scan through the C ABI vs the CPU oracle on the same seeded inputs.
+Bit-exact scores (FP32 summation order of the reference is reproduced), ids equal modulo exact-tie groups."""
+import numpy as np
+import pytest
+
+from _oracle import F16, F32, I8, assert_topk_equal
+
+pytestmark = pytest.mark.gpu
+DT = {"f32": F32, "f16": F16, "i8": I8}
+
+
+def make_base(oracle, dtype, n, d, seed=11):
+    return oracle.synth(dtype, seed, 0, n, d)
+
+
+def check(nv, oracle, dtype, base, scales, queries, k, row_offset=0):
+    with nv.FlatIndexCuda.from_host(base, scales, dtype, row_offset=row_offset) as idx:
+        ids, sc = idx.search_topk_dot_batch(queries, k)
+    oids, osc = oracle.search_batch(dtype, base, scales, queries, k)
+    n = base.shape[0]
+    kk = min(k, n)
+    for qi in range(queries.shape[0]):
+        assert_topk_equal(ids[qi, :kk], sc[qi, :kk], oids[qi, :kk] + row_offset, osc[qi, :kk], what=f"q{qi}")
+        if kk < k:
+            assert np.all(ids[qi, kk:] == np.uint64(0xFFFFFFFFFFFFFFFF))
+            assert np.all(np.isneginf(sc[qi, kk:]))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "i8"])
+@pytest.mark.parametrize("n,d", [(5000, 768), (1000, 384), (257, 64), (40000, 128)])
+@pytest.mark.parametrize("k", [1, 10, 100])
+def test_scan_matches_oracle(nv, oracle, dt, n, d, k):
+    dtype = DT[dt]
+    base, scales = make_base(oracle, dtype, n, d)
+    f = oracle.synth_f32(11, 0, n, d)
+    rng = np.random.default_rng(5)
+    for nq in (1, 3, 8, 13):
+        rows = rng.integers(0, n, nq)
+        queries = f[rows] + (0.01 * rng.standard_normal((nq, d))).astype(np.float32)
+        check(nv, oracle, dtype, base, scales, queries, k)
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "i8"])
+@pytest.mark.parametrize("d", [100, 13, 24, 7, 1, 40])
+def test_scan_ragged_dims_generic_kernel(nv, oracle, dt, d):
+    """dims with scalar tails / rows the tensor map cannot describe go through the generic kernel."""
+    dtype = DT[dt]
+    n = 3001
+    base, scales = make_base(oracle, dtype, n, d, seed=3)
+    rng = np.random.default_rng(6)
+    queries = rng.standard_normal((5, d)).astype(np.float32)
+    check(nv, oracle, dtype, base, scales, queries, 10)
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "i8"])
+def test_scan_ties_duplicated_rows(nv, oracle, dt):
+    """4 identical copies of 2000 rows (SURVEY.md Appendix B tie probe): canonical (score desc, id asc) order."""
+    dtype = DT[dt]
+    b, s = make_base(oracle, dtype, 2000, 128, seed=9)
+    base = np.concatenate([b] * 4)
+    scales = None if s is None else np.concatenate([s] * 4)
+    f = oracle.synth_f32(9, 0, 2000, 128)
+    queries = f[[5, 77]]
+    with nv.FlatIndexCuda.from_host(base, scales, dtype) as idx:
+        ids, sc = idx.search_topk_dot_batch(queries, 6)
+    oids, osc = oracle.search_batch(dtype, base, scales, queries, 6)
+    assert np.array_equal(ids, oids)  # canonical order is exactly reproducible, not only modulo ties
+    assert np.array_equal(sc.view(np.uint32), osc.view(np.uint32))
+
+
+def test_scan_k_larger_than_n_and_row_offset(nv, oracle):
+    base, scales = make_base(oracle, F16, 37, 64)
+    q = oracle.synth_f32(11, 0, 37, 64)[:2]
+    check(nv, oracle, F16, base, scales, q, 50, row_offset=10_000_000_000)
+
+
+def test_scan_all_equal_scores(nv, oracle):
+    base = np.ones((3000, 64), np.float32)
+    q = np.ones((1, 64), np.float32)
+    check(nv, oracle, F32, base, None, q, 10)
+
+
+def test_scan_ascending_scores_worst_case_for_selector(nv, oracle):
+    """Scores strictly increasing with the row id: every row passes the running threshold."""
+    n, d = 20000, 16
+    base = np.zeros((n, d), np.float32)
+    base[:, 0] = np.arange(n, dtype=np.float32)
+    q = np.zeros((1, d), np.float32)
+    q[0, 0] = 1.0
+    check(nv, oracle, F32, base, None, q, 10)
+    check(nv, oracle, F32, base, None, q, 300)
+
+
+def test_errors(nv):
+    with pytest.raises(nv.NvdbError) as e:
+        nv.FlatIndexCuda.from_host(np.zeros((0, 8), np.float32), None, F32)
+    assert "Empty base" in str(e.value)
+    with nv.FlatIndexCuda.from_host(np.zeros((4, 8), np.float32), None, F32) as idx:
+        ids, sc = idx.search_topk_dot_batch(np.zeros((1, 8), np.float32), 0)
+        assert ids.shape == (1, 0)
+        with pytest.raises(nv.NvdbError):
+            idx.search_topk_dot_batch(np.zeros((1, 9), np.float32), 1)
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "i8"])
+def test_device_synth_matches_oracle(nv, oracle, dt):
+    dtype = DT[dt]
+    n, d, seed, first = 1000, 768, 20240229, 123456789
+    with nv.FlatIndexCuda.synthetic(dtype, n, d, seed, first_row=first) as idx:
+        payload, scales = idx.read_rows(0, n)
+    op, osc = oracle.synth(dtype, seed, first, n, d)
+    assert np.array_equal(payload, op)
+    if dtype == I8:
+        assert np.array_equal(scales.view(np.uint32), osc.view(np.uint32))
