@@ -1,0 +1,458 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 flat-scan path (contract: see DESIGN.md "Measurement").
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA kernels through the C ABI)
+  python bench.py --impl reference --gpus N ...            the reference's own CPU flat scan on the host cores
+
+Workload (BASELINE.json configs[1]): FP16 exact flat-scan top-10 over a 2,903,054 x 768 synthetic base,
+batch 1. A "step" is one query batch scanned over the whole base. metric = the reference harness's own
+`payload_equiv_bandwidth_GBps` (apps/nvdb_bench.cpp:414-418): payload bytes scanned per second; QPS is
+reported beside it. At N > 1 every rank holds its own 2,903,054-row shard of an N-times larger index
+(weak scaling); a step = local scan on every rank + NCCL all-gather of the local top-k + merge.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import statistics
+import sys
+import tempfile
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+N_ROWS = 2_903_054          # the reference's full set (Performance.md:195)
+DIM = 768
+TOPK = 10
+SEED = 20240229
+F32, F16, I8 = 1, 2, 3
+ESZ = {F32: 4, F16: 2, I8: 1}
+NQ_POOL = 64                # distinct queries cycled through the steps
+
+
+def payload_bytes(n, dim, dtype):
+    """reference include/nvdb/vecbin_format.h:57-59 (bytes_for_payload_and_aux)"""
+    return n * dim * ESZ[dtype] + (4 * n if dtype == I8 else 0)
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ----------------------------------------------------------------------------------------------------------
+# clocks / throttle sampling during the timed region (NVML, ~every 25 ms)
+# ----------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x100: "display_clock_setting"}
+
+    def __init__(self, device_index):
+        self.samples, self.reason_bits, self.max_mhz, self.err = [], 0, None, None
+        self._stop = threading.Event()
+        self._thread = None
+        self._timed = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # noqa: BLE001
+            self.nv, self.err = None, repr(e)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
+                bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                self.samples.append((self._timed, mhz))
+                if self._timed:
+                    self.reason_bits |= int(bits)
+            except Exception as e:  # noqa: BLE001
+                self.err = repr(e)
+                return
+            time.sleep(0.025)
+
+    def start(self):
+        if self.nv:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def mark_timed(self, on):
+        self._timed = on
+
+    def stop(self):
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=2)
+        timed = [m for t, m in self.samples if t]
+        used = timed or [m for _, m in self.samples]
+        reasons = [name for bit, name in self.REASONS.items() if self.reason_bits & bit]
+        out = {"sm_mhz": statistics.median(used) if used else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+               "samples_in_timed_region": len(timed), "samples_total": len(self.samples)}
+        if self.err:
+            out["error"] = self.err
+        return out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's own OpenMP flat scan on the host cores, bounded sample
+# ----------------------------------------------------------------------------------------------------------
+def cpu_reference_run(sample_payload: np.ndarray, queries: np.ndarray, steps: int, warmup: int, budget_s: float):
+    """Times FlatIndexOMP::search_topk_dot (compiled, unmodified reference in oracle/_ref) over a vecbin file that
+    holds `sample_payload` (f16). Falls back to the C port of the oracle when oracle/_ref is absent.
+    Returns dict(value GB/s, qps, ms_per_step, steps, kind, cores, sample)."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import _oracle as O
+
+    n, d = sample_payload.shape
+    nbytes = payload_bytes(n, d, F16)
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    kind, run = "port", None
+    tmpdir = None
+    if O.REF_SO.exists() or O.REFERENCE_SRC.exists():
+        try:
+            ref = O.Reference()
+            shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+            tmpdir = tempfile.TemporaryDirectory(dir=shm)
+            path = os.path.join(tmpdir.name, "sample_f16.vecbin")
+            O.write_vecbin(path, F16, sample_payload)
+            h = ref.load(path)
+            kind = "reference"
+
+            def run(q):
+                return ref.search(h, q, TOPK, "omp")
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] oracle/_ref unusable ({e!r}); using the C port", file=sys.stderr)
+    if run is None:
+        orc = O.Oracle()
+
+        def run(q):
+            return orc.search(F16, sample_payload, None, q, TOPK, mt=True)
+
+    for i in range(warmup):
+        run(queries[i % len(queries)])
+    t0 = time.perf_counter()
+    done = 0
+    for i in range(steps):
+        run(queries[i % len(queries)])
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    if tmpdir is not None:
+        tmpdir.cleanup()
+    return {"value": nbytes * done / dt / 1e9, "qps_on_sample": done / dt, "ms_per_step": dt / done * 1e3, "steps": done,
+            "kind": kind, "cores": cores,
+            "sample": f"first {n} rows x {d} f16 of the synthetic base ({nbytes / 1e6:.0f} MB), {done} single-query "
+                      f"top-{TOPK} scans, FlatIndexOMP, OMP_NUM_THREADS={os.environ['OMP_NUM_THREADS']}"}
+
+
+def make_cpu_sample(rows: int):
+    """First `rows` rows of the synthetic base as f16 + a pool of f32 queries, generated on the CPU by the
+    oracle's restatement of the generator (bit-identical to the device generator; tests/test_gpu_scan.py)."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import _oracle as O
+    orc = O.Oracle()
+    f = orc.synth_f32(SEED, 0, rows, DIM)
+    payload = orc.to_f16(f)
+    qrows = [(i * 104729) % rows for i in range(NQ_POOL)]
+    return payload, np.ascontiguousarray(f[qrows])
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    rows = int(os.environ.get("NVDB_BENCH_CPU_ROWS", "262144"))
+    payload, queries = make_cpu_sample(rows)
+    r = cpu_reference_run(payload, queries, args.steps, args.warmup, budget_s=150.0)
+    line = {
+        "impl": "reference", "metric": "payload_equiv_bandwidth_GBps", "value": r["value"], "unit": "GB/s",
+        "n_gpus": args.gpus, "steps": r["steps"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"FP16 exact flat-scan top-{TOPK}, {N_ROWS}x{DIM}, batch 1 (BASELINE.json configs[1])",
+                   "note": "reference CPU scan is bandwidth-normalised on a bounded row sample; GB/s is size independent"},
+        "qps_equiv_full_base": r["value"] * 1e9 / payload_bytes(N_ROWS, DIM, F16),
+        "cpu_baseline": {"value": r["value"], "unit": "GB/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback")
+    nv = importlib.import_module("nano-vectordb_b200")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    K, W = args.steps, args.warmup
+    n_rows = int(os.environ.get("NVDB_BENCH_ROWS", N_ROWS))
+    nbytes = payload_bytes(n_rows, DIM, F16)
+
+    # ---- the shard of this rank, generated on the device; global rows [rank*n, (rank+1)*n)
+    idx = nv.FlatIndexCuda.synthetic(F16, n_rows, DIM, SEED, first_row=rank * n_rows, device=local_rank,
+                                     row_offset=rank * n_rows)
+    total_rows = world * n_rows
+    qrows = [(i * 104729 * 31) % total_rows for i in range(NQ_POOL)]   # queries = f32 rows of the (global) base
+    stream = torch.cuda.Stream(device=dev)
+    sp = stream.cuda_stream
+    q_dev = torch.empty((NQ_POOL, DIM), dtype=torch.float32, device=dev)
+    with torch.cuda.stream(stream):
+        for i, r in enumerate(qrows):
+            nv.synth_fill_device(local_rank, F32, 1, DIM, SEED, r, q_dev[i].data_ptr(), None, sp)
+    stream.synchronize()
+    q_host = q_dev.cpu().numpy()
+    out_ids = torch.empty((1, TOPK), dtype=torch.int64, device=dev)
+    out_sc = torch.empty((1, TOPK), dtype=torch.float32, device=dev)
+    if world > 1:
+        g_ids = torch.empty((world, 1, TOPK), dtype=torch.int64, device=dev)
+        g_sc = torch.empty((world, 1, TOPK), dtype=torch.float32, device=dev)
+        f_ids = torch.empty((1, TOPK), dtype=torch.int64, device=dev)
+        f_sc = torch.empty((1, TOPK), dtype=torch.float32, device=dev)
+
+    def step_device(i):
+        idx.search_device(q_dev[i % NQ_POOL].data_ptr(), 1, TOPK, out_ids.data_ptr(), out_sc.data_ptr(), sp)
+        if world > 1:
+            dist.all_gather_into_tensor(g_ids, out_ids)
+            dist.all_gather_into_tensor(g_sc, out_sc)
+            nv.merge_topk_device(local_rank, g_ids.data_ptr(), g_sc.data_ptr(), world, 1, TOPK, f_ids.data_ptr(),
+                                 f_sc.data_ptr(), sp)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        for i in range(W):
+            step_device(i)
+        sync_all()
+        idx.profile(True)
+        l0 = nv.launch_count()
+        sampler.mark_timed(True)
+        ev0.record(stream)
+        for i in range(K):
+            step_device(W + i)
+        ev1.record(stream)
+        sync_all()
+        sampler.mark_timed(False)
+        l1 = nv.launch_count()
+    ms = ev0.elapsed_time(ev1)
+    scan_ms, merge_ms, calls = idx.profile_read()
+    idx.profile(False)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * nbytes * K / (ms * 1e-3) / 1e9
+    qps = K / (ms * 1e-3)
+
+    # ---- end to end through the host-buffer API (H2D of the query + D2H of the result inside the timed region)
+    if world == 1:
+        def step_e2e(i):
+            return idx.search_topk_dot(q_host[i % NQ_POOL], TOPK)
+    else:
+        q_pin = torch.from_numpy(q_host).pin_memory()
+        r_ids = torch.empty((1, TOPK), dtype=torch.int64).pin_memory()
+        r_sc = torch.empty((1, TOPK), dtype=torch.float32).pin_memory()
+        q_stage = torch.empty((DIM,), dtype=torch.float32, device=dev)
+
+        def step_e2e(i):
+            with torch.cuda.stream(stream):
+                q_stage.copy_(q_pin[i % NQ_POOL], non_blocking=True)
+                idx.search_device(q_stage.data_ptr(), 1, TOPK, out_ids.data_ptr(), out_sc.data_ptr(), sp)
+                dist.all_gather_into_tensor(g_ids, out_ids)
+                dist.all_gather_into_tensor(g_sc, out_sc)
+                nv.merge_topk_device(local_rank, g_ids.data_ptr(), g_sc.data_ptr(), world, 1, TOPK, f_ids.data_ptr(),
+                                     f_sc.data_ptr(), sp)
+                r_ids.copy_(f_ids, non_blocking=True)
+                r_sc.copy_(f_sc, non_blocking=True)
+            stream.synchronize()
+            return r_ids, r_sc
+    for i in range(W):
+        step_e2e(i)
+    sync_all()
+    t0 = time.perf_counter()
+    for i in range(K):
+        step_e2e(W + i)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = world * nbytes * K / e2e_s / 1e9
+    clocks = sampler.stop()
+
+    # ---- sanity: the top-1 of a base-row query is the row itself
+    ids0, sc0 = (idx.search_topk_dot(q_host[0], TOPK) if world == 1 else (None, None))
+    if world == 1:
+        assert int(ids0[0]) == qrows[0], f"self-query check failed: {ids0[0]} vs {qrows[0]}"
+
+    peak, peak_src = measured_peaks()
+    kern_ms = scan_ms / max(calls, 1)
+    achieved = nbytes / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else None
+    line = {
+        "metric": "payload_equiv_bandwidth_GBps", "value": value, "unit": "GB/s", "n_gpus": world, "steps": K,
+        "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"FP16 exact flat-scan top-{TOPK}, {n_rows}x{DIM} per GPU, batch 1 (BASELINE.json configs[1])",
+                   "rows_per_gpu": n_rows, "dim": DIM, "k": TOPK, "batch": 1, "base_dtype": "f16",
+                   "l2": f"base ({nbytes / 1e9:.2f} GB) is larger than L2 (126 MB); queries cycle through {NQ_POOL} rows",
+                   "parallelism": f"row-shard x{world}, all-gather + merge" if world > 1 else "single GPU"},
+        "qps": qps,
+        "e2e": {"value": e2e_value, "unit": "GB/s", "qps": K / e2e_s, "ms_per_step": e2e_s / K * 1e3,
+                "h2d_bytes_per_step": DIM * 4, "d2h_bytes_per_step": TOPK * 12,
+                "api": "nvdb_b200_search (host buffers)" if world == 1 else "host query -> H2D -> search_device -> all_gather -> merge -> D2H"},
+        "gpu_launches": int(l1 - l0),
+        "roofline": {"bound": "hbm", "kernel": "scan_gemv_tma_kernel<f16,1>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                     "peak_source": peak_src, "frac_of_nominal_8TBps": (achieved / 8000.0) if achieved else None,
+                     "kernel_ms": kern_ms, "merge_kernel_ms": merge_ms / max(calls, 1),
+                     "algorithmic_bytes_per_launch": nbytes},
+        "clocks": clocks,
+    }
+    ncu_traffic = ROOT / "profiles" / "scan_f16_traffic.json"
+    if ncu_traffic.exists():
+        try:
+            line["roofline"]["traffic"] = json.loads(ncu_traffic.read_text()).get("dram_bytes_per_launch")
+        except Exception:  # noqa: BLE001
+            pass
+    if rank == 0 and world == 1 and not args.no_extras:
+        line["extras"] = run_extras(nv, torch, idx, dev, local_rank, stream, q_dev, args)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        rows = int(os.environ.get("NVDB_BENCH_CPU_ROWS", "262144"))
+        payload, cq = make_cpu_sample(rows)
+        r = cpu_reference_run(payload, cq, steps=400, warmup=3, budget_s=15.0)
+        line["cpu_baseline"] = {"value": r["value"], "unit": "GB/s", "cores": r["cores"], "kind": r["kind"],
+                                "sample": r["sample"], "qps_equiv_full_base": r["value"] * 1e9 / nbytes}
+    idx.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def _time_search(torch, idx, stream, q_dev, nq, k, iters, warm=3):
+    """device-resident timing of `iters` searches of an nq-query batch; returns (ms per batch, scan kernel ms)."""
+    dev = q_dev.device
+    out_ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    out_sc = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    qs = q_dev
+    if qs.shape[0] < nq:
+        qs = qs.repeat((nq + qs.shape[0] - 1) // qs.shape[0], 1)[:nq].contiguous()
+        qs += 1e-3 * torch.randn_like(qs)   # distinct queries
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        for _ in range(warm):
+            idx.search_device(qs.data_ptr(), nq, k, out_ids.data_ptr(), out_sc.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        idx.profile(True)
+        e0.record(stream)
+        for _ in range(iters):
+            idx.search_device(qs.data_ptr(), nq, k, out_ids.data_ptr(), out_sc.data_ptr(), stream.cuda_stream)
+        e1.record(stream)
+        stream.synchronize()
+    scan_ms, _, calls = idx.profile_read()
+    idx.profile(False)
+    return e0.elapsed_time(e1) / iters, scan_ms / max(calls, 1)
+
+
+def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
+    """Other BASELINE.json configs on one GPU, short runs (explanatory numbers, not the headline)."""
+    peak, _ = measured_peaks()
+    ex = {}
+    nb16 = payload_bytes(idx16.count, DIM, F16)
+    sweep = {}
+    for b in (1, 2, 4, 8, 16, 64):
+        ms, kms = _time_search(torch, idx16, stream, q_dev, b, TOPK, iters=max(3, 40 // b))
+        sweep[str(b)] = {"ms_per_batch": ms, "qps": b / ms * 1e3, "base_GBps": nb16 * ((b + 7) // 8) / (kms * 1e-3) / 1e9}
+    ex["fp16_batch_sweep_gemv"] = sweep
+    ms, kms = _time_search(torch, idx16, stream, q_dev, 1, 100, iters=20)
+    ex["fp16_batch1_top100"] = {"ms": ms, "qps": 1e3 / ms}
+    # INT8 (+scale), batch 1 — BASELINE.json configs[2]
+    with nv.FlatIndexCuda.synthetic(I8, idx16.count, DIM, SEED, device=local_rank) as idx8:
+        nb8 = payload_bytes(idx8.count, DIM, I8)
+        ms, kms = _time_search(torch, idx8, stream, q_dev, 1, TOPK, iters=50)
+        ex["int8_batch1"] = {"ms": ms, "qps": 1e3 / ms, "kernel_ms": kms, "GBps": nb8 / (kms * 1e-3) / 1e9,
+                             "roofline_frac": nb8 / (kms * 1e-3) / 1e9 / peak}
+        ms, kms = _time_search(torch, idx8, stream, q_dev, 8, TOPK, iters=10)
+        ex["int8_batch8"] = {"ms_per_batch": ms, "qps": 8e3 / ms}
+    # FP32 500K x 768 — BASELINE.json configs[0]
+    with nv.FlatIndexCuda.synthetic(F32, 500_000, DIM, SEED, device=local_rank) as idx32:
+        nb32 = payload_bytes(500_000, DIM, F32)
+        ms, kms = _time_search(torch, idx32, stream, q_dev, 1, TOPK, iters=50)
+        ex["fp32_500k_batch1"] = {"ms": ms, "qps": 1e3 / ms, "kernel_ms": kms, "GBps": nb32 / (kms * 1e-3) / 1e9,
+                                  "roofline_frac": nb32 / (kms * 1e-3) / 1e9 / peak}
+    # refine: 1M x 768 f16, Q=10000, R=256, K=10 — BASELINE.json configs[4] (synthetic candidate lists)
+    nref, Q, R, Kr = 1_000_000, 10_000, 256, 10
+    with nv.FlatIndexCuda.synthetic(F16, nref, DIM, SEED, device=local_rank) as idxr:
+        g = torch.Generator(device=dev)
+        g.manual_seed(1)
+        cand = torch.randint(0, nref, (Q, R), dtype=torch.int32, device=dev, generator=g)
+        qs = q_dev.repeat((Q + NQ_POOL - 1) // NQ_POOL, 1)[:Q].contiguous()
+        oid = torch.empty((Q, Kr), dtype=torch.int32, device=dev)
+        od = torch.empty((Q, Kr), dtype=torch.float32, device=dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                idxr.refine_l2_device(qs.data_ptr(), cand.data_ptr(), Q, R, Kr, oid.data_ptr(), od.data_ptr(), stream.cuda_stream)
+            e0.record(stream)
+            for _ in range(10):
+                idxr.refine_l2_device(qs.data_ptr(), cand.data_ptr(), Q, R, Kr, oid.data_ptr(), od.data_ptr(), stream.cuda_stream)
+            e1.record(stream)
+            stream.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        gb = (Q * R * DIM * 2 + Q * DIM * 4 + Q * R * 4 + Q * Kr * 8) / 1e9
+        ex["refine_f16_1M_Q10000_R256_K10"] = {"kernel_ms": ms, "us_per_query": ms * 1e3 / Q, "gather_GBps": gb / (ms * 1e-3),
+                                               "roofline_frac": gb / (ms * 1e-3) / peak}
+    return ex
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the other configs (int8 / fp32 / batch sweep / refine)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -126,6 +126,11 @@ int nvdb_b200_synth_fill_device(int device, uint32_t dtype, uint64_t n, uint32_t
 /* ---- introspection for the harness ------------------------------------------------------------------------ */
 /* kernels launched by this library in this process so far (bench.py's gpu_launches). */
 uint64_t nvdb_b200_launch_count(void);
+/* Per-kernel CUDA-event timing of nvdb_b200_search*(): enable, run searches, then read the summed device
+ * time of the scan kernels and of the merge kernel over `calls` searches (read synchronises and resets).
+ * This is the analogue of the reference's ev1->ev2 kernel timing (src/cuda_refine.cu:1147-1157). */
+int nvdb_b200_index_profile(nvdb_b200_index* idx, int enable);
+int nvdb_b200_index_profile_read(nvdb_b200_index* idx, double* scan_ms_sum, double* merge_ms_sum, uint32_t* calls);
 
 #ifdef __cplusplus
 }

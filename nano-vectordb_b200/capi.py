@@ -56,6 +56,8 @@ _sig = {
     "nvdb_b200_refine_l2_device": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_synth_fill_device": (_i, [_i, _u32, _u64, _u32, _u64, _u64, _vp, _vp, _vp]),
     "nvdb_b200_launch_count": (_u64, []),
+    "nvdb_b200_index_profile": (_i, [_vp, _i]),
+    "nvdb_b200_index_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_u32)]),
 }
 for _name, (_res, _args) in _sig.items():
     _f = getattr(lib, _name)
@@ -148,6 +150,14 @@ class FlatIndexCuda:
         scales = np.empty(nrows, np.float32) if self.dtype == I8 else None
         _check(lib.nvdb_b200_index_read_rows(self._h, row0, nrows, _ptr(payload), _ptr(scales)), self._h)
         return payload, scales
+
+    def profile(self, enable=True):
+        _check(lib.nvdb_b200_index_profile(self._h, int(enable)), self._h)
+
+    def profile_read(self):
+        a, b, n = C.c_double(), C.c_double(), _u32()
+        _check(lib.nvdb_b200_index_profile_read(self._h, C.byref(a), C.byref(b), C.byref(n)), self._h)
+        return a.value, b.value, n.value
 
     # ---- search (mirrors FlatIndex::search_topk_dot / batched_scan_*)
     def search_topk_dot(self, q, k, timing: Timing | None = None):

@@ -5,6 +5,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/nvdb_b200.h"
 #include "common.cuh"
@@ -40,6 +41,10 @@ struct nvdb_b200_index {
   size_t h_pin_bytes[2] = {0, 0};
   std::mutex mu;
   mutable std::string err;
+  // optional per-kernel event timing (bench.py's roofline figure)
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_ev;  // triples: before scan passes, after scan passes, after merge
+  size_t prof_used = 0;
 };
 
 namespace {
@@ -215,6 +220,7 @@ int nvdb_b200_index_destroy(nvdb_b200_index* idx) {
     if (p) cudaFreeHost(p);
   for (auto& e : idx->ev)
     if (e) cudaEventDestroy(e);
+  for (auto& e : idx->prof_ev) cudaEventDestroy(e);
   if (idx->stream) cudaStreamDestroy(idx->stream);
   delete idx;
   return NVDB_B200_OK;
@@ -426,6 +432,19 @@ int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq
   a.num_tiles = (uint32_t)((idx->n + kScanRowsPerTile - 1) / kScanRowsPerTile);
   a.kchunks = (uint32_t)(((size_t)idx->dim * elem_size(idx->dtype) + 127) / 128);
   a.stages = plan.stages;
+  cudaEvent_t* pev = nullptr;
+  if (idx->profiling) {
+    if (idx->prof_used + 3 > idx->prof_ev.size()) {
+      for (int i = 0; i < 3; ++i) {
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e), "profile event");
+        idx->prof_ev.push_back(e);
+      }
+    }
+    pev = &idx->prof_ev[idx->prof_used];
+    idx->prof_used += 3;
+    CK(cudaEventRecord(pev[0], stream), "profile event record");
+  }
   for (uint32_t q0 = 0; q0 < nq; q0 += (uint32_t)plan.nq_template) {
     const uint32_t left = nq - q0;
     // shrink the template for the remainder so a tail of 1-2 queries does not pay for 8
@@ -438,8 +457,10 @@ int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq
     count_launch();
     if (launches) ++*launches;
   }
+  if (pev) CK(cudaEventRecord(pev[1], stream), "profile event record");
   CK(merge_partials_launch(partial, (uint32_t)plan.grid, nq, k, idx->row_offset, d_out_ids, d_out_scores, stream),
      "merge_partials launch");
+  if (pev) CK(cudaEventRecord(pev[2], stream), "profile event record");
   if (launches) ++*launches;
   return NVDB_B200_OK;
 }
@@ -586,6 +607,41 @@ int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const u
     cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
     timing->kernel_launches = 1;
   }
+  return NVDB_B200_OK;
+}
+
+}  // extern "C"
+
+// =====================================================================================================
+// per-kernel event timing for the harness
+// =====================================================================================================
+extern "C" {
+
+int nvdb_b200_index_profile(nvdb_b200_index* idx, int enable) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  idx->profiling = enable != 0;
+  idx->prof_used = 0;
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_profile_read(nvdb_b200_index* idx, double* scan_ms_sum, double* merge_ms_sum, uint32_t* calls) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  double a = 0, b = 0;
+  for (size_t i = 0; i + 2 < idx->prof_used + 0 && i + 2 < idx->prof_ev.size() + 0; i += 3) {
+    CK(cudaEventSynchronize(idx->prof_ev[i + 2]), "profile sync");
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, idx->prof_ev[i], idx->prof_ev[i + 1]), "profile elapsed");
+    a += ms;
+    CK(cudaEventElapsedTime(&ms, idx->prof_ev[i + 1], idx->prof_ev[i + 2]), "profile elapsed");
+    b += ms;
+  }
+  if (scan_ms_sum) *scan_ms_sum = a;
+  if (merge_ms_sum) *merge_ms_sum = b;
+  if (calls) *calls = (uint32_t)(idx->prof_used / 3);
+  idx->prof_used = 0;
   return NVDB_B200_OK;
 }
 
