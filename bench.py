@@ -227,19 +227,13 @@ def run_ours(args):
     q_host = q_dev.cpu().numpy()
     out_ids = torch.empty((1, TOPK), dtype=torch.int64, device=dev)
     out_sc = torch.empty((1, TOPK), dtype=torch.float32, device=dev)
-    if world > 1:
-        g_ids = torch.empty((world, 1, TOPK), dtype=torch.int64, device=dev)
-        g_sc = torch.empty((world, 1, TOPK), dtype=torch.float32, device=dev)
-        f_ids = torch.empty((1, TOPK), dtype=torch.int64, device=dev)
-        f_sc = torch.empty((1, TOPK), dtype=torch.float32, device=dev)
+    sharded = nv.ShardedFlatIndex(idx, dev) if world > 1 else None   # local scan -> ONE packed all-gather -> merge
 
     def step_device(i):
-        idx.search_device(q_dev[i % NQ_POOL].data_ptr(), 1, TOPK, out_ids.data_ptr(), out_sc.data_ptr(), sp)
         if world > 1:
-            dist.all_gather_into_tensor(g_ids, out_ids)
-            dist.all_gather_into_tensor(g_sc, out_sc)
-            nv.merge_topk_device(local_rank, g_ids.data_ptr(), g_sc.data_ptr(), world, 1, TOPK, f_ids.data_ptr(),
-                                 f_sc.data_ptr(), sp)
+            sharded.search(q_dev[i % NQ_POOL:i % NQ_POOL + 1], TOPK)
+        else:
+            idx.search_device(q_dev[i % NQ_POOL].data_ptr(), 1, TOPK, out_ids.data_ptr(), out_sc.data_ptr(), sp)
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -287,11 +281,7 @@ def run_ours(args):
         def step_e2e(i):
             with torch.cuda.stream(stream):
                 q_stage.copy_(q_pin[i % NQ_POOL], non_blocking=True)
-                idx.search_device(q_stage.data_ptr(), 1, TOPK, out_ids.data_ptr(), out_sc.data_ptr(), sp)
-                dist.all_gather_into_tensor(g_ids, out_ids)
-                dist.all_gather_into_tensor(g_sc, out_sc)
-                nv.merge_topk_device(local_rank, g_ids.data_ptr(), g_sc.data_ptr(), world, 1, TOPK, f_ids.data_ptr(),
-                                     f_sc.data_ptr(), sp)
+                f_ids, f_sc = sharded.search(q_stage.view(1, DIM), TOPK)
                 r_ids.copy_(f_ids, non_blocking=True)
                 r_sc.copy_(f_sc, non_blocking=True)
             stream.synchronize()
@@ -330,7 +320,7 @@ def run_ours(args):
         "qps": qps,
         "e2e": {"value": e2e_value, "unit": "GB/s", "qps": K / e2e_s, "ms_per_step": e2e_s / K * 1e3,
                 "h2d_bytes_per_step": DIM * 4, "d2h_bytes_per_step": TOPK * 12,
-                "api": "nvdb_b200_search (host buffers)" if world == 1 else "host query -> H2D -> search_device -> all_gather -> merge -> D2H"},
+                "api": "nvdb_b200_search (host buffers)" if world == 1 else "ShardedFlatIndex.search: host query -> H2D -> local scan -> packed all_gather -> merge -> D2H"},
         "gpu_launches": int(l1 - l0),
         "roofline": {"bound": "hbm", "kernel": "scan_gemv_tma_kernel<f16,1>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,

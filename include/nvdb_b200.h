@@ -106,6 +106,11 @@ int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float
                                 uint32_t nq, uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev,
                                 void* stream);
 
+/* Same merge over the PACKED per-rank layout that one all-gather produces (nano-vectordb_b200/sharded.py):
+ * list l starts at packed + l*W 8-byte words, W = nq*k + (nq*k+1)/2, and holds [nq*k u64 ids][nq*k f32 scores]. */
+int nvdb_b200_merge_topk_packed_device(int device, const void* packed_dev, uint32_t nlists, uint32_t nq, uint32_t k,
+                                       uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+
 /* ---- exact refine -------------------------------------------------------------------------------------------
  * Replaces nvdb::cuda_l2_topk_batch: for each of Q queries, squared-L2 distance to its R candidate rows
  * (ids >= n, incl. 0xFFFFFFFF, are skipped), K smallest in ascending order; unfilled slots are

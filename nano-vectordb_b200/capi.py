@@ -52,6 +52,7 @@ _sig = {
     "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_search_device": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_merge_topk_device": (_i, [_i, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_merge_topk_packed_device": (_i, [_i, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_refine_l2_device": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_synth_fill_device": (_i, [_i, _u32, _u64, _u32, _u64, _u64, _vp, _vp, _vp]),
@@ -87,6 +88,10 @@ def synth_fill_device(device, dtype, n, dim, seed, first_row, payload_ptr, scale
 def merge_topk_device(device, ids_ptr, scores_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
     _check(lib.nvdb_b200_merge_topk_device(device, ids_ptr, scores_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr,
                                            stream))
+
+
+def merge_topk_packed_device(device, packed_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
+    _check(lib.nvdb_b200_merge_topk_packed_device(device, packed_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr, stream))
 
 
 class FlatIndexCuda:

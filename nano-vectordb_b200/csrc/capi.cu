@@ -533,7 +533,23 @@ int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float
   if (!ids_dev || !scores_dev || !out_ids_dev || !out_scores_dev || nlists == 0)
     return fail(nullptr, NVDB_B200_ERR_ARG, "merge_topk: bad arguments");
   CK(cudaSetDevice(device), "cudaSetDevice");
-  CK(merge_lists_launch(ids_dev, scores_dev, nlists, nq, k, out_ids_dev, out_scores_dev, (cudaStream_t)stream),
+  CK(merge_lists_launch(ids_dev, scores_dev, (size_t)nq * k, (size_t)nq * k, nlists, nq, k, out_ids_dev, out_scores_dev,
+                        (cudaStream_t)stream),
+     "merge_lists launch");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_merge_topk_packed_device(int device, const void* packed_dev, uint32_t nlists, uint32_t nq, uint32_t k,
+                                       uint64_t* out_ids_dev, float* out_scores_dev, void* stream) {
+  const nvdb_b200_index* idx = nullptr;
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!packed_dev || !out_ids_dev || !out_scores_dev || nlists == 0)
+    return fail(nullptr, NVDB_B200_ERR_ARG, "merge_topk_packed: bad arguments");
+  CK(cudaSetDevice(device), "cudaSetDevice");
+  const size_t nk = (size_t)nq * k, words = nk + (nk + 1) / 2;
+  const uint64_t* ids = (const uint64_t*)packed_dev;
+  const float* scores = (const float*)(ids + nk);
+  CK(merge_lists_launch(ids, scores, words, 2 * words, nlists, nq, k, out_ids_dev, out_scores_dev, (cudaStream_t)stream),
      "merge_lists launch");
   return NVDB_B200_OK;
 }

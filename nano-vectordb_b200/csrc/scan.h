@@ -39,9 +39,11 @@ cudaError_t scan_gemv_launch(const ScanLaunch& l, const ScanArgs& a, int nq_temp
 // partial [nq][nlists][k] keys -> final ids / scores [nq][k]
 cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
                                   uint64_t row_offset, uint64_t* out_ids, float* out_scores, cudaStream_t stream);
-// per-shard results [nlists][nq][k] (global ids, scores) -> [nq][k]
-cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, uint32_t nlists, uint32_t nq, uint32_t k,
-                               uint64_t* out_ids, float* out_scores, cudaStream_t stream);
+// per-shard results (global ids, scores), list l at ids + l*id_list_stride / scores + l*score_list_stride, each
+// [nq][k] -> [nq][k]
+cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, size_t id_list_stride,
+                               size_t score_list_stride, uint32_t nlists, uint32_t nq, uint32_t k, uint64_t* out_ids,
+                               float* out_scores, cudaStream_t stream);
 
 cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim,
                              const float* queries, const uint32_t* cand, uint32_t Q, uint32_t R, uint32_t K,

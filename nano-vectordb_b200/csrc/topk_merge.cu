@@ -49,8 +49,9 @@ __device__ __forceinline__ bool better(uint32_t sa, uint64_t ia, uint32_t pa, ui
 }
 
 __global__ void __launch_bounds__(256)
-merge_lists_kernel(const uint64_t* __restrict__ ids, const float* __restrict__ scores, uint32_t nlists, uint32_t nq,
-                   uint32_t k, uint64_t* __restrict__ out_ids, float* __restrict__ out_scores) {
+merge_lists_kernel(const uint64_t* __restrict__ ids, const float* __restrict__ scores, size_t id_list_stride,
+                   size_t score_list_stride, uint32_t nlists, uint32_t nq, uint32_t k, uint64_t* __restrict__ out_ids,
+                   float* __restrict__ out_scores) {
   extern __shared__ uint64_t sm[];
   const uint32_t L = nlists * k;
   uint64_t* sid = sm;                                      // [L]
@@ -58,10 +59,10 @@ merge_lists_kernel(const uint64_t* __restrict__ ids, const float* __restrict__ s
   const uint32_t q = blockIdx.x, tid = threadIdx.x;
   for (uint32_t e = tid; e < L; e += blockDim.x) {
     const uint32_t l = e / k, j = e - l * k;
-    const size_t src = ((size_t)l * nq + q) * k + j;
-    const uint64_t id = ids[src];
+    const size_t src = (size_t)q * k + j;
+    const uint64_t id = ids[(size_t)l * id_list_stride + src];
     sid[e] = id;
-    ssc[e] = (id == ~0ull) ? 0u : float_to_ordered(scores[src]);
+    ssc[e] = (id == ~0ull) ? 0u : float_to_ordered(scores[(size_t)l * score_list_stride + src]);
   }
   for (uint32_t j = tid; j < k; j += blockDim.x) {
     out_ids[(size_t)q * k + j] = ~0ull;
@@ -102,8 +103,9 @@ cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint
   return cudaGetLastError();
 }
 
-cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, uint32_t nlists, uint32_t nq, uint32_t k,
-                               uint64_t* out_ids, float* out_scores, cudaStream_t stream) {
+cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, size_t id_list_stride,
+                               size_t score_list_stride, uint32_t nlists, uint32_t nq, uint32_t k, uint64_t* out_ids,
+                               float* out_scores, cudaStream_t stream) {
   if (nq == 0 || k == 0) return cudaSuccess;
   const size_t smem = (size_t)nlists * k * 12u + 8u;
   if (smem > 200u * 1024u) return cudaErrorInvalidValue;
@@ -111,7 +113,8 @@ cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, uint32_
     cudaError_t e = cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  merge_lists_kernel<<<nq, 256, smem, stream>>>(ids, scores, nlists, nq, k, out_ids, out_scores);
+  merge_lists_kernel<<<nq, 256, smem, stream>>>(ids, scores, id_list_stride, score_list_stride, nlists, nq, k, out_ids,
+                                                out_scores);
   count_launch();
   return cudaGetLastError();
 }
