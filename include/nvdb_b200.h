@@ -45,7 +45,9 @@ enum { NVDB_B200_F32 = 1, NVDB_B200_F16 = 2, NVDB_B200_I8 = 3 };
 enum {
   NVDB_B200_PATH_AUTO = 0, /* GEMV for small batches, tensor-core GEMM above the crossover */
   NVDB_B200_PATH_GEMV = 1, /* bit-exact FP32-FMA streaming scan (all dtypes) */
-  NVDB_B200_PATH_MMA = 2   /* tcgen05 tensor-core scan (f16 / i8), tolerance-mode parity */
+  NVDB_B200_PATH_MMA = 2,  /* tcgen05 tensor-core scan (f16: query = fp16 hi + lo limbs; i8: two int8 query limbs,
+                              exact int32 limb dot products), tolerance-mode parity vs the FP32-FMA reference */
+  NVDB_B200_PATH_MMA_FAST = 3 /* f16 only: single fp16 query limb (half the tensor work, ~5e-5 relative error) */
 };
 
 typedef struct nvdb_b200_index nvdb_b200_index;
@@ -110,6 +112,13 @@ int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float
  * list l starts at packed + l*W 8-byte words, W = nq*k + (nq*k+1)/2, and holds [nq*k u64 ids][nq*k f32 scores]. */
 int nvdb_b200_merge_topk_packed_device(int device, const void* packed_dev, uint32_t nlists, uint32_t nq, uint32_t k,
                                        uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+
+/* Test hook for the tensor-core scan: runs the NVDB_B200_PATH_MMA / _MMA_FAST scan of `nq` host queries (k = 1) and
+ * returns the RAW accumulators of every (query, row) pair: f16 base -> out_acc[nq][n] float bit patterns (before
+ * the power-of-two rescale); i8 base -> out_acc[2][nq][n] int32 limb dot products I1, I2 (exact integers).
+ * Small cases only (nq * n * 8 bytes of device scratch). */
+int nvdb_b200_debug_mma_accumulators(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, int path,
+                                     uint32_t* out_acc);
 
 /* ---- exact refine -------------------------------------------------------------------------------------------
  * Replaces nvdb::cuda_l2_topk_batch: for each of Q queries, squared-L2 distance to its R candidate rows

@@ -13,7 +13,7 @@ from pathlib import Path
 import numpy as np
 
 F32, F16, I8 = 1, 2, 3
-PATH_AUTO, PATH_GEMV, PATH_MMA = 0, 1, 2
+PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST = 0, 1, 2, 3
 _NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
 
 lib_path = Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"
@@ -51,6 +51,7 @@ _sig = {
     "nvdb_b200_index_read_rows": (_i, [_vp, _u64, _u64, _vp, _vp]),
     "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_search_device": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_debug_mma_accumulators": (_i, [_vp, _vp, _u32, _i, _vp]),
     "nvdb_b200_merge_topk_device": (_i, [_i, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_merge_topk_packed_device": (_i, [_i, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
@@ -155,6 +156,15 @@ class FlatIndexCuda:
         scales = np.empty(nrows, np.float32) if self.dtype == I8 else None
         _check(lib.nvdb_b200_index_read_rows(self._h, row0, nrows, _ptr(payload), _ptr(scales)), self._h)
         return payload, scales
+
+    def debug_mma_accumulators(self, queries, path=PATH_MMA):
+        """raw tensor-core accumulators: f16 -> float32 [nq, n]; i8 -> int32 [2, nq, n] (exact limb dot products)"""
+        queries = np.ascontiguousarray(queries, np.float32)
+        nq = queries.shape[0]
+        nacc = 2 if self.dtype == I8 else 1
+        out = np.zeros((nacc, nq, self.count), np.uint32)
+        _check(lib.nvdb_b200_debug_mma_accumulators(self._h, _ptr(queries), nq, path, _ptr(out)), self._h)
+        return out.view(np.int32) if self.dtype == I8 else out[0].view(np.float32)
 
     def profile(self, enable=True):
         _check(lib.nvdb_b200_index_profile(self._h, int(enable)), self._h)

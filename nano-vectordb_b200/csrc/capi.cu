@@ -34,9 +34,15 @@ struct nvdb_b200_index {
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   bool tma_ok = false;
   CUtensorMap tmap;
+  // tensor-core scan: base tensor map with box rows = scan_mma_block_n(dtype); query (A operand) tensor map cache
+  bool mma_ok = false;
+  CUtensorMap tmap_mma_b;   // box rows 128 (the streaming scan's `tmap` has 256-row boxes and serves the 256-row tiles)
+  CUtensorMap tmap_mma_a;
+  const void* tmap_a_ptr = nullptr;
+  uint32_t tmap_a_rows = 0;
   // grow-only workspaces
-  void* d_ws[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  size_t d_ws_bytes[6] = {0, 0, 0, 0, 0, 0};
+  void* d_ws[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t d_ws_bytes[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   void* h_pin[2] = {nullptr, nullptr};
   size_t h_pin_bytes[2] = {0, 0};
   std::mutex mu;
@@ -50,7 +56,8 @@ struct nvdb_b200_index {
 namespace {
 
 thread_local std::string t_err;
-enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5 };
+enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5, WS_MMA_A = 6,
+       WS_MMA_QS = 7, WS_DBG = 8 };
 
 int fail(const nvdb_b200_index* idx, int code, const std::string& msg) {
   t_err = msg;
@@ -123,23 +130,35 @@ bool tma_eligible(const nvdb_b200_index* idx) {
   return true;
 }
 
-int build_tmap(nvdb_b200_index* idx) {
-  idx->tma_ok = false;
-  if (!tma_eligible(idx)) return NVDB_B200_OK;
+int encode_2d(const nvdb_b200_index* idx, CUtensorMap* out, uint32_t dtype, const void* ptr, uint64_t rows, uint32_t dim,
+              uint32_t box_rows) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return fail(idx, NVDB_B200_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
-  const size_t es = elem_size(idx->dtype);
-  const CUtensorMapDataType dt = idx->dtype == kDtF32   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
-                                 : idx->dtype == kDtF16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
-                                                        : CU_TENSOR_MAP_DATA_TYPE_UINT8;
-  cuuint64_t gdim[2] = {idx->dim, idx->n};
-  cuuint64_t gstride[1] = {(cuuint64_t)idx->dim * es};
-  cuuint32_t box[2] = {(cuuint32_t)(128 / es), (cuuint32_t)kScanRowsPerTile};
+  const size_t es = elem_size(dtype);
+  const CUtensorMapDataType dt = dtype == kDtF32   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : dtype == kDtF16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                   : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  cuuint64_t gdim[2] = {dim, rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)dim * es};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / es), box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(&idx->tmap, dt, 2, idx->payload, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  CUresult r = enc(out, dt, 2, const_cast<void*>(ptr), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(idx, NVDB_B200_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
+  return NVDB_B200_OK;
+}
+
+int build_tmap(nvdb_b200_index* idx) {
+  idx->tma_ok = idx->mma_ok = false;
+  if (!tma_eligible(idx)) return NVDB_B200_OK;
+  int rc = encode_2d(idx, &idx->tmap, idx->dtype, idx->payload, idx->n, idx->dim, (uint32_t)kScanRowsPerTile);
+  if (rc) return rc;
   idx->tma_ok = true;
+  if (idx->dtype == kDtF16 || idx->dtype == kDtI8) {
+    rc = encode_2d(idx, &idx->tmap_mma_b, idx->dtype, idx->payload, idx->n, idx->dim, 128u);
+    if (rc) return rc;
+    idx->mma_ok = true;
+  }
   return NVDB_B200_OK;
 }
 
@@ -343,7 +362,7 @@ int nvdb_b200_index_info(const nvdb_b200_index* idx, uint64_t* n, uint32_t* dim,
 
 int nvdb_b200_index_set_path(nvdb_b200_index* idx, int path) {
   if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
-  if (path < NVDB_B200_PATH_AUTO || path > NVDB_B200_PATH_MMA) return fail(idx, NVDB_B200_ERR_ARG, "bad path");
+  if (path < NVDB_B200_PATH_AUTO || path > NVDB_B200_PATH_MMA_FAST) return fail(idx, NVDB_B200_ERR_ARG, "bad path");
   idx->path = path;
   return NVDB_B200_OK;
 }
@@ -408,8 +427,97 @@ int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) 
   return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "dim / k too large for shared memory");
 }
 
-int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
-                       float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
+int prof_begin(nvdb_b200_index* idx, cudaStream_t stream, cudaEvent_t** pev) {
+  *pev = nullptr;
+  if (!idx->profiling) return NVDB_B200_OK;
+  if (idx->prof_used + 3 > idx->prof_ev.size()) {
+    for (int i = 0; i < 3; ++i) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e), "profile event");
+      idx->prof_ev.push_back(e);
+    }
+  }
+  *pev = &idx->prof_ev[idx->prof_used];
+  idx->prof_used += 3;
+  CK(cudaEventRecord((*pev)[0], stream), "profile event record");
+  return NVDB_B200_OK;
+}
+
+// ---- tensor-core path: prep (limb split) -> scan_mma_kernel -> merge of the per-CTA lists -------------------
+// `dbg` (tests only): raw accumulators [NACC][mpad][n]; mpad_out receives the padded query count.
+int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                    float* d_out_scores, cudaStream_t stream, uint32_t* launches, int limbs, void* dbg) {
+  if (!idx->mma_ok)
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED,
+                "tensor-core scan needs an f16 / i8 base with a 16-byte row pitch and whole 8/16-element chains");
+  if (idx->dtype == kDtI8) limbs = 2;
+  int stages = 0;
+  uint32_t block_n = 0;
+  if (!scan_mma_plan((int)idx->dtype, limbs, k, idx->max_smem, &block_n, &stages))
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "k too large for the tensor-core scan's shared memory");
+  const size_t es = elem_size(idx->dtype);
+  const uint32_t max_q = 128u * (uint32_t)idx->num_sms;
+  cudaEvent_t* pev = nullptr;
+  int rc = prof_begin(idx, stream, &pev);
+  if (rc) return rc;
+  // every pass handles up to 128 * num_sms queries; G M-tiles x P CTAs each
+  uint32_t maxP = 1;
+  for (uint32_t q0 = 0; q0 < nq; q0 += max_q) {
+    const uint32_t g = ((nq - q0 < max_q ? nq - q0 : max_q) + 127u) / 128u;
+    const uint32_t p_ = (uint32_t)idx->num_sms / g;
+    if (p_ > maxP) maxP = p_;
+  }
+  if ((rc = ensure_ws(idx, WS_PARTIAL, (size_t)nq * maxP * k * 8))) return rc;
+  for (uint32_t q0 = 0; q0 < nq; q0 += max_q) {
+    const uint32_t nqp = nq - q0 < max_q ? nq - q0 : max_q;
+    MmaArgs a{};
+    a.G = (nqp + 127u) / 128u;
+    a.P = (uint32_t)idx->num_sms / a.G;
+    a.mpad = a.G * 128u;
+    a.num_tiles = (uint32_t)((idx->n + block_n - 1) / block_n);
+    if (a.P > a.num_tiles) a.P = a.num_tiles;
+    if ((rc = ensure_ws(idx, WS_MMA_A, (size_t)limbs * a.mpad * idx->dim * es))) return rc;
+    if ((rc = ensure_ws(idx, WS_MMA_QS, (size_t)2 * a.mpad * 4))) return rc;
+    void* A = idx->d_ws[WS_MMA_A];
+    float* qs1 = (float*)idx->d_ws[WS_MMA_QS];
+    float* qs2 = qs1 + a.mpad;
+    if (idx->tmap_a_ptr != A || idx->tmap_a_rows != (uint32_t)limbs * a.mpad) {
+      if ((rc = encode_2d(idx, &idx->tmap_mma_a, idx->dtype, A, (uint64_t)limbs * a.mpad, idx->dim, 128u))) return rc;
+      idx->tmap_a_ptr = A;
+      idx->tmap_a_rows = (uint32_t)limbs * a.mpad;
+    }
+    CK(scan_mma_prep_launch((int)idx->dtype, limbs, d_queries + (size_t)q0 * idx->dim, nqp, idx->dim, a.mpad, A, qs1, qs2,
+                            stream),
+       "mma query prep launch");
+    a.scales = idx->scales;
+    a.qscale = qs1;
+    a.qscale2 = qs2;
+    a.partial = (uint64_t*)idx->d_ws[WS_PARTIAL];
+    a.dbg = dbg;
+    a.n_rows = (uint32_t)idx->n;
+    a.dim = idx->dim;
+    a.k = k;
+    a.nq = nqp;
+    a.kchunks = (uint32_t)(((size_t)idx->dim * es + 127) / 128);
+    a.stages = stages;
+    a.block_n = block_n;
+    a.evict_first_base = (a.G == 1);
+    CK(scan_mma_launch((int)idx->dtype, limbs, &idx->tmap_mma_a, block_n == 256 ? &idx->tmap : &idx->tmap_mma_b, a, stream),
+       "scan_mma launch");
+    if (launches) *launches += 2;
+    // merge this pass right away (the partial buffer is reused by the next pass)
+    if (pev && q0 + max_q >= nq) CK(cudaEventRecord(pev[1], stream), "profile event record");
+    CK(merge_partials_launch(a.partial, a.P, nqp, k, idx->row_offset, d_out_ids + (size_t)q0 * k,
+                             d_out_scores + (size_t)q0 * k, stream),
+       "merge_partials launch");
+    if (launches) ++*launches;
+  }
+  if (pev) CK(cudaEventRecord(pev[2], stream), "profile event record");
+  return NVDB_B200_OK;
+}
+
+int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                     float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
   ScanPlan plan;
   int rc = plan_scan(idx, nq, k, &plan);
   if (rc) return rc;
@@ -433,18 +541,7 @@ int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq
   a.kchunks = (uint32_t)(((size_t)idx->dim * elem_size(idx->dtype) + 127) / 128);
   a.stages = plan.stages;
   cudaEvent_t* pev = nullptr;
-  if (idx->profiling) {
-    if (idx->prof_used + 3 > idx->prof_ev.size()) {
-      for (int i = 0; i < 3; ++i) {
-        cudaEvent_t e;
-        CK(cudaEventCreate(&e), "profile event");
-        idx->prof_ev.push_back(e);
-      }
-    }
-    pev = &idx->prof_ev[idx->prof_used];
-    idx->prof_used += 3;
-    CK(cudaEventRecord(pev[0], stream), "profile event record");
-  }
+  if ((rc = prof_begin(idx, stream, &pev))) return rc;
   for (uint32_t q0 = 0; q0 < nq; q0 += (uint32_t)plan.nq_template) {
     const uint32_t left = nq - q0;
     // shrink the template for the remainder so a tail of 1-2 queries does not pay for 8
@@ -465,6 +562,27 @@ int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq
   return NVDB_B200_OK;
 }
 
+// AUTO: the bit-exact streaming scan for the smallest batches, tensor cores from kMmaCrossover queries on
+// (the GEMV scan re-reads the base once per 8 queries; the tensor-core scan reads it once per 128 * num_sms).
+constexpr uint32_t kMmaCrossover = 4;
+
+int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                       float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* path_used) {
+  int path = idx->path;
+  if (path == NVDB_B200_PATH_AUTO)
+  {
+    uint32_t bn;
+    int st;
+    path = (idx->mma_ok && nq >= kMmaCrossover && scan_mma_plan((int)idx->dtype, 2, k, idx->max_smem, &bn, &st))
+               ? NVDB_B200_PATH_MMA
+               : NVDB_B200_PATH_GEMV;
+  }
+  if (path_used) *path_used = (uint32_t)path;
+  if (path == NVDB_B200_PATH_GEMV) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
+  return mma_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches,
+                         path == NVDB_B200_PATH_MMA_FAST ? 1 : 2, nullptr);
+}
+
 }  // namespace
 
 extern "C" {
@@ -478,7 +596,7 @@ int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint
   std::lock_guard<std::mutex> g(idx->mu);
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
   return search_device_impl(idx, queries_dev, nq, k, out_ids_dev, out_scores_dev,
-                            stream ? (cudaStream_t)stream : idx->stream, nullptr);
+                            stream ? (cudaStream_t)stream : idx->stream, nullptr, nullptr);
 }
 
 int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, uint32_t k, uint64_t* out_ids,
@@ -502,9 +620,9 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   CK(cudaEventRecord(idx->ev[0], s), "event");
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
   CK(cudaEventRecord(idx->ev[1], s), "event");
-  uint32_t launches = 0;
+  uint32_t launches = 0, path_used = 0;
   rc = search_device_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, (uint64_t*)idx->d_ws[WS_OUT_IDS],
-                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches);
+                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches, &path_used);
   if (rc) return rc;
   CK(cudaEventRecord(idx->ev[2], s), "event");
   char* hp = (char*)idx->h_pin[1];
@@ -520,8 +638,38 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
     cudaEventElapsedTime(&timing->d2h_ms, idx->ev[2], idx->ev[3]);
     cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
     timing->kernel_launches = launches;
-    timing->path = NVDB_B200_PATH_GEMV;
+    timing->path = path_used;
   }
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_debug_mma_accumulators(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, int path,
+                                     uint32_t* out_acc) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (!queries_host || !out_acc || nq == 0) return fail(idx, NVDB_B200_ERR_ARG, "debug_mma: bad arguments");
+  if (path != NVDB_B200_PATH_MMA && path != NVDB_B200_PATH_MMA_FAST) return fail(idx, NVDB_B200_ERR_ARG, "bad path");
+  if (nq > 128u * (uint32_t)idx->num_sms) return fail(idx, NVDB_B200_ERR_ARG, "debug_mma: too many queries");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  const uint32_t nacc = idx->dtype == kDtI8 ? 2u : 1u, mpad = (nq + 127u) / 128u * 128u;
+  const size_t qbytes = (size_t)nq * idx->dim * 4, dbytes = (size_t)nacc * mpad * idx->n * 4;
+  int rc;
+  if ((rc = ensure_ws(idx, WS_QUERIES, qbytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_IDS, (size_t)nq * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_SCORES, (size_t)nq * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_DBG, dbytes))) return rc;
+  cudaStream_t s = idx->stream;
+  CK(cudaMemsetAsync(idx->d_ws[WS_DBG], 0, dbytes, s), "memset");
+  CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], queries_host, qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
+  rc = mma_search_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, 1, (uint64_t*)idx->d_ws[WS_OUT_IDS],
+                       (float*)idx->d_ws[WS_OUT_SCORES], s, nullptr, path == NVDB_B200_PATH_MMA_FAST ? 1 : 2,
+                       idx->d_ws[WS_DBG]);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(s), "debug_mma sync");
+  for (uint32_t a = 0; a < nacc; ++a)
+    CK(cudaMemcpy(out_acc + (size_t)a * nq * idx->n, (const uint32_t*)idx->d_ws[WS_DBG] + (size_t)a * mpad * idx->n,
+                  (size_t)nq * idx->n * 4, cudaMemcpyDeviceToHost),
+       "D2H accumulators");
   return NVDB_B200_OK;
 }
 

@@ -52,6 +52,29 @@ cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, u
 cudaError_t synth_fill_launch(int dtype, uint64_t n, uint32_t dim, uint64_t seed, uint64_t first_row, void* payload,
                               float* scales, cudaStream_t stream);
 
+// ---- tensor-core scan (scan_mma.cu)
+struct MmaArgs {
+  const float* scales;   // [n_rows] row scales (i8) or null
+  const float* qscale;   // [mpad]  f16: 2^-e of the query prescale;  i8: s1
+  const float* qscale2;  // [mpad]  i8: s2
+  uint64_t* partial;     // [nq][P][k] ordered keys (0 = empty)
+  void* dbg;             // optional raw accumulators [NACC][mpad][n_rows] (tests only), else null
+  uint32_t n_rows, dim, k, nq;
+  uint32_t num_tiles;    // ceil(n_rows / BLOCK_N)
+  uint32_t kchunks;      // ceil(dim * elem_size / 128)
+  uint32_t G, P;         // M-tiles (128 queries each), CTAs per M-tile; grid = G * P
+  uint32_t mpad;         // G * 128
+  uint32_t block_n;      // base rows per tile (template selector; the base tensor map's box rows)
+  int stages;
+  int evict_first_base;  // base tiles are read once (G == 1): keep them out of L2
+};
+
+bool scan_mma_plan(int dtype, int limbs, uint32_t k, int max_smem, uint32_t* block_n, int* stages);
+cudaError_t scan_mma_prep_launch(int dtype, int limbs, const float* queries, uint32_t nq, uint32_t dim, uint32_t mpad,
+                                 void* A, float* qs1, float* qs2, cudaStream_t stream);
+cudaError_t scan_mma_launch(int dtype, int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
+                            cudaStream_t stream);
+
 void count_launch(uint32_t n = 1);
 
 }  // namespace nvdb_b200

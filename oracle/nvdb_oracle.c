@@ -438,3 +438,80 @@ void orc_synth_rows_f32(uint64_t seed, uint64_t row0, uint64_t nrows, uint32_t d
     for (uint32_t j = 0; j < dim; ++j)
       out[(size_t)r * dim + j] = (float)orc_synth_i16(seed, (row0 + (uint64_t)r) * dim + j) * c;
 }
+
+/* ---------------------------------------------------------------- tensor-core scan: query limb schemes (ours)
+ * Restatement of nano-vectordb_b200/csrc/scan_mma.cu's query preparation and epilogue arithmetic, so that the
+ * kind::i8 path can be checked bit-for-bit and the kind::f16 path against its exact real-number value. These are
+ * not reference functions (the reference has no quantised-query path); the parity of the final
+ * scores against the reference's AVX2 kernels is checked with a tolerance in tests/test_gpu_scan_mma.py. */
+
+/* q ~= s1*q1 + s2*q2 with int8 limbs (two limbs) */
+void orc_query_limbs_i8(const float* q, uint32_t dim, int8_t* q1, int8_t* q2, float* s1_out, float* s2_out) {
+  float amax = 0.f;
+  for (uint32_t i = 0; i < dim; ++i) amax = fmaxf(amax, fabsf(q[i]));
+  const float s1 = (amax > 0.f && amax < INFINITY) ? amax / 127.f : 1.f;
+  const float inv1 = 1.f / s1;
+  const float s2 = s1 / 254.f;
+  const float inv2 = 1.f / s2;
+  for (uint32_t i = 0; i < dim; ++i) {
+    long a = lrintf(q[i] * inv1);
+    a = a > 127 ? 127 : (a < -127 ? -127 : a);
+    const float r = fmaf(-(float)a, s1, q[i]);
+    long b = lrintf(r * inv2);
+    b = b > 127 ? 127 : (b < -127 ? -127 : b);
+    q1[i] = (int8_t)a;
+    q2[i] = (int8_t)b;
+  }
+  *s1_out = s1;
+  *s2_out = s2;
+}
+
+/* exact int32 limb dot products + the epilogue's fixed FP32 combination */
+float orc_dot_i8_limbs(const int8_t* q1, const int8_t* q2, float s1, float s2, const int8_t* x, uint32_t dim,
+                       float scale, int32_t* i1_out, int32_t* i2_out) {
+  int32_t i1 = 0, i2 = 0;
+  for (uint32_t i = 0; i < dim; ++i) {
+    i1 += (int32_t)q1[i] * (int32_t)x[i];
+    i2 += (int32_t)q2[i] * (int32_t)x[i];
+  }
+  if (i1_out) *i1_out = i1;
+  if (i2_out) *i2_out = i2;
+  const float t = s1 * (float)i1;
+  return fmaf(s2, (float)i2, t) * scale;
+}
+
+/* all rows of an i8 base against one query under the limb scheme */
+void orc_score_all_i8_limbs(const int8_t* payload, const float* scales, uint64_t n, uint32_t dim, const float* q,
+                            float* out_scores, int32_t* out_i1, int32_t* out_i2) {
+  int8_t* q1 = (int8_t*)malloc(dim);
+  int8_t* q2 = (int8_t*)malloc(dim);
+  float s1, s2;
+  orc_query_limbs_i8(q, dim, q1, q2, &s1, &s2);
+#pragma omp parallel for schedule(static)
+  for (int64_t r = 0; r < (int64_t)n; ++r) {
+    int32_t a, b;
+    out_scores[r] = orc_dot_i8_limbs(q1, q2, s1, s2, payload + (size_t)r * dim, dim, scales[r], &a, &b);
+    if (out_i1) out_i1[r] = a;
+    if (out_i2) out_i2[r] = b;
+  }
+  free(q1);
+  free(q2);
+}
+
+/* f16 limbs: v = q * 2^e with max|v| in [0.5,1); hi = fp16(v), lo = fp16(v - hi); qscale = 2^-e */
+void orc_query_limbs_f16(const float* q, uint32_t dim, uint16_t* hi, uint16_t* lo, float* qscale_out) {
+  float amax = 0.f;
+  for (uint32_t i = 0; i < dim; ++i) amax = fmaxf(amax, fabsf(q[i]));
+  int e = 0;
+  if (amax > 0.f && amax < INFINITY) {
+    e = -(ilogbf(amax) + 1);
+    e = e > 100 ? 100 : (e < -100 ? -100 : e);
+  }
+  for (uint32_t i = 0; i < dim; ++i) {
+    const float v = scalbnf(q[i], e);
+    const uint16_t h = orc_f32_to_f16_rne(v);
+    hi[i] = h;
+    lo[i] = orc_f32_to_f16_rne(v - orc_f16_to_f32(h));
+  }
+  *qscale_out = scalbnf(1.0f, -e);
+}

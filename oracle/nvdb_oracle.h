@@ -42,6 +42,14 @@ void orc_refine_l2(int mode, const void* payload, const float* scales, uint32_t 
                    const float* queries, const uint32_t* cand, uint32_t Q, uint32_t R, uint32_t K,
                    uint32_t* out_ids, float* out_dist);
 
+/* tensor-core scan limb schemes (restatement of nano-vectordb_b200/csrc/scan_mma.cu, not of the reference) */
+void orc_query_limbs_i8(const float* q, uint32_t dim, int8_t* q1, int8_t* q2, float* s1_out, float* s2_out);
+float orc_dot_i8_limbs(const int8_t* q1, const int8_t* q2, float s1, float s2, const int8_t* x, uint32_t dim,
+                       float scale, int32_t* i1_out, int32_t* i2_out);
+void orc_score_all_i8_limbs(const int8_t* payload, const float* scales, uint64_t n, uint32_t dim, const float* q,
+                            float* out_scores, int32_t* out_i1, int32_t* out_i2);
+void orc_query_limbs_f16(const float* q, uint32_t dim, uint16_t* hi, uint16_t* lo, float* qscale_out);
+
 /* synthetic base generator (ours, not the reference's): integer hash -> exactly reproducible anywhere */
 int32_t orc_synth_i16(uint64_t seed, uint64_t global_index);
 void orc_synth_rows_f32(uint64_t seed, uint64_t row0, uint64_t nrows, uint32_t dim, float* out);

@@ -75,6 +75,11 @@ class Oracle:
         L.orc_refine_l2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p,
                                     C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         L.orc_synth_rows_f32.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]
+        L.orc_score_all_i8_limbs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
+        L.orc_query_limbs_f16.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]
+        L.orc_query_limbs_i8.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_float),
+                                         C.POINTER(C.c_float)]
         L.orc_f16_to_f32.restype = C.c_float
         L.orc_f16_to_f32.argtypes = [C.c_uint16]
         L.orc_f32_to_f16_rne.restype = C.c_uint16
@@ -115,6 +120,28 @@ class Oracle:
         sc = np.empty((nq, k), np.float32)
         self.lib.orc_flat_search_batch(_p(base), _p(scales), dtype, n, d, _p(queries), nq, k, _p(ids), _p(sc))
         return ids, sc
+
+    # --- tensor-core scan limb schemes (restatement of csrc/scan_mma.cu)
+    def score_all_i8_limbs(self, base, scales, q):
+        n, d = base.shape
+        q = np.ascontiguousarray(q, np.float32)
+        sc, i1, i2 = np.empty(n, np.float32), np.empty(n, np.int32), np.empty(n, np.int32)
+        self.lib.orc_score_all_i8_limbs(_p(base), _p(scales), n, d, _p(q), _p(sc), _p(i1), _p(i2))
+        return sc, i1, i2
+
+    def query_limbs_f16(self, q):
+        q = np.ascontiguousarray(q, np.float32)
+        hi, lo = np.empty(q.size, np.uint16), np.empty(q.size, np.uint16)
+        s = C.c_float()
+        self.lib.orc_query_limbs_f16(_p(q), q.size, _p(hi), _p(lo), C.byref(s))
+        return hi, lo, np.float32(s.value)
+
+    def query_limbs_i8(self, q):
+        q = np.ascontiguousarray(q, np.float32)
+        q1, q2 = np.empty(q.size, np.int8), np.empty(q.size, np.int8)
+        s1, s2 = C.c_float(), C.c_float()
+        self.lib.orc_query_limbs_i8(_p(q), q.size, _p(q1), _p(q2), C.byref(s1), C.byref(s2))
+        return q1, q2, np.float32(s1.value), np.float32(s2.value)
 
     # --- converters
     def to_f16(self, x):

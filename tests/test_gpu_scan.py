@@ -15,6 +15,7 @@ def make_base(oracle, dtype, n, d, seed=11):
 
 def check(nv, oracle, dtype, base, scales, queries, k, row_offset=0):
     with nv.FlatIndexCuda.from_host(base, scales, dtype, row_offset=row_offset) as idx:
+        idx.set_path(nv.PATH_GEMV)    # the bit-exact streaming scan (AUTO switches to tensor cores for batches)
         ids, sc = idx.search_topk_dot_batch(queries, k)
     oids, osc = oracle.search_batch(dtype, base, scales, queries, k)
     n = base.shape[0]

@@ -34,6 +34,7 @@ def test_logical_shards_merge_equals_unsharded(nv, oracle, dt, S, n_total, k, nq
             continue
         idx = nv.FlatIndexCuda.from_host(base[r0:r0 + nrows], None if scales is None else scales[r0:r0 + nrows], dtype,
                                          row_offset=r0)
+        idx.set_path(nv.PATH_GEMV)
         shards.append(idx)
         idx.search_device(q_dev.data_ptr(), nq, k, ids_view.data_ptr(), sc_view.data_ptr(),
                           torch.cuda.current_stream().cuda_stream)
@@ -52,6 +53,7 @@ def test_logical_shards_merge_equals_unsharded(nv, oracle, dt, S, n_total, k, nq
         assert np.all(ids[qi, kk:] == np.uint64(0xFFFFFFFFFFFFFFFF))
     # the world==1 path of ShardedFlatIndex (same code as N ranks minus the collective)
     with nv.FlatIndexCuda.from_host(base, scales, dtype) as whole:
+        whole.set_path(nv.PATH_GEMV)
         sh = nv.ShardedFlatIndex(whole, dev)
         i2, s2 = sh.search(q_dev, k)
         torch.cuda.synchronize()

@@ -141,3 +141,22 @@ def test_refine_restatements_agree(oracle):
         order = np.lexsort((ids, dist))[:K]
         assert np.array_equal(ids[order], i0[qi])
         assert np.array_equal(dist[order], d0[qi])
+
+
+def test_limb_schemes_approximate_the_reference_scores(oracle):
+    """the tensor-core path's query limb schemes (restated in the oracle) vs the reference-order FP32 scores:
+    i8 two-limb <= 3e-5 relative to max|score|; f16 hi+lo limbs reconstruct the scaled query to ~2^-21."""
+    n, d = 4000, 768
+    base, scales = oracle.synth(I8, 41, 0, n, d)
+    f = oracle.synth_f32(41, 0, n, d)
+    for r in (0, 17, 3999):
+        q = f[r]
+        ref = oracle.score_all(I8, base, scales, q)
+        sc, i1, i2 = oracle.score_all_i8_limbs(base, scales, q)
+        assert np.max(np.abs(sc - ref)) <= 3e-5 * np.max(np.abs(ref))
+        q1, q2, s1, s2 = oracle.query_limbs_i8(q)
+        assert np.array_equal(i1, base.astype(np.int32) @ q1.astype(np.int32))
+        assert np.array_equal(i2, base.astype(np.int32) @ q2.astype(np.int32))
+        hi, lo, qs = oracle.query_limbs_f16(q)
+        rec = (hi.view(np.float16).astype(np.float64) + lo.view(np.float16).astype(np.float64)) * float(qs)
+        assert np.max(np.abs(rec - q)) <= 2.0 ** -21 * np.max(np.abs(q))
