@@ -377,26 +377,59 @@ def _time_search(torch, idx, stream, q_dev, nq, k, iters, warm=3):
     return e0.elapsed_time(e1) / iters, scan_ms / max(calls, 1)
 
 
+def measured_tensor_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["bf16_tflops"]), "measured burst (MEASURED_PEAKS.json bf16_tflops)"
+    return 1590.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s)"
+
+
 def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
     """Other BASELINE.json configs on one GPU, short runs (explanatory numbers, not the headline)."""
     peak, _ = measured_peaks()
-    ex = {}
-    nb16 = payload_bytes(idx16.count, DIM, F16)
-    sweep = {}
-    for b in (1, 2, 4, 8, 16, 64):
-        ms, kms = _time_search(torch, idx16, stream, q_dev, b, TOPK, iters=max(3, 40 // b))
-        sweep[str(b)] = {"ms_per_batch": ms, "qps": b / ms * 1e3, "base_GBps": nb16 * ((b + 7) // 8) / (kms * 1e-3) / 1e9}
-    ex["fp16_batch_sweep_gemv"] = sweep
+    tpeak, tsrc = measured_tensor_peak()
+    ex = {"tensor_peak_TFLOPs": tpeak, "tensor_peak_source": tsrc}
+    n = idx16.count
+    nb16 = payload_bytes(n, DIM, F16)
+    qbig = q_dev.repeat(1024 // NQ_POOL, 1).contiguous()
+    qbig += 1e-3 * torch.randn_like(qbig)
+
+    def sweep(idx, nbytes, plan, limbs_of):
+        out = {}
+        for pname, path, b in plan:
+            idx.set_path(path)
+            ms, kms = _time_search(torch, idx, stream, qbig, b, TOPK, iters=max(5, min(50, 2048 // b)))
+            rec = {"path": pname, "ms_per_batch": ms, "qps": b / ms * 1e3, "scan_kernel_ms": kms}
+            if pname == "gemv":
+                rec["base_GBps"] = nbytes * ((b + 7) // 8) / (kms * 1e-3) / 1e9
+            else:
+                rec["base_GBps"] = nbytes / (kms * 1e-3) / 1e9
+                issued = 2.0 * ((b + 127) // 128 * 128) * n * DIM * limbs_of(pname) / (kms * 1e-3) / 1e12
+                rec["issued_TFLOPs"] = issued
+                rec["useful_TFLOPs"] = 2.0 * b * n * DIM / (kms * 1e-3) / 1e12
+                rec["tensor_frac_of_measured_bf16_peak"] = issued / tpeak
+            out[f"{pname}_b{b}"] = rec
+        idx.set_path(nv.PATH_AUTO)
+        return out
+
+    # FP16 batch sweep (BASELINE.json configs[1]): GEMV scan -> tcgen05 GEMM crossover
+    plan16 = [("gemv", nv.PATH_GEMV, 1), ("gemv", nv.PATH_GEMV, 2), ("gemv", nv.PATH_GEMV, 8),
+              ("mma", nv.PATH_MMA, 2), ("mma", nv.PATH_MMA, 8), ("mma", nv.PATH_MMA, 64), ("mma", nv.PATH_MMA, 128),
+              ("mma", nv.PATH_MMA, 256), ("mma", nv.PATH_MMA, 1024),
+              ("mma_fast", nv.PATH_MMA_FAST, 128), ("mma_fast", nv.PATH_MMA_FAST, 1024)]
+    ex["fp16_batch_sweep"] = sweep(idx16, nb16, plan16, lambda p_: 2 if p_ == "mma" else 1)
+    idx16.set_path(nv.PATH_GEMV)
     ms, kms = _time_search(torch, idx16, stream, q_dev, 1, 100, iters=20)
     ex["fp16_batch1_top100"] = {"ms": ms, "qps": 1e3 / ms}
-    # INT8 (+scale), batch 1 — BASELINE.json configs[2]
-    with nv.FlatIndexCuda.synthetic(I8, idx16.count, DIM, SEED, device=local_rank) as idx8:
-        nb8 = payload_bytes(idx8.count, DIM, I8)
-        ms, kms = _time_search(torch, idx8, stream, q_dev, 1, TOPK, iters=50)
-        ex["int8_batch1"] = {"ms": ms, "qps": 1e3 / ms, "kernel_ms": kms, "GBps": nb8 / (kms * 1e-3) / 1e9,
-                             "roofline_frac": nb8 / (kms * 1e-3) / 1e9 / peak}
-        ms, kms = _time_search(torch, idx8, stream, q_dev, 8, TOPK, iters=10)
-        ex["int8_batch8"] = {"ms_per_batch": ms, "qps": 8e3 / ms}
+    idx16.set_path(nv.PATH_AUTO)
+    # INT8 (+scale) — BASELINE.json configs[2]: batch 1 (bit-exact GEMV) and batch 1024 (kind::i8, 2 exact limbs)
+    with nv.FlatIndexCuda.synthetic(I8, n, DIM, SEED, device=local_rank) as idx8:
+        nb8 = payload_bytes(n, DIM, I8)
+        plan8 = [("gemv", nv.PATH_GEMV, 1), ("mma", nv.PATH_MMA, 8), ("mma", nv.PATH_MMA, 128), ("mma", nv.PATH_MMA, 1024)]
+        ex["int8_batch_sweep"] = sweep(idx8, nb8, plan8, lambda p_: 2)
+        r = ex["int8_batch_sweep"]["gemv_b1"]
+        r["roofline_frac"] = r["base_GBps"] / peak
     # FP32 500K x 768 — BASELINE.json configs[0]
     with nv.FlatIndexCuda.synthetic(F32, 500_000, DIM, SEED, device=local_rank) as idx32:
         nb32 = payload_bytes(500_000, DIM, F32)

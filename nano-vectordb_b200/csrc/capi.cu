@@ -562,9 +562,10 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   return NVDB_B200_OK;
 }
 
-// AUTO: the bit-exact streaming scan for the smallest batches, tensor cores from kMmaCrossover queries on
-// (the GEMV scan re-reads the base once per 8 queries; the tensor-core scan reads it once per 128 * num_sms).
-constexpr uint32_t kMmaCrossover = 4;
+// AUTO: a single query takes the bit-exact streaming scan; from kMmaCrossover queries on the tensor-core scan wins
+// (measured, profiles/r1_batch_sweep_*.jsonl: the GEMV scan re-reads the base once per 8 queries and is FMA-bound
+// from 4 queries per pass; the tensor-core scan reads the base once per 128 * num_sms queries).
+constexpr uint32_t kMmaCrossover = 2;
 
 int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
                        float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* path_used) {

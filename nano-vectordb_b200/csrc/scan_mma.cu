@@ -34,6 +34,7 @@ namespace {
 constexpr int kMmaThreads = 192;
 constexpr int kBlockM = 128;
 constexpr uint32_t kTmemCols = 512;
+constexpr int kMmaRegK = 16;  // k <= 16: per-thread top-k lists in registers, else in shared memory
 constexpr uint32_t kAccColsPerBuf = 256;
 constexpr uint64_t kSentinelKey = ((uint64_t)0x007FFFFFu << 32);  // (ordered(-inf), row 0xFFFFFFFF): below any real key
 
@@ -164,14 +165,60 @@ __device__ __noinline__ float list_insert(uint64_t* list, uint32_t k, uint64_t k
   return key_score(list[(k - 1) * kBlockM]);
 }
 
-template <int DT, int LIMBS, int BLOCK_N>
+// The per-thread top-k container. KREG == 0: list in shared memory (any k that fits). KREG > 0 (k <= KREG): the list
+// lives in registers — an insert is ~KREG compare/select pairs with no memory latency, which matters because a warp
+// runs the insert path whenever ANY of its 32 queries admits a row.
+template <int KREG>
+struct ThreadTopK {
+  // right-aligned: the best entry is e[KREG - k], the k-th best is ALWAYS e[KREG - 1] (a fixed register); the unused
+  // leading entries hold UINT64_MAX so nothing ever shifts into them. All indices below are compile-time constants.
+  uint64_t e[KREG];
+  uint32_t k;
+  __device__ __forceinline__ void init(uint64_t*, uint32_t k_) {
+    k = k_;
+#pragma unroll
+    for (int u = 0; u < KREG; ++u) e[u] = ((uint32_t)u + k >= (uint32_t)KREG) ? kSentinelKey : ~0ull;
+  }
+  __device__ __forceinline__ float insert(uint64_t key, float thr) {
+    if (key <= e[KREG - 1]) return thr;
+#pragma unroll
+    for (int u = KREG - 1; u >= 1; --u) e[u] = (e[u - 1] < key) ? e[u - 1] : ((e[u] < key) ? key : e[u]);
+    if (e[0] < key) e[0] = key;
+    return key_score(e[KREG - 1]);
+  }
+  // out[jj] = jj-th best, sentinel (row 0xFFFFFFFF) -> 0 (empty)
+  __device__ __forceinline__ void store(uint64_t* out) const {
+#pragma unroll
+    for (int u = 0; u < KREG; ++u)
+      if ((uint32_t)u + k >= (uint32_t)KREG) out[(uint32_t)u + k - (uint32_t)KREG] = ((uint32_t)e[u] == 0u) ? 0ull : e[u];
+  }
+};
+template <>
+struct ThreadTopK<0> {
+  uint64_t* list;
+  uint32_t k;
+  __device__ __forceinline__ void init(uint64_t* l, uint32_t k_) {
+    list = l;
+    k = k_;
+    for (uint32_t jj = 0; jj < k; ++jj) list[jj * kBlockM] = kSentinelKey;
+  }
+  __device__ __forceinline__ float insert(uint64_t key, float thr) { return list_insert(list, k, key, thr); }
+  __device__ __forceinline__ void store(uint64_t* out) const {
+    for (uint32_t jj = 0; jj < k; ++jj) {
+      const uint64_t key = list[jj * kBlockM];
+      out[jj] = ((uint32_t)key == 0u) ? 0ull : key;
+    }
+  }
+};
+
+template <int DT, int LIMBS, int BLOCK_N, int KREG>
 __global__ void __launch_bounds__(kMmaThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const MmaArgs a) {
   constexpr int ES = (DT == kDtF16) ? 2 : 1, EPC = 128 / ES;  // elements per 128-byte chunk
   constexpr bool kI8 = (DT == kDtI8);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, a.k);
+  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, KREG > 0 ? 0u : a.k);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars_off);
   uint64_t* empty = full + a.stages;
   uint64_t* tfull = empty + a.stages;   // [2] accumulator buffer ready for the epilogue
@@ -269,9 +316,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const uint32_t et = (warp - 2) * 32 + lane;    // 0..127 among the epilogue threads
     const uint32_t qg = m_tile * kBlockM + ql;     // < mpad
     const bool valid = qg < a.nq;
-    uint64_t* list = reinterpret_cast<uint64_t*>(smem + L.lists_off) + ql;  // entry jj at list[jj * 128]
+    ThreadTopK<KREG> top;
+    top.init(reinterpret_cast<uint64_t*>(smem + L.lists_off) + ql, a.k);  // smem variant: entry jj at list[jj * 128]
     float* rscale = reinterpret_cast<float*>(smem + L.rscale_off);          // [2][BLOCK_N] row scales (i8)
-    for (uint32_t jj = 0; jj < a.k; ++jj) list[jj * kBlockM] = kSentinelKey;
     float thr = valid ? -INFINITY : INFINITY;      // score of the current k-th best; padding lanes never insert
     const float qs1 = a.qscale[qg];
     const float qs2 = kI8 ? a.qscale2[qg] : 0.f;
@@ -328,17 +375,17 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               if (row0 + c0 + i < a.n_rows) d[(size_t)qg * a.n_rows + row0 + c0 + i] = __uint_as_float(v[i]);
           }
         }
-        bool any = false;
+        uint32_t mask = 0;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) any |= (s[i] >= thr);
-        if (any) {
+        for (int i = 0; i < 32; ++i) mask |= (s[i] >= thr) ? (1u << i) : 0u;
+        while (mask) {  // rare after the first tiles: P(admit) ~ k / rows seen
+          const int i = __ffs(mask) - 1;
+          mask &= mask - 1;
+          float sv = s[0];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            if (s[i] >= thr) {
-              const uint32_t row = row0 + c0 + i;
-              if (row < a.n_rows) thr = list_insert(list, a.k, make_key(s[i], row), thr);
-            }
-          }
+          for (int u = 1; u < 32; ++u) sv = (i == u) ? s[u] : sv;
+          const uint32_t row = row0 + c0 + (uint32_t)i;
+          if (sv >= thr && row < a.n_rows) thr = top.insert(make_key(sv, row), thr);
         }
       }
       tc::fence_before_thread_sync();
@@ -346,11 +393,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       if (lane == 0) mbar_arrive(&tempty[buf]);
     }
     if (valid) {
-      uint64_t* out = a.partial + ((size_t)qg * a.P + j) * a.k;
-      for (uint32_t jj = 0; jj < a.k; ++jj) {
-        const uint64_t key = list[jj * kBlockM];
-        out[jj] = ((uint32_t)key == 0u) ? 0ull : key;  // sentinel (row 0xFFFFFFFF) -> empty
-      }
+      top.store(a.partial + ((size_t)qg * a.P + j) * a.k);
     }
   }
 
@@ -359,15 +402,21 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   if (warp == 2) tc::tmem_dealloc(tmem_base, kTmemCols);
 }
 
-template <int DT, int LIMBS, int BLOCK_N>
-cudaError_t launch_mma(const CUtensorMap* ta, const CUtensorMap* tb, const MmaArgs& a, cudaStream_t stream) {
-  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, a.k);
-  auto kern = scan_mma_kernel<DT, LIMBS, BLOCK_N>;
+template <int DT, int LIMBS, int BLOCK_N, int KREG>
+cudaError_t launch_mma_k(const CUtensorMap* ta, const CUtensorMap* tb, const MmaArgs& a, cudaStream_t stream) {
+  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, KREG > 0 ? 0u : a.k);
+  auto kern = scan_mma_kernel<DT, LIMBS, BLOCK_N, KREG>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
   if (e != cudaSuccess) return e;
   kern<<<a.G * a.P, kMmaThreads, L.total, stream>>>(*ta, *tb, a);
   count_launch();
   return cudaGetLastError();
+}
+
+template <int DT, int LIMBS, int BLOCK_N>
+cudaError_t launch_mma(const CUtensorMap* ta, const CUtensorMap* tb, const MmaArgs& a, cudaStream_t stream) {
+  if (a.k <= (uint32_t)kMmaRegK) return launch_mma_k<DT, LIMBS, BLOCK_N, kMmaRegK>(ta, tb, a, stream);
+  return launch_mma_k<DT, LIMBS, BLOCK_N, 0>(ta, tb, a, stream);
 }
 
 }  // namespace
@@ -378,7 +427,7 @@ bool scan_mma_plan(int dtype, int limbs, uint32_t k, int max_smem, uint32_t* blo
   for (int c = 0; c < 2; ++c) {
     const int min_stages = (c == 0 && cand[0] != cand[1]) ? 3 : 2;
     for (int st = 6; st >= min_stages; --st)
-      if (mma_layout(cand[c], limbs, st, k).total <= (uint32_t)max_smem) {
+      if (mma_layout(cand[c], limbs, st, k <= (uint32_t)kMmaRegK ? 0u : k).total <= (uint32_t)max_smem) {
         *block_n = cand[c];
         *stages = st;
         return true;

@@ -46,6 +46,9 @@ class ShardedFlatIndex:
         self._local_search = local_search or self._cuda_local_search
         self._merge = merge or self._cuda_merge
         self._bufs = {}
+        # The C ABI reads a NULL stream as "the index's own stream", so the CUDA steps never run on torch's legacy
+        # default stream (handle 0): they run on this side stream, ordered after / before the caller's stream.
+        self._stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
 
     # ---- default (CUDA) implementations: raw pointers into the C ABI, asynchronous on the current stream
     def _cuda_local_search(self, queries, nq, k, ids_out, scores_out):
@@ -72,6 +75,16 @@ class ShardedFlatIndex:
     def search(self, queries: torch.Tensor, k: int):
         """queries: [nq, dim] f32 on `device`. Returns (ids int64 [nq,k] — u64 bit patterns, UINT64_MAX padding —,
         scores f32 [nq,k]) on every rank; buffers are reused by the next call with the same (nq, k)."""
+        if self._stream is None:
+            return self._search(queries, k)
+        cur = torch.cuda.current_stream(self.device)
+        self._stream.wait_stream(cur)
+        with torch.cuda.stream(self._stream):
+            out = self._search(queries, k)
+        cur.wait_stream(self._stream)
+        return out
+
+    def _search(self, queries, k):
         nq = int(queries.shape[0])
         local, gathered, out_ids, out_sc = self._buffers(nq, k)
         ids_view = local[:nq * k].view(nq, k)

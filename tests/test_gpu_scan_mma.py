@@ -119,9 +119,9 @@ def test_auto_path_crossover_and_timing_path(nv, oracle):
     rng = np.random.default_rng(1)
     with nv.FlatIndexCuda.from_host(base, None, F16) as idx:
         t = nv.Timing()
-        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 2, rng), 10, t)
+        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 1, rng), 10, t)
         assert t.path == nv.PATH_GEMV
-        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 16, rng), 10, t)
+        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 2, rng), 10, t)
         assert t.path == nv.PATH_MMA
     f32 = oracle.synth_f32(2, 0, n, d)
     with nv.FlatIndexCuda.from_host(f32, None, F32) as idx:   # FP32 base: no tensor path (tf32 excluded), GEMV always
