@@ -1,0 +1,233 @@
+// nvdb_bench (mode=cuda) — the reference's benchmark harness for the B200 path.
+//
+// Same positional arguments and the same stdout keys as the reference harness (apps/nvdb_bench.cpp:254-432):
+//   nvdb_bench <base.vecbin> <query.vecbin> <k> [mode=cuda] [gpus=1] [warmup=5] [batch_q=1] [path=auto]
+// `threads` of the reference becomes `gpus` (row shards, one per device); `tile_vecs` / `prefetch_dist` have no
+// meaning on the GPU and are replaced by `path` = auto | gemv | mma | mma_fast. Per-query (or per-batch) latencies are
+// std::chrono::steady_clock around the host-buffer search call, i.e. end to end incl. H2D of the queries and D2H of
+// the results; percentiles use the reference's linear interpolation (:370-377); bytes_per_query /
+// payload_equiv_bandwidth_GBps as in :414-418. Extra keys: gt_match (when GT_PATH names a gtbin written by the
+// reference's nvdb_gt_build), kernel_ms_avg, path_used.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdlib>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "dataset.h"
+#include "flat_index_cuda.h"
+
+namespace {
+
+double ms_since(std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+  return std::chrono::duration<double, std::milli>(b - a).count();
+}
+
+// Row shards on `gpus` devices of this process; per-shard searches run concurrently, results are merged on the host
+// under (score desc, id asc). One shard == plain FlatIndexCuda.
+class ShardedIndex {
+ public:
+  ShardedIndex(const nvdb::VectorDataset& base, int gpus, int path) {
+    const uint64_t n = base.count(), per = (n + gpus - 1) / gpus;
+    const size_t row_bytes = (size_t)base.dim() * nvdb::bytes_per_elem(base.dtype());
+    for (int g = 0; g < gpus; ++g) {
+      const uint64_t r0 = std::min<uint64_t>(n, (uint64_t)g * per), nr = std::min<uint64_t>(n, r0 + per) - r0;
+      if (nr == 0) continue;
+      nvdb_b200_index* h = nullptr;
+      const char* payload = static_cast<const char*>(base.data_ptr()) + r0 * row_bytes;
+      const float* scales = base.scales_ptr() ? base.scales_ptr() + r0 : nullptr;
+      nvdb::detail::check(nvdb_b200_index_create(payload, scales, base.dtype(), nr, base.dim(), g, r0, &h), nullptr);
+      nvdb::detail::check(nvdb_b200_index_set_path(h, path), h);
+      shards_.push_back(h);
+    }
+    n_ = n;
+  }
+  ~ShardedIndex() {
+    for (auto* h : shards_) nvdb_b200_index_destroy(h);
+  }
+  // ids/scores: nq*k, padded like nvdb_b200_search
+  void search(const float* q, uint32_t nq, uint32_t k, std::vector<uint64_t>& ids, std::vector<float>& sc,
+              nvdb_b200_timing* t0) {
+    const size_t S = shards_.size(), nk = (size_t)nq * k;
+    ids.resize(nk);
+    sc.resize(nk);
+    if (S == 1) {
+      nvdb::detail::check(nvdb_b200_search(shards_[0], q, nq, k, ids.data(), sc.data(), t0), shards_[0]);
+      return;
+    }
+    tmp_ids_.resize(S * nk);
+    tmp_sc_.resize(S * nk);
+    std::vector<std::thread> th;
+    std::vector<int> rc(S, 0);
+    std::vector<nvdb_b200_timing> tt(S);
+    for (size_t s = 0; s < S; ++s)
+      th.emplace_back([&, s] { rc[s] = nvdb_b200_search(shards_[s], q, nq, k, &tmp_ids_[s * nk], &tmp_sc_[s * nk], &tt[s]); });
+    for (auto& x : th) x.join();
+    for (size_t s = 0; s < S; ++s) nvdb::detail::check(rc[s], shards_[s]);
+    if (t0) *t0 = tt[0];
+    std::vector<std::pair<float, uint64_t>> c;
+    for (uint32_t qi = 0; qi < nq; ++qi) {
+      c.clear();
+      for (size_t s = 0; s < S; ++s)
+        for (uint32_t j = 0; j < k; ++j) {
+          const uint64_t id = tmp_ids_[s * nk + (size_t)qi * k + j];
+          if (id != UINT64_MAX) c.emplace_back(tmp_sc_[s * nk + (size_t)qi * k + j], id);
+        }
+      std::sort(c.begin(), c.end(), [](const auto& a, const auto& b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
+      for (uint32_t j = 0; j < k; ++j) {
+        ids[(size_t)qi * k + j] = j < c.size() ? c[j].second : UINT64_MAX;
+        sc[(size_t)qi * k + j] = j < c.size() ? c[j].first : -INFINITY;
+      }
+    }
+  }
+  size_t shards() const { return shards_.size(); }
+
+ private:
+  std::vector<nvdb_b200_index*> shards_;
+  std::vector<uint64_t> tmp_ids_;
+  std::vector<float> tmp_sc_;
+  uint64_t n_ = 0;
+};
+
+// gtbin (include/nvdb/gtbin_format.h:18-35): 64-byte header {u64 magic "NVDBGT01", u32 version, u32 metric, u32 k,
+// u32 dim, u64 Q, u64 N, pad} + u32 ids[Q*k]
+bool load_gtbin(const std::string& path, uint32_t* k, uint64_t* Q, std::vector<uint32_t>* ids) {
+  std::ifstream f(path, std::ios::binary);
+  if (!f) return false;
+  unsigned char h[64];
+  f.read(reinterpret_cast<char*>(h), 64);
+  if (!f) return false;
+  uint64_t magic;
+  std::memcpy(&magic, h, 8);
+  if (magic != 0x4E56444247543031ULL) return false;
+  std::memcpy(k, h + 16, 4);
+  std::memcpy(Q, h + 24, 8);
+  ids->resize((size_t)*Q * *k);
+  f.read(reinterpret_cast<char*>(ids->data()), (std::streamsize)ids->size() * 4);
+  return (bool)f;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  if (argc < 4) {
+    std::cerr << "Usage: nvdb_bench <base.vecbin> <query.vecbin> <k> [mode=cuda] [gpus=1] [warmup=5] [batch_q=1] "
+                 "[path=auto|gemv|mma|mma_fast]\n";
+    return 1;
+  }
+  try {
+    const std::string base_path = argv[1], query_path = argv[2];
+    const uint32_t k = (uint32_t)std::stoul(argv[3]);
+    const std::string mode = argc >= 5 ? argv[4] : "cuda";
+    int gpus = argc >= 6 ? std::stoi(argv[5]) : 1;
+    const int warmup = argc >= 7 ? std::stoi(argv[6]) : 5;
+    const int batch_q = std::max(1, argc >= 8 ? std::stoi(argv[7]) : 1);
+    const std::string path_s = argc >= 9 ? argv[8] : "auto";
+    if (mode != "cuda") {
+      std::cerr << "mode=" << mode << " is one of the reference's CPU scans; this harness drives mode=cuda only\n";
+      return 1;
+    }
+    int path = NVDB_B200_PATH_AUTO;
+    if (path_s == "gemv") path = NVDB_B200_PATH_GEMV;
+    else if (path_s == "mma") path = NVDB_B200_PATH_MMA;
+    else if (path_s == "mma_fast") path = NVDB_B200_PATH_MMA_FAST;
+    else if (path_s != "auto") throw std::runtime_error("Unknown path: " + path_s);
+    nvdb::VectorDataset base, query;
+    base.load(base_path);
+    query.load(query_path);
+    if (base.dim() != query.dim()) {
+      std::cerr << "Dim mismatch: base.dim=" << base.dim() << ", query.dim=" << query.dim() << "\n";
+      return 2;
+    }
+    if (query.dtype() != 1) throw std::runtime_error("Dataset is not float32");  // queries must be f32 (raw12 / vecbin f32)
+    int ndev = 0;
+    nvdb::detail::check(nvdb_b200_device_count(&ndev), nullptr);
+    if (gpus <= 0) gpus = ndev;
+    if (gpus > ndev) throw std::runtime_error("gpus=" + std::to_string(gpus) + " but only " + std::to_string(ndev) + " CUDA devices");
+    std::cout << "mode=" << mode << " gpus=" << gpus << "\n";
+    const auto tu0 = std::chrono::steady_clock::now();
+    ShardedIndex index(base, gpus, path);
+    const double upload_ms = ms_since(tu0, std::chrono::steady_clock::now());
+    std::cout << "Base count=" << base.count() << " dim=" << base.dim() << " | Query count=" << query.count()
+              << " | k=" << k << " | warmup=" << warmup << "\n";
+
+    std::vector<uint64_t> ids;
+    std::vector<float> sc;
+    for (int i = 0; i < warmup; ++i) index.search(query.vector_ptr(0), 1, k, ids, sc, nullptr);
+
+    const uint64_t Q = query.count();
+    std::vector<double> lat_ms;
+    std::vector<uint64_t> all_ids((size_t)Q * k);
+    volatile float sink = 0.0f;
+    double kernel_ms_sum = 0;
+    uint32_t path_used = 0;
+    const auto t_all0 = std::chrono::steady_clock::now();
+    for (uint64_t qb = 0; qb < Q; qb += (uint64_t)batch_q) {
+      const uint32_t b = (uint32_t)std::min<uint64_t>((uint64_t)batch_q, Q - qb);
+      nvdb_b200_timing t{};
+      const auto t0 = std::chrono::steady_clock::now();
+      index.search(query.vector_ptr_f32(qb), b, k, ids, sc, &t);  // query rows are contiguous in the file
+      lat_ms.push_back(ms_since(t0, std::chrono::steady_clock::now()));
+      kernel_ms_sum += t.kernel_ms;
+      path_used = t.path;
+      for (uint32_t qi = 0; qi < b; ++qi) {
+        sink = sink + sc[(size_t)qi * k];
+        std::copy(ids.begin() + (size_t)qi * k, ids.begin() + (size_t)(qi + 1) * k, all_ids.begin() + (size_t)(qb + qi) * k);
+      }
+    }
+    const double total_ms = ms_since(t_all0, std::chrono::steady_clock::now());
+
+    std::sort(lat_ms.begin(), lat_ms.end());
+    auto pct = [&](double p) {
+      if (lat_ms.empty()) return 0.0;
+      const double pos = (p / 100.0) * (double)(lat_ms.size() - 1);
+      const size_t i0 = (size_t)std::floor(pos), i1 = std::min(i0 + 1, lat_ms.size() - 1);
+      const double frac = pos - (double)i0;
+      return lat_ms[i0] * (1.0 - frac) + lat_ms[i1] * frac;
+    };
+    if (batch_q > 1) std::cout << "batch_samples=" << lat_ms.size() << "\n";
+    const double avg_query = total_ms / (double)Q, qps = (double)Q * 1000.0 / total_ms;
+    std::cout << std::fixed << std::setprecision(3);
+    std::cout << "Total:     " << total_ms << " ms\n";
+    std::cout << "Avg_query: " << avg_query << " ms/query  (" << qps << " QPS)\n";
+    if (batch_q > 1) {
+      const double nb = (double)lat_ms.size();
+      std::cout << "Avg_batch: " << total_ms / nb << " ms/batch  (" << nb * 1000.0 / total_ms << " batches/s)\n";
+      std::cout << "batch_p50: " << pct(50) << " ms\n" << "batch_p95: " << pct(95) << " ms\n" << "batch_p99: " << pct(99) << " ms\n";
+    } else {
+      std::cout << "p50:       " << pct(50) << " ms\n" << "p95:       " << pct(95) << " ms\n" << "p99:       " << pct(99) << " ms\n";
+    }
+    std::cout << "sink=" << sink << "\n";
+    const double bytes_per_query = (double)nvdb::bytes_for_payload_and_aux(base.count(), base.dim(), base.dtype());
+    std::cout << std::setprecision(0) << "bytes_per_query=" << bytes_per_query << "\n" << std::setprecision(3);
+    std::cout << "payload_equiv_bandwidth_GBps=" << (avg_query > 0 ? bytes_per_query * 1e-6 / avg_query : 0.0) << "\n";
+    if (batch_q > 1) std::cout << "(note) payload_equiv_bandwidth_GBps may exceed DRAM peak due to cache reuse\n";
+    std::cout << "batch_q=" << batch_q << " path=" << path_s << " path_used=" << path_used << " shards=" << index.shards() << "\n";
+    std::cout << "kernel_ms_avg=" << kernel_ms_sum / (double)lat_ms.size() << " upload_ms=" << upload_ms << "\n";
+
+    if (const char* gt = std::getenv("GT_PATH")) {
+      uint32_t gk = 0;
+      uint64_t gq = 0;
+      std::vector<uint32_t> gids;
+      if (!load_gtbin(gt, &gk, &gq, &gids) || gq != Q || gk < std::min<uint64_t>(k, base.count())) {
+        std::cerr << "GT_PATH: unreadable gtbin or shape mismatch\n";
+        return 3;
+      }
+      const uint32_t kk = (uint32_t)std::min<uint64_t>(k, base.count());
+      uint64_t same = 0;
+      for (uint64_t qi = 0; qi < Q; ++qi)
+        for (uint32_t j = 0; j < kk; ++j) same += (all_ids[(size_t)qi * k + j] == (uint64_t)gids[(size_t)qi * gk + j]);
+      std::cout << std::setprecision(6) << "gt_match=" << (double)same / (double)(Q * kk) << " gt_positions=" << Q * kk << "\n";
+    }
+    return 0;
+  } catch (const std::exception& e) {
+    std::cerr << "error: " << e.what() << "\n";
+    return 4;
+  }
+}
