@@ -30,6 +30,7 @@ struct nvdb_b200_index {
   int path = NVDB_B200_PATH_AUTO;
   int num_sms = 148;
   int max_smem = 227 * 1024;
+  int max_smem_sm = 228 * 1024;  // per SM (all resident CTAs together)
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   bool tma_ok = false;
@@ -181,6 +182,7 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
   if (e == cudaSuccess) {
     h->num_sms = prop.multiProcessorCount;
     h->max_smem = (int)prop.sharedMemPerBlockOptin;
+    h->max_smem_sm = (int)prop.sharedMemPerMultiprocessor;
   }
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
@@ -396,6 +398,16 @@ struct ScanPlan {
 };
 
 // Queries per pass: as many as fit next to >= 3 ring stages (each 32 KB) in shared memory, at most 8.
+int gemv_ctas(const nvdb_b200_index* idx) {
+  static const int env = [] {
+    const char* e = getenv("NVDB_B200_GEMV_CTAS");
+    return e ? atoi(e) : 0;
+  }();
+  if (env == 1 || env == 2) return env;
+  (void)idx;
+  return 1;  // measured (profiles/r1_gemv_ffma2_ctas.jsonl): one CTA with the deep ring beats two for every dtype
+}
+
 int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) {
   const uint64_t need = (uint64_t)k + kScanRowsPerTile;
   if (need > 8192) return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "k too large for the fused selector (k <= 7936)");
@@ -419,6 +431,16 @@ int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) 
     if (fixed + 3u * 32768u > (uint32_t)idx->max_smem) continue;
     int st = (int)(((uint32_t)idx->max_smem - fixed) / (32768u + 16u));
     if (st > 6) st = 6;
+    // single-query passes may run two CTAs per SM (more consumer warps to cover the int8 conversion chain); each CTA
+    // then gets half of the shared memory. Tuning knob: NVDB_B200_GEMV_CTAS=1|2 (default 1, see gemv_ctas()).
+    if (t == 1 && gemv_ctas(idx) == 2) {
+      const uint32_t half = ((uint32_t)idx->max_smem_sm / 2u) - 1024u;  // 1 KB per-CTA reservation
+      int st2 = half > fixed ? (int)((half - fixed) / (32768u + 16u)) : 0;
+      if (st2 >= 3 && tiles >= 2u * (uint32_t)idx->num_sms) {
+        st = st2 > 6 ? 6 : st2;
+        p->grid = 2 * idx->num_sms;
+      }
+    }
     while (st > 3 && scan_gemv_smem_bytes(true, st, t, idx->dim, p->cap) > (uint32_t)idx->max_smem) --st;
     p->nq_template = t;
     p->stages = st;

@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "scan.h"
 #include "topk_select.cuh"
+#include "dot_chains.cuh"
 
 namespace nvdb_b200 {
 
@@ -31,86 +32,6 @@ constexpr int kRows = kScanRowsPerTile;        // 256 rows per tile == consumer 
 constexpr int kConsumers = kRows;
 constexpr int kThreads = kConsumers + 32;      // + producer warp
 constexpr int kStageBytes = kRows * 128;       // 32 KB
-
-template <int DT>
-struct Elem;
-template <>
-struct Elem<kDtF32> { static constexpr int size = 4, per16 = 4; };
-template <>
-struct Elem<kDtF16> { static constexpr int size = 2, per16 = 8; };
-template <>
-struct Elem<kDtI8> { static constexpr int size = 1, per16 = 16; };
-
-// ---- 16 bytes of one row -> FMAs into the 8 chains of every query -------------------------------------------
-// `c` is the 16-byte piece index inside the 128-byte chunk (compile-time after unrolling).
-
-template <int NQ>
-__device__ __forceinline__ void fma8(float (&acc)[NQ][8], const float (&x)[8], const float* __restrict__ q,
-                                     uint32_t qstride) {
-#pragma unroll
-  for (int qi = 0; qi < NQ; ++qi) {
-    const float4 qa = *reinterpret_cast<const float4*>(q + qi * qstride);
-    const float4 qb = *reinterpret_cast<const float4*>(q + qi * qstride + 4);
-    acc[qi][0] = __fmaf_rn(qa.x, x[0], acc[qi][0]);
-    acc[qi][1] = __fmaf_rn(qa.y, x[1], acc[qi][1]);
-    acc[qi][2] = __fmaf_rn(qa.z, x[2], acc[qi][2]);
-    acc[qi][3] = __fmaf_rn(qa.w, x[3], acc[qi][3]);
-    acc[qi][4] = __fmaf_rn(qb.x, x[4], acc[qi][4]);
-    acc[qi][5] = __fmaf_rn(qb.y, x[5], acc[qi][5]);
-    acc[qi][6] = __fmaf_rn(qb.z, x[6], acc[qi][6]);
-    acc[qi][7] = __fmaf_rn(qb.w, x[7], acc[qi][7]);
-  }
-}
-
-template <int DT, int NQ>
-__device__ __forceinline__ void consume16(float (&acc)[NQ][8], const uint4 v, const float* __restrict__ q,
-                                          uint32_t qstride, int c) {
-  if constexpr (DT == kDtF16) {
-    float x[8];
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));  // exact widening
-      x[2 * i] = f.x;
-      x[2 * i + 1] = f.y;
-    }
-    fma8<NQ>(acc, x, q, qstride);
-  } else if constexpr (DT == kDtF32) {
-    // 4 elements: chains 0..3 for even pieces, 4..7 for odd pieces
-    const float x[4] = {__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w)};
-    const int j0 = (c & 1) * 4;
-#pragma unroll
-    for (int qi = 0; qi < NQ; ++qi) {
-      const float4 qa = *reinterpret_cast<const float4*>(q + qi * qstride);
-      acc[qi][j0 + 0] = __fmaf_rn(qa.x, x[0], acc[qi][j0 + 0]);
-      acc[qi][j0 + 1] = __fmaf_rn(qa.y, x[1], acc[qi][j0 + 1]);
-      acc[qi][j0 + 2] = __fmaf_rn(qa.z, x[2], acc[qi][j0 + 2]);
-      acc[qi][j0 + 3] = __fmaf_rn(qa.w, x[3], acc[qi][j0 + 3]);
-    }
-  } else {
-    // 16 int8: elements 0..7 then 8..15 into the same 8 chains (src/simd_dot.cpp:175-187).
-    // int8 -> f32 exactly: byte ^ 0x80 placed in the mantissa of 2^23 gives 2^23 + (x+128); subtracting
-    // (2^23 + 128) is exact. One LOP3 per 4 bytes + one PRMT and one FADD per element, no I2F.
-    const uint32_t w[4] = {v.x ^ 0x80808080u, v.y ^ 0x80808080u, v.z ^ 0x80808080u, v.w ^ 0x80808080u};
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      float x[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint32_t word = w[h * 2 + (i >> 2)];
-        const uint32_t bits = __byte_perm(word, 0x4B000000u, 0x7650 + (i & 3));  // {0x4B,0x00,0x00,byte}
-        x[i] = __fsub_rn(__uint_as_float(bits), 8388736.0f);                     // 2^23 + 128
-      }
-      fma8<NQ>(acc, x, q + h * 8, qstride);
-    }
-  }
-}
-
-__device__ __forceinline__ float hsum8_ref_order(const float (&a)[8]) {
-  const float s0 = __fadd_rn(a[0], a[4]), s1 = __fadd_rn(a[1], a[5]);
-  const float s2 = __fadd_rn(a[2], a[6]), s3 = __fadd_rn(a[3], a[7]);
-  return __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
-}
 
 struct SmemLayout {
   uint32_t stages_off, queries_off, keys_off, cnt_off, thr_off, bars_off, total;
@@ -137,8 +58,10 @@ __host__ __device__ inline SmemLayout make_layout(int stages, int nq, uint32_t d
   return L;
 }
 
+// Single-query passes are compiled for two resident CTAs per SM (<= 113 registers); capi.cu decides per dtype
+// whether the launch actually uses one CTA with a deep ring or two with half the ring each.
 template <int DT, int NQ>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, NQ == 1 ? 2 : 1)
 scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -195,6 +118,7 @@ scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a)
   const uint32_t swz = (row_in_tile & 7u) << 4;
   const uint32_t stages_u32 = smem_u32(smem + L.stages_off) + row_in_tile * 128u;
   const uint32_t row_bytes = a.dim * ES;
+  const uint32_t sq_u32 = smem_u32(sq), qstride_b = a.dim * 4u;
   uint32_t stage = 0, phase = 0;
   auto csync = [] { named_bar_sync(1, kConsumers); };
 
@@ -203,30 +127,30 @@ scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a)
     float scale = 1.f;
     if constexpr (DT == kDtI8) scale = (row < a.n_rows) ? __ldg(a.scales + row) : 0.f;
 
-    float acc[NQ][8];
+    uint64_t acc[NQ][4];  // packed chain pairs, +0.0f in both halves
 #pragma unroll
     for (int qi = 0; qi < NQ; ++qi)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[qi][j] = 0.f;
+      for (int p = 0; p < 4; ++p) acc[qi][p] = 0ull;
 
     for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
       const uint32_t rem = row_bytes - kc * 128u;
       const int npieces = rem >= 128u ? 8 : (int)(rem >> 4);
-      const float* qk = sq + kc * EPC;
+      const uint32_t qk = sq_u32 + kc * (EPC * 4u);
       mbar_wait(&full[stage], phase);
       const uint32_t base = stages_u32 + stage * kStageBytes;
       if (npieces == 8) {
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
           const uint4 v = lds128(base + (((uint32_t)c << 4) ^ swz));
-          consume16<DT, NQ>(acc, v, qk + c * P16, a.dim, c);
+          consume16<DT, NQ>(acc, v, qk + c * (P16 * 4u), qstride_b, c);
         }
       } else {
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
           if (c < npieces) {
             const uint4 v = lds128(base + (((uint32_t)c << 4) ^ swz));
-            consume16<DT, NQ>(acc, v, qk + c * P16, a.dim, c);
+            consume16<DT, NQ>(acc, v, qk + c * (P16 * 4u), qstride_b, c);
           }
         }
       }

@@ -16,6 +16,8 @@ N = int(os.environ.get("NVDB_BENCH_ROWS", 2_903_054))
 D, K, SEED = 768, int(os.environ.get("NVDB_K", 10)), 20240229
 dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
+PATHS = os.environ.get("NVDB_PATHS", "gemv,mma,mma_fast").split(",")
+DTYPES = os.environ.get("NVDB_DTYPES", "f16,i8").split(",")
 BATCHES = [int(b) for b in os.environ.get("NVDB_BATCHES", "1,2,4,8,16,32,64,128,256,512,1024").split(",")]
 
 
@@ -35,6 +37,8 @@ def time_search(idx, qs, nq, iters):
 
 
 for dtype, name, esz in ((nv.F16, "f16", 2), (nv.I8, "i8", 1)):
+    if name not in DTYPES:
+        continue
     idx = nv.FlatIndexCuda.synthetic(dtype, N, D, SEED, device=0)
     nbytes = N * D * esz + (4 * N if dtype == nv.I8 else 0)
     qall = torch.empty((1024, D), dtype=torch.float32, device=dev)
@@ -44,7 +48,7 @@ for dtype, name, esz in ((nv.F16, "f16", 2), (nv.I8, "i8", 1)):
     stream.synchronize()
     qall += 1e-3 * torch.randn_like(qall)
     for pname, path in (("gemv", nv.PATH_GEMV), ("mma", nv.PATH_MMA), ("mma_fast", nv.PATH_MMA_FAST)):
-        if dtype == nv.I8 and pname == "mma_fast":
+        if (dtype == nv.I8 and pname == "mma_fast") or pname not in PATHS:
             continue
         idx.set_path(path)
         for b in BATCHES:

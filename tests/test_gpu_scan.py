@@ -63,10 +63,16 @@ def test_scan_ties_duplicated_rows(nv, oracle, dt):
     f = oracle.synth_f32(9, 0, 2000, 128)
     queries = f[[5, 77]]
     with nv.FlatIndexCuda.from_host(base, scales, dtype) as idx:
+        idx.set_path(nv.PATH_GEMV)
         ids, sc = idx.search_topk_dot_batch(queries, 6)
+        idx.set_path(nv.PATH_AUTO)   # a batch on AUTO takes the tensor-core scan for f16 / i8: tolerance-mode scores
+        aids, asc = idx.search_topk_dot_batch(queries, 6)
     oids, osc = oracle.search_batch(dtype, base, scales, queries, 6)
     assert np.array_equal(ids, oids)  # canonical order is exactly reproducible, not only modulo ties
     assert np.array_equal(sc.view(np.uint32), osc.view(np.uint32))
+    # identical rows get identical tensor-core scores too, so the (score desc, id asc) order is still exact
+    assert np.array_equal(aids, oids)
+    np.testing.assert_allclose(asc, osc, rtol=1e-4)
 
 
 def test_scan_k_larger_than_n_and_row_offset(nv, oracle):
