@@ -401,6 +401,9 @@ def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
             idx.set_path(path)
             ms, kms = _time_search(torch, idx, stream, qbig, b, TOPK, iters=max(5, min(50, 2048 // b)))
             rec = {"path": pname, "ms_per_batch": ms, "qps": b / ms * 1e3, "scan_kernel_ms": kms}
+            if pname == "mma_exact":
+                nqx, nfb = idx.exact_stats(reset=True)
+                rec["certificate_fallback_rate"] = nfb / max(nqx, 1)
             if pname == "gemv":
                 rec["base_GBps"] = nbytes * ((b + 7) // 8) / (kms * 1e-3) / 1e9
             else:
@@ -417,7 +420,9 @@ def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
     plan16 = [("gemv", nv.PATH_GEMV, 1), ("gemv", nv.PATH_GEMV, 2), ("gemv", nv.PATH_GEMV, 8),
               ("mma", nv.PATH_MMA, 2), ("mma", nv.PATH_MMA, 8), ("mma", nv.PATH_MMA, 64), ("mma", nv.PATH_MMA, 128),
               ("mma", nv.PATH_MMA, 256), ("mma", nv.PATH_MMA, 1024),
-              ("mma_fast", nv.PATH_MMA_FAST, 128), ("mma_fast", nv.PATH_MMA_FAST, 1024)]
+              ("mma_fast", nv.PATH_MMA_FAST, 128), ("mma_fast", nv.PATH_MMA_FAST, 1024),
+              ("mma_exact", nv.PATH_MMA_EXACT, 8), ("mma_exact", nv.PATH_MMA_EXACT, 128),
+              ("mma_exact", nv.PATH_MMA_EXACT, 1024)]
     ex["fp16_batch_sweep"] = sweep(idx16, nb16, plan16, lambda p_: 2 if p_ == "mma" else 1)
     idx16.set_path(nv.PATH_GEMV)
     ms, kms = _time_search(torch, idx16, stream, q_dev, 1, 100, iters=20)
@@ -426,7 +431,8 @@ def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
     # INT8 (+scale) — BASELINE.json configs[2]: batch 1 (bit-exact GEMV) and batch 1024 (kind::i8, 2 exact limbs)
     with nv.FlatIndexCuda.synthetic(I8, n, DIM, SEED, device=local_rank) as idx8:
         nb8 = payload_bytes(n, DIM, I8)
-        plan8 = [("gemv", nv.PATH_GEMV, 1), ("mma", nv.PATH_MMA, 8), ("mma", nv.PATH_MMA, 128), ("mma", nv.PATH_MMA, 1024)]
+        plan8 = [("gemv", nv.PATH_GEMV, 1), ("mma", nv.PATH_MMA, 8), ("mma", nv.PATH_MMA, 128), ("mma", nv.PATH_MMA, 1024),
+                 ("mma_exact", nv.PATH_MMA_EXACT, 128), ("mma_exact", nv.PATH_MMA_EXACT, 1024)]
         ex["int8_batch_sweep"] = sweep(idx8, nb8, plan8, lambda p_: 2)
         r = ex["int8_batch_sweep"]["gemv_b1"]
         r["roofline_frac"] = r["base_GBps"] / peak

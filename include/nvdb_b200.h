@@ -47,7 +47,12 @@ enum {
   NVDB_B200_PATH_GEMV = 1, /* bit-exact FP32-FMA streaming scan (all dtypes) */
   NVDB_B200_PATH_MMA = 2,  /* tcgen05 tensor-core scan (f16: query = fp16 hi + lo limbs; i8: two int8 query limbs,
                               exact int32 limb dot products), tolerance-mode parity vs the FP32-FMA reference */
-  NVDB_B200_PATH_MMA_FAST = 3 /* f16 only: single fp16 query limb (half the tensor work, ~5e-5 relative error) */
+  NVDB_B200_PATH_MMA_FAST = 3, /* f16 only: single fp16 query limb (half the tensor work, ~5e-5 relative error) */
+  NVDB_B200_PATH_MMA_EXACT = 4 /* tensor-core candidate scan (f16: one limb, i8: two limbs) keeping k' > k rows per
+                                  query, exact FP32 re-score of the candidates in the reference's summation order, and a
+                                  per-query error-bound certificate; queries that fail it are re-run on PATH_GEMV. Ids and
+                                  scores are bit-identical to PATH_GEMV. AUTO uses this for batches of >= 3 queries.
+                                  Synchronises the stream once per call. */
 };
 
 typedef struct nvdb_b200_index nvdb_b200_index;
@@ -112,6 +117,19 @@ int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float
  * list l starts at packed + l*W 8-byte words, W = nq*k + (nq*k+1)/2, and holds [nq*k u64 ids][nq*k f32 scores]. */
 int nvdb_b200_merge_topk_packed_device(int device, const void* packed_dev, uint32_t nlists, uint32_t nq, uint32_t k,
                                        uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+
+/* Kernel-selection knobs for A/B measurements and tests; results never depend on them. Defaults can also be set with
+ * the environment variables NVDB_B200_MMA_SEED / NVDB_B200_GEMV_CTAS / NVDB_B200_MMA_2CTA at index creation. */
+enum {
+  NVDB_B200_TUNE_MMA_SEED = 1,  /* threshold-seeding pass of the tensor-core scan: 0 off, 1 auto (default), 2 always */
+  NVDB_B200_TUNE_GEMV_CTAS = 2, /* CTAs per SM of the single-query streaming scan: 1 (default) | 2 */
+  NVDB_B200_TUNE_MMA_2CTA = 3   /* CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 auto (default) */
+};
+int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value);
+
+/* Certificate statistics of NVDB_B200_PATH_MMA_EXACT since creation / the last reset: queries answered through it and
+ * how many of them failed the certificate and were re-run on the streaming scan. */
+int nvdb_b200_index_exact_stats(nvdb_b200_index* idx, uint64_t* queries, uint64_t* fallbacks, int reset);
 
 /* Test hook for the tensor-core scan: runs the NVDB_B200_PATH_MMA / _MMA_FAST scan of `nq` host queries (k = 1) and
  * returns the RAW accumulators of every (query, row) pair: f16 base -> out_acc[nq][n] float bit patterns (before

@@ -13,7 +13,8 @@ from pathlib import Path
 import numpy as np
 
 F32, F16, I8 = 1, 2, 3
-PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST = 0, 1, 2, 3
+PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST, PATH_MMA_EXACT = 0, 1, 2, 3, 4
+TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA = 1, 2, 3
 _NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
 
 lib_path = Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"
@@ -52,6 +53,8 @@ _sig = {
     "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_search_device": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_debug_mma_accumulators": (_i, [_vp, _vp, _u32, _i, _vp]),
+    "nvdb_b200_index_set_tuning": (_i, [_vp, _i, _i]),
+    "nvdb_b200_index_exact_stats": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), _i]),
     "nvdb_b200_merge_topk_device": (_i, [_i, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_merge_topk_packed_device": (_i, [_i, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
@@ -150,6 +153,15 @@ class FlatIndexCuda:
 
     def set_path(self, path):
         _check(lib.nvdb_b200_index_set_path(self._h, path), self._h)
+
+    def set_tuning(self, knob, value):
+        _check(lib.nvdb_b200_index_set_tuning(self._h, knob, value), self._h)
+
+    def exact_stats(self, reset=False):
+        """(queries answered by PATH_MMA_EXACT, how many failed the certificate and were re-run on the streaming scan)"""
+        q, f = C.c_uint64(0), C.c_uint64(0)
+        _check(lib.nvdb_b200_index_exact_stats(self._h, C.byref(q), C.byref(f), int(reset)), self._h)
+        return q.value, f.value
 
     def read_rows(self, row0, nrows):
         payload = np.empty((nrows, self.dim), _NP[self.dtype])

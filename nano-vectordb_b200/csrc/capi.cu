@@ -2,6 +2,7 @@
 // No CPU compute path lives here: every result is produced by the kernels in this directory.
 #include <atomic>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -42,10 +43,18 @@ struct nvdb_b200_index {
   const void* tmap_a_ptr = nullptr;
   uint32_t tmap_a_rows = 0;
   // grow-only workspaces
-  void* d_ws[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  size_t d_ws_bytes[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-  void* h_pin[2] = {nullptr, nullptr};
-  size_t h_pin_bytes[2] = {0, 0};
+  void* d_ws[16] = {};
+  size_t d_ws_bytes[16] = {};
+  void* h_pin[3] = {nullptr, nullptr, nullptr};
+  size_t h_pin_bytes[3] = {0, 0, 0};
+  // exact tensor-core path (rescore.cu): row-norm maxima of the base (lazy) and certificate statistics
+  bool norms_ready = false;
+  float max_l2 = 0.f, max_l1 = 0.f;
+  uint64_t exact_queries = 0, exact_fallbacks = 0;
+  // tuning knobs (nvdb_b200_index_set_tuning; defaults may be overridden by environment variables at creation)
+  int tune_mma_seed = 1;   // 0 off, 1 auto (>= 256 queries and >= 32 tiles per CTA), 2 whenever there are >= 2 tiles per CTA
+  int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
+  int tune_mma_2cta = 1;   // 0 never, 1 auto: CTA-pair (cta_group::2) tensor-core scan where it applies
   std::mutex mu;
   mutable std::string err;
   // optional per-kernel event timing (bench.py's roofline figure)
@@ -58,7 +67,8 @@ namespace {
 
 thread_local std::string t_err;
 enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5, WS_MMA_A = 6,
-       WS_MMA_QS = 7, WS_DBG = 8 };
+       WS_MMA_QS = 7, WS_DBG = 8, WS_X_IDS = 9, WS_X_APX = 10, WS_X_FLAGS = 11, WS_X_Q = 12, WS_X_OUT_IDS = 13,
+       WS_X_OUT_SC = 14, WS_SEED = 15 };
 
 int fail(const nvdb_b200_index* idx, int code, const std::string& msg) {
   t_err = msg;
@@ -184,6 +194,9 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
     h->max_smem = (int)prop.sharedMemPerBlockOptin;
     h->max_smem_sm = (int)prop.sharedMemPerMultiprocessor;
   }
+  if (const char* ev = getenv("NVDB_B200_MMA_SEED")) h->tune_mma_seed = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_GEMV_CTAS")) h->tune_gemv_ctas = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_MMA_2CTA")) h->tune_mma_2cta = atoi(ev);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
   if (e != cudaSuccess) {
@@ -364,7 +377,7 @@ int nvdb_b200_index_info(const nvdb_b200_index* idx, uint64_t* n, uint32_t* dim,
 
 int nvdb_b200_index_set_path(nvdb_b200_index* idx, int path) {
   if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
-  if (path < NVDB_B200_PATH_AUTO || path > NVDB_B200_PATH_MMA_FAST) return fail(idx, NVDB_B200_ERR_ARG, "bad path");
+  if (path < NVDB_B200_PATH_AUTO || path > NVDB_B200_PATH_MMA_EXACT) return fail(idx, NVDB_B200_ERR_ARG, "bad path");
   idx->path = path;
   return NVDB_B200_OK;
 }
@@ -399,13 +412,8 @@ struct ScanPlan {
 
 // Queries per pass: as many as fit next to >= 3 ring stages (each 32 KB) in shared memory, at most 8.
 int gemv_ctas(const nvdb_b200_index* idx) {
-  static const int env = [] {
-    const char* e = getenv("NVDB_B200_GEMV_CTAS");
-    return e ? atoi(e) : 0;
-  }();
-  if (env == 1 || env == 2) return env;
-  (void)idx;
-  return 1;  // measured (profiles/r1_gemv_ffma2_ctas.jsonl): one CTA with the deep ring beats two for every dtype
+  // measured (profiles/r1_gemv_ffma2_ctas.jsonl): one CTA with the deep ring beats two for every dtype
+  return idx->tune_gemv_ctas == 2 ? 2 : 1;
 }
 
 int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) {
@@ -432,7 +440,7 @@ int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) 
     int st = (int)(((uint32_t)idx->max_smem - fixed) / (32768u + 16u));
     if (st > 6) st = 6;
     // single-query passes may run two CTAs per SM (more consumer warps to cover the int8 conversion chain); each CTA
-    // then gets half of the shared memory. Tuning knob: NVDB_B200_GEMV_CTAS=1|2 (default 1, see gemv_ctas()).
+    // then gets half of the shared memory. Tuning knob NVDB_B200_TUNE_GEMV_CTAS (default 1).
     if (t == 1 && gemv_ctas(idx) == 2) {
       const uint32_t half = ((uint32_t)idx->max_smem_sm / 2u) - 1024u;  // 1 KB per-CTA reservation
       int st2 = half > fixed ? (int)((half - fixed) / (32768u + 16u)) : 0;
@@ -468,7 +476,8 @@ int prof_begin(nvdb_b200_index* idx, cudaStream_t stream, cudaEvent_t** pev) {
 // ---- tensor-core path: prep (limb split) -> scan_mma_kernel -> merge of the per-CTA lists -------------------
 // `dbg` (tests only): raw accumulators [NACC][mpad][n]; mpad_out receives the padded query count.
 int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
-                    float* d_out_scores, cudaStream_t stream, uint32_t* launches, int limbs, void* dbg) {
+                    float* d_out_scores, cudaStream_t stream, uint32_t* launches, int limbs, void* dbg,
+                    uint64_t row_offset) {
   if (!idx->mma_ok)
     return fail(idx, NVDB_B200_ERR_UNSUPPORTED,
                 "tensor-core scan needs an f16 / i8 base with a 16-byte row pitch and whole 8/16-element chains");
@@ -482,27 +491,44 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
   cudaEvent_t* pev = nullptr;
   int rc = prof_begin(idx, stream, &pev);
   if (rc) return rc;
-  // every pass handles up to 128 * num_sms queries; G M-tiles x P CTAs each
+  // every pass handles up to 128 * num_sms queries; G M-tiles x P CTAs (or CTA pairs) each.
+  // CTA-pair kernel (scan_mma2.cu): f16 bases, an even number of M-tiles, 256-row tiles, P = clusters per pair column.
+  int stages2 = 0;
+  const bool pair_ok = idx->dtype == kDtF16 && idx->tune_mma_2cta && !dbg && scan_mma2_plan(limbs, k, idx->max_smem, &stages2);
+  struct PassPlan {
+    bool pair;
+    uint32_t G, P, bn, tiles;
+  };
+  auto plan_pass = [&](uint32_t nqp) {
+    PassPlan pp;
+    pp.G = (nqp + 127u) / 128u;
+    pp.pair = pair_ok && pp.G >= 2u && (pp.G % 2u) == 0u;
+    pp.bn = pp.pair ? 256u : block_n;
+    pp.tiles = (uint32_t)((idx->n + pp.bn - 1) / pp.bn);
+    pp.P = pp.pair ? ((uint32_t)idx->num_sms / 2u) / (pp.G / 2u) : (uint32_t)idx->num_sms / pp.G;
+    if (pp.P > pp.tiles) pp.P = pp.tiles;
+    return pp;
+  };
   uint32_t maxP = 1;
   for (uint32_t q0 = 0; q0 < nq; q0 += max_q) {
-    const uint32_t g = ((nq - q0 < max_q ? nq - q0 : max_q) + 127u) / 128u;
-    const uint32_t p_ = (uint32_t)idx->num_sms / g;
-    if (p_ > maxP) maxP = p_;
+    const PassPlan pp = plan_pass(nq - q0 < max_q ? nq - q0 : max_q);
+    if (pp.P > maxP) maxP = pp.P;
   }
-  if ((rc = ensure_ws(idx, WS_PARTIAL, (size_t)nq * maxP * k * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_PARTIAL, (size_t)nq * (maxP + 1) * k * 8))) return rc;
   for (uint32_t q0 = 0; q0 < nq; q0 += max_q) {
     const uint32_t nqp = nq - q0 < max_q ? nq - q0 : max_q;
+    const PassPlan pp = plan_pass(nqp);
+    const uint32_t tiles_all = pp.tiles;
     MmaArgs a{};
-    a.G = (nqp + 127u) / 128u;
-    a.P = (uint32_t)idx->num_sms / a.G;
+    a.G = pp.G;
+    a.P = pp.P;
     a.mpad = a.G * 128u;
-    a.num_tiles = (uint32_t)((idx->n + block_n - 1) / block_n);
-    if (a.P > a.num_tiles) a.P = a.num_tiles;
     if ((rc = ensure_ws(idx, WS_MMA_A, (size_t)limbs * a.mpad * idx->dim * es))) return rc;
-    if ((rc = ensure_ws(idx, WS_MMA_QS, (size_t)2 * a.mpad * 4))) return rc;
+    if ((rc = ensure_ws(idx, WS_MMA_QS, (size_t)3 * a.mpad * 4))) return rc;
     void* A = idx->d_ws[WS_MMA_A];
     float* qs1 = (float*)idx->d_ws[WS_MMA_QS];
     float* qs2 = qs1 + a.mpad;
+    float* thr_seed = qs2 + a.mpad;
     if (idx->tmap_a_ptr != A || idx->tmap_a_rows != (uint32_t)limbs * a.mpad) {
       if ((rc = encode_2d(idx, &idx->tmap_mma_a, idx->dtype, A, (uint64_t)limbs * a.mpad, idx->dim, 128u))) return rc;
       idx->tmap_a_ptr = A;
@@ -514,22 +540,54 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
     a.scales = idx->scales;
     a.qscale = qs1;
     a.qscale2 = qs2;
-    a.partial = (uint64_t*)idx->d_ws[WS_PARTIAL];
     a.dbg = dbg;
     a.n_rows = (uint32_t)idx->n;
     a.dim = idx->dim;
     a.k = k;
     a.nq = nqp;
     a.kchunks = (uint32_t)(((size_t)idx->dim * es + 127) / 128);
-    a.stages = stages;
-    a.block_n = block_n;
+    a.stages = pp.pair ? stages2 : stages;
+    a.block_n = pp.bn;
     a.evict_first_base = (a.G == 1);
-    CK(scan_mma_launch((int)idx->dtype, limbs, &idx->tmap_mma_a, block_n == 256 ? &idx->tmap : &idx->tmap_mma_b, a, stream),
-       "scan_mma launch");
+    const CUtensorMap* tmb = (pp.bn == 256 && !pp.pair) ? &idx->tmap : &idx->tmap_mma_b;
+    auto launch_scan = [&](const MmaArgs& args) {
+      return pp.pair ? scan_mma2_launch(limbs, &idx->tmap_mma_a, tmb, args, stream)
+                     : scan_mma_launch((int)idx->dtype, limbs, &idx->tmap_mma_a, tmb, args, stream);
+    };
+    uint64_t* partial = (uint64_t*)idx->d_ws[WS_PARTIAL];
+    // Threshold seeding: a first pass over ~1/16 of the base (the same number of tiles for every CTA) gives each query
+    // its k-th best score among those rows — a valid lower bound of its final k-th best. The main pass over the
+    // remaining rows starts from that threshold, so its epilogue threads admit ~k*15/P rows instead of
+    // ~k*ln(rows per CTA / k) (the per-thread list insert is the expensive, warp-divergent part of the epilogue).
+    // Auto mode seeds only multi-tile batches (G >= 2): a single M-tile is HBM-bound and the two extra launches cost more
+    // than the inserts they save (profiles/r1_ab_*.jsonl).
+    // The seed pass's own top-k joins the final merge as list number P.
+    uint32_t seed_tiles = 0;
+    if (!dbg && idx->tune_mma_seed && (idx->tune_mma_seed == 2 ? tiles_all >= 2u * a.P : (a.G >= 2u && tiles_all >= 32u * a.P))) {
+      seed_tiles = ((tiles_all / 16u + a.P - 1u) / a.P) * a.P;
+      if ((rc = ensure_ws(idx, WS_SEED, (size_t)nqp * a.P * k * 8))) return rc;
+      MmaArgs s0 = a;
+      s0.partial = (uint64_t*)idx->d_ws[WS_SEED];
+      s0.lists = a.P;
+      s0.tile0 = 0;
+      s0.num_tiles = seed_tiles;
+      s0.thr_init = nullptr;
+      CK(launch_scan(s0), "scan_mma seed launch");
+      CK(merge_partials_seed_launch(s0.partial, a.P, nqp, k, partial + (size_t)a.P * k, (size_t)(a.P + 1) * k, thr_seed,
+                                    stream),
+         "merge_partials seed launch");
+      if (launches) *launches += 2;
+    }
+    a.partial = partial;
+    a.lists = a.P + (seed_tiles ? 1u : 0u);
+    a.tile0 = seed_tiles;
+    a.num_tiles = tiles_all;
+    a.thr_init = seed_tiles ? thr_seed : nullptr;
+    CK(launch_scan(a), "scan_mma launch");
     if (launches) *launches += 2;
     // merge this pass right away (the partial buffer is reused by the next pass)
     if (pev && q0 + max_q >= nq) CK(cudaEventRecord(pev[1], stream), "profile event record");
-    CK(merge_partials_launch(a.partial, a.P, nqp, k, idx->row_offset, d_out_ids + (size_t)q0 * k,
+    CK(merge_partials_launch(a.partial, a.lists, nqp, k, row_offset, d_out_ids + (size_t)q0 * k,
                              d_out_scores + (size_t)q0 * k, stream),
        "merge_partials launch");
     if (launches) ++*launches;
@@ -584,26 +642,133 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   return NVDB_B200_OK;
 }
 
-// AUTO: a single query takes the bit-exact streaming scan; from kMmaCrossover queries on the tensor-core scan wins
-// (measured, profiles/r1_batch_sweep_*.jsonl: the GEMV scan re-reads the base once per 8 queries and is FMA-bound
-// from 4 queries per pass; the tensor-core scan reads the base once per 128 * num_sms queries).
-constexpr uint32_t kMmaCrossover = 2;
+// ---- exact tensor-core path: candidate scan (k' > k) -> exact re-score + certificate -> streaming-scan fallback ----
+// f16: ONE fp16 query limb (half the tensor work of PATH_MMA); i8: two int8 limbs. Results are bit-identical to
+// PATH_GEMV (and therefore to the reference) for every query: certified ones by construction (rescore.cu), the rest
+// because they are re-run on the streaming scan. Synchronises `stream` once (the flag count comes back to the host).
+uint32_t exact_kprime(uint32_t k) {
+  if (k <= 12u) return 16u;  // per-thread register lists of the scan hold 16 entries
+  const uint32_t extra = k / 4u > 8u ? k / 4u : 8u;  // k = 100 -> 125: ~25 ranks of slack against the error margin
+  return k + extra;
+}
+
+int ensure_norms(nvdb_b200_index* idx, cudaStream_t stream) {
+  if (idx->norms_ready) return NVDB_B200_OK;
+  int rc;
+  if ((rc = ensure_ws(idx, WS_X_FLAGS, 4096))) return rc;
+  if ((rc = ensure_pin(idx, 2, 4096))) return rc;
+  uint32_t* d2 = (uint32_t*)idx->d_ws[WS_X_FLAGS];
+  CK(row_norm_max_launch((int)idx->dtype, idx->payload, idx->scales, idx->n, idx->dim, d2, idx->num_sms, stream),
+     "row_norm_max launch");
+  CK(cudaMemcpyAsync(idx->h_pin[2], d2, 8, cudaMemcpyDeviceToHost, stream), "D2H norms");
+  CK(cudaStreamSynchronize(stream), "norms sync");
+  std::memcpy(&idx->max_l2, idx->h_pin[2], 4);
+  std::memcpy(&idx->max_l1, (char*)idx->h_pin[2] + 4, 4);
+  idx->norms_ready = true;
+  return NVDB_B200_OK;
+}
+
+bool mma_exact_supported(const nvdb_b200_index* idx, uint32_t k) {
+  uint32_t bn;
+  int st;
+  return idx->mma_ok && scan_mma_plan((int)idx->dtype, idx->dtype == kDtF16 ? 1 : 2, exact_kprime(k), idx->max_smem, &bn, &st);
+}
+
+int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                          float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
+  if (!mma_exact_supported(idx, k))
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "exact tensor-core scan: unsupported base layout or k too large");
+  const uint32_t kp = exact_kprime(k);
+  int rc;
+  if ((rc = ensure_norms(idx, stream))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_IDS, (size_t)nq * kp * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_APX, (size_t)nq * kp * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_FLAGS, ((size_t)nq + 4) * 4))) return rc;
+  if ((rc = ensure_pin(idx, 2, ((size_t)nq + 4) * 4))) return rc;
+  uint64_t* cand_ids = (uint64_t*)idx->d_ws[WS_X_IDS];
+  float* cand_apx = (float*)idx->d_ws[WS_X_APX];
+  uint32_t* nflag = (uint32_t*)idx->d_ws[WS_X_FLAGS];
+  uint32_t* flags = nflag + 4;
+  CK(cudaMemsetAsync(nflag, 0, 4, stream), "memset flag count");
+  const int limbs = idx->dtype == kDtF16 ? 1 : 2;
+  if ((rc = mma_search_impl(idx, d_queries, nq, kp, cand_ids, cand_apx, stream, launches, limbs, nullptr, 0))) return rc;
+
+  RescoreArgs r{};
+  r.base = idx->payload;
+  r.scales = idx->scales;
+  r.queries = d_queries;
+  r.cand_ids = cand_ids;
+  r.cand_approx = cand_apx;
+  r.out_ids = d_out_ids;
+  r.out_scores = d_out_scores;
+  r.flags = flags;
+  r.nflag = nflag;
+  r.row_offset = idx->row_offset;
+  r.n_rows = (uint32_t)idx->n;
+  r.dim = idx->dim;
+  r.kp = kp;
+  r.k = k;
+  r.max_l2 = idx->max_l2;
+  r.max_l1 = idx->max_l1;
+  const double D = (double)idx->dim, u24 = 1.0 / 16777216.0;
+  r.rel_err = idx->dtype == kDtF16
+                  ? (float)(D * 2.0 * u24 + (D / 8.0 + 4.0) * u24)  // + |delta|_2 of the limb split, added per query
+                  : (float)((D / 8.0 + 16.0) * u24);
+  CK(rescore_exact_launch((int)idx->dtype, r, nq, stream), "rescore launch");
+  if (launches) ++*launches;
+  uint32_t* h = (uint32_t*)idx->h_pin[2];
+  CK(cudaMemcpyAsync(h, nflag, 4, cudaMemcpyDeviceToHost, stream), "D2H flag count");
+  CK(cudaStreamSynchronize(stream), "exact scan sync");
+  const uint32_t nf = h[0];
+  idx->exact_queries += nq;
+  idx->exact_fallbacks += nf;
+  if (nf == 0) return NVDB_B200_OK;
+
+  // ---- fallback: flagged queries go through the streaming scan ------------------------------------------------
+  if (nf == nq) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
+  CK(cudaMemcpyAsync(h + 4, flags, (size_t)nq * 4, cudaMemcpyDeviceToHost, stream), "D2H flags");
+  CK(cudaStreamSynchronize(stream), "exact scan sync");
+  std::vector<uint32_t> list;
+  list.reserve(nf);
+  for (uint32_t q = 0; q < nq; ++q)
+    if (h[4 + q]) list.push_back(q);
+  const size_t qb = (size_t)idx->dim * 4;
+  if ((rc = ensure_ws(idx, WS_X_Q, list.size() * qb))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_OUT_IDS, list.size() * k * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_OUT_SC, list.size() * k * 4))) return rc;
+  char* gq = (char*)idx->d_ws[WS_X_Q];
+  for (size_t j = 0; j < list.size(); ++j)
+    CK(cudaMemcpyAsync(gq + j * qb, (const char*)d_queries + (size_t)list[j] * qb, qb, cudaMemcpyDeviceToDevice, stream),
+       "gather flagged queries");
+  uint64_t* fo_ids = (uint64_t*)idx->d_ws[WS_X_OUT_IDS];
+  float* fo_sc = (float*)idx->d_ws[WS_X_OUT_SC];
+  if ((rc = gemv_search_impl(idx, (const float*)gq, (uint32_t)list.size(), k, fo_ids, fo_sc, stream, launches))) return rc;
+  for (size_t j = 0; j < list.size(); ++j) {
+    CK(cudaMemcpyAsync(d_out_ids + (size_t)list[j] * k, fo_ids + j * k, (size_t)k * 8, cudaMemcpyDeviceToDevice, stream),
+       "scatter fallback ids");
+    CK(cudaMemcpyAsync(d_out_scores + (size_t)list[j] * k, fo_sc + j * k, (size_t)k * 4, cudaMemcpyDeviceToDevice, stream),
+       "scatter fallback scores");
+  }
+  return NVDB_B200_OK;
+}
+
+// AUTO: one or two queries take the bit-exact streaming scan; from kMmaCrossover queries on the exact tensor-core path
+// wins (measured, profiles/r1_batch_sweep_*.jsonl: the streaming scan serves 2 queries per pass at the HBM roofline
+// and is FMA-bound from 4; the tensor-core scan reads the base once per 128 * num_sms queries). Both are bit-identical
+// to the reference, so AUTO never changes results.
+constexpr uint32_t kMmaCrossover = 3;
 
 int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
                        float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* path_used) {
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
-  {
-    uint32_t bn;
-    int st;
-    path = (idx->mma_ok && nq >= kMmaCrossover && scan_mma_plan((int)idx->dtype, 2, k, idx->max_smem, &bn, &st))
-               ? NVDB_B200_PATH_MMA
-               : NVDB_B200_PATH_GEMV;
-  }
+    path = (nq >= kMmaCrossover && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
   if (path_used) *path_used = (uint32_t)path;
   if (path == NVDB_B200_PATH_GEMV) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
+  if (path == NVDB_B200_PATH_MMA_EXACT)
+    return mma_exact_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
   return mma_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches,
-                         path == NVDB_B200_PATH_MMA_FAST ? 1 : 2, nullptr);
+                         path == NVDB_B200_PATH_MMA_FAST ? 1 : 2, nullptr, idx->row_offset);
 }
 
 }  // namespace
@@ -666,6 +831,27 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   return NVDB_B200_OK;
 }
 
+int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  switch (knob) {
+    case NVDB_B200_TUNE_MMA_SEED: idx->tune_mma_seed = value; break;
+    case NVDB_B200_TUNE_GEMV_CTAS: idx->tune_gemv_ctas = value; break;
+    case NVDB_B200_TUNE_MMA_2CTA: idx->tune_mma_2cta = value; break;
+    default: return fail(idx, NVDB_B200_ERR_ARG, "unknown tuning knob");
+  }
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_exact_stats(nvdb_b200_index* idx, uint64_t* queries, uint64_t* fallbacks, int reset) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  if (queries) *queries = idx->exact_queries;
+  if (fallbacks) *fallbacks = idx->exact_fallbacks;
+  if (reset) idx->exact_queries = idx->exact_fallbacks = 0;
+  return NVDB_B200_OK;
+}
+
 int nvdb_b200_debug_mma_accumulators(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, int path,
                                      uint32_t* out_acc) {
   if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
@@ -686,7 +872,7 @@ int nvdb_b200_debug_mma_accumulators(nvdb_b200_index* idx, const float* queries_
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], queries_host, qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
   rc = mma_search_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, 1, (uint64_t*)idx->d_ws[WS_OUT_IDS],
                        (float*)idx->d_ws[WS_OUT_SCORES], s, nullptr, path == NVDB_B200_PATH_MMA_FAST ? 1 : 2,
-                       idx->d_ws[WS_DBG]);
+                       idx->d_ws[WS_DBG], idx->row_offset);
   if (rc) return rc;
   CK(cudaStreamSynchronize(s), "debug_mma sync");
   for (uint32_t a = 0; a < nacc; ++a)

@@ -1,0 +1,263 @@
+// rescore.cu — exact FP32 re-score + certificate for the candidates of the tensor-core scan.
+//
+// The tensor-core scan (scan_mma.cu) ranks rows by an APPROXIMATE score (fp16 / int8 query limbs). This file turns
+// its output into the reference's exact answer (FlatIndex::search_topk_dot, src/flat_index.cpp:16-48):
+//
+//   1. the scan keeps k' > k candidates per query (ranked by approximate score);
+//   2. rescore_exact_kernel recomputes each candidate's score with the reference arithmetic (dot_chains.cuh: the AVX2
+//      kernels' FP32 FMA chain order, bit for bit), sorts by (exact score desc, id asc) and emits the best k;
+//   3. certificate: every row that is NOT a candidate has approximate score <= a' (the smallest candidate's), hence
+//      exact score <= a' + margin, where margin bounds |approx - exact| for this query. If a' + margin < (k-th exact
+//      score) no outsider can enter — or tie into — the top k, so the answer is exactly the reference's. Otherwise the
+//      query is flagged and the caller re-runs it on the bit-exact streaming scan (capi.cu).
+//
+// Error bounds (rows b, query q, D = dim; all norms over one row / the query):
+//   f16, one fp16 limb: hi = RN16(q * 2^e); delta = q - hi * 2^-e is EXACT in FP32 and recomputed here per query, so
+//     |approx - real| <= |delta|_2 |b|_2 (Cauchy-Schwarz; ~3x tighter than the worst case 2^-11 |q|_2 |b|_2);
+//     tensor-core FP32 accumulation <= D 2^-23 |q|_2 |b|_2 (one ulp of the running sum per addition, any order);
+//     reference chain rounding <= (D/8 + 4) 2^-24 |q|_2 |b|_2.
+//   i8, two int8 limbs: |q_i - s1 q1_i - s2 q2_i| <= s2/2, so |approx - real| <= (s2/2) * scale_b * |b|_1; FP32
+//     evaluation of fmaf(s2, I2, s1 I1) * scale and the reference chain together <= (D/8 + 8) 2^-24 |q|_2 scale_b |b|_2.
+//   max over rows of |b|_2 and |b|_1 (times the row scale for int8) is computed once per index (row_norm_max_kernel).
+#include <math.h>
+
+#include "common.cuh"
+#include "dot_chains.cuh"
+#include "scan.h"
+
+namespace nvdb_b200 {
+namespace {
+
+constexpr int kRescoreThreads = 128;
+
+__device__ __forceinline__ float block_reduce_max(float v, float* red) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, off));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float m = red[0];
+  for (uint32_t w = 1; w < (blockDim.x >> 5); ++w) m = fmaxf(m, red[w]);
+  __syncthreads();
+  return m;
+}
+__device__ __forceinline__ float block_reduce_sum(float v, float* red) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float s = 0.f;
+  for (uint32_t w = 0; w < (blockDim.x >> 5); ++w) s += red[w];
+  __syncthreads();
+  return s;
+}
+
+// exact score of one row, reference arithmetic. Rows are whole 16-byte pieces (the tensor-core scan's eligibility rule).
+template <int DT>
+__device__ __forceinline__ float exact_dot_row(const uint8_t* __restrict__ rowp, uint32_t row_bytes, uint32_t sq_u32) {
+  constexpr int P16 = Elem<DT>::per16;
+  uint64_t acc[1][4] = {{0ull, 0ull, 0ull, 0ull}};
+  const uint32_t pieces = row_bytes >> 4;
+  uint32_t p = 0;
+  for (; p + 4 <= pieces; p += 4) {  // four 16-byte loads in flight
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ldg128_stream(rowp + (size_t)(p + u) * 16u);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) consume16<DT, 1>(acc, v[u], sq_u32 + (p + u) * (P16 * 4u), 0u, (int)((p + u) & 1u));
+  }
+  for (; p < pieces; ++p) {
+    const uint4 v = ldg128_stream(rowp + (size_t)p * 16u);
+    consume16<DT, 1>(acc, v, sq_u32 + p * (P16 * 4u), 0u, (int)(p & 1u));
+  }
+  return hsum8_ref_order(acc[0]);
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kRescoreThreads)
+rescore_exact_kernel(const RescoreArgs a) {
+  extern __shared__ __align__(16) uint8_t rs_smem[];
+  float* sq = reinterpret_cast<float*>(rs_smem);                                   // [dim]
+  uint64_t* keys = reinterpret_cast<uint64_t*>(rs_smem + ((a.dim * 4u + 15u) & ~15u));  // [bufn]
+  __shared__ float red[kRescoreThreads / 32];
+  __shared__ float s_amin;
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  const float* qsrc = a.queries + (size_t)q * a.dim;
+  float sumsq = 0.f, amax = 0.f;
+  for (uint32_t i = tid; i < a.dim; i += kRescoreThreads) {
+    const float v = qsrc[i];
+    sq[i] = v;
+    sumsq = fmaf(v, v, sumsq);
+    amax = fmaxf(amax, fabsf(v));
+  }
+  sumsq = block_reduce_sum(sumsq, red);  // also orders the sq[] writes before the reads below
+  amax = block_reduce_max(amax, red);
+  float dsq = 0.f;  // f16: |delta|_2^2 of the one-limb query split (same arithmetic as prep_queries_f16_kernel)
+  if constexpr (DT == kDtF16) {
+    int e = 0;
+    if (amax > 0.f && amax < INFINITY) {
+      e = -(ilogbf(amax) + 1);
+      e = e > 100 ? 100 : (e < -100 ? -100 : e);
+    }
+    for (uint32_t i = tid; i < a.dim; i += kRescoreThreads) {
+      const float v = scalbnf(sq[i], e);
+      const float dl = scalbnf(__fsub_rn(v, __half2float(__float2half_rn(v))), -e);  // exact
+      dsq = fmaf(dl, dl, dsq);
+    }
+    dsq = block_reduce_sum(dsq, red);
+  }
+
+  const uint32_t bufn = next_pow2(a.kp);
+  const uint32_t sq_u32 = smem_u32(sq);
+  const uint32_t row_bytes = a.dim * (uint32_t)Elem<DT>::size;
+  const uint64_t* cid = a.cand_ids + (size_t)q * a.kp;
+  const float* capx = a.cand_approx + (size_t)q * a.kp;
+  float amin = INFINITY;  // smallest approximate score among the valid candidates
+  for (uint32_t c = tid; c < bufn; c += kRescoreThreads) {
+    uint64_t key = 0ull;
+    if (c < a.kp) {
+      const uint64_t row64 = cid[c];
+      if (row64 != ~0ull && row64 < (uint64_t)a.n_rows) {
+        const uint32_t row = (uint32_t)row64;
+        float s = exact_dot_row<DT>(reinterpret_cast<const uint8_t*>(a.base) + (size_t)row * row_bytes, row_bytes, sq_u32);
+        if constexpr (DT == kDtI8) s = __fmul_rn(s, __ldg(a.scales + row));  // src/simd_dot.cpp:198
+        key = make_key(s, row);
+        amin = fminf(amin, capx[c]);
+      }
+    }
+    keys[c] = key;
+  }
+  __syncthreads();
+  auto sync = [] { __syncthreads(); };
+  bitonic_sort_desc(keys, bufn, tid, kRescoreThreads, sync);
+  amin = -block_reduce_max(-amin, red);
+  // count valid candidates (keys != 0 after the sort are contiguous at the front)
+  uint32_t cnt = 0;
+  for (uint32_t c = tid; c < bufn; c += kRescoreThreads) cnt += keys[c] != 0ull ? 1u : 0u;
+  const float cntf = block_reduce_sum((float)cnt, red);  // kp <= 8192: exact in float
+  if (tid == 0) s_amin = amin;
+  __syncthreads();
+
+  for (uint32_t j = tid; j < a.k; j += kRescoreThreads) {
+    const uint64_t key = (j < bufn) ? keys[j] : 0ull;
+    const bool ok = key != 0ull;
+    a.out_ids[(size_t)q * a.k + j] = ok ? a.row_offset + (uint64_t)key_row(key) : ~0ull;
+    a.out_scores[(size_t)q * a.k + j] = ok ? key_score(key) : -INFINITY;
+  }
+
+  if (tid == 0) {
+    bool pass;
+    const uint32_t valid = (uint32_t)cntf;
+    if (valid < a.kp) {
+      pass = true;  // the scan returned every row it saw: nothing was excluded
+    } else {
+      const float qn = sqrtf(sumsq) * 1.000001f;
+      float margin;
+      if constexpr (DT == kDtI8) {
+        const float s1 = (amax > 0.f && amax < INFINITY) ? __fdiv_rn(amax, 127.f) : 1.f;  // scan_mma.cu prep
+        const float s2 = __fdiv_rn(s1, 254.f);
+        margin = 0.5f * s2 * a.max_l1 * 1.001f + a.rel_err * qn * a.max_l2;
+      } else {
+        margin = (sqrtf(dsq) * 1.00001f + a.rel_err * qn) * a.max_l2;
+      }
+      margin = margin * 1.0001f + 1e-37f;
+      const uint32_t kk = a.k < valid ? a.k : valid;
+      const float ek = key_score(keys[kk - 1]);
+      const float bound = __fadd_ru(s_amin, margin);
+      pass = (bound < ek) && isfinite(ek) && isfinite(bound);
+    }
+    a.flags[q] = pass ? 0u : 1u;
+    if (!pass) atomicAdd(a.nflag, 1u);
+  }
+}
+
+// max over rows of |row|_2 and |row|_1 (times the row scale for int8), rounded up. One warp per row.
+template <int DT>
+__global__ void __launch_bounds__(256) row_norm_max_kernel(const void* __restrict__ base, const float* __restrict__ scales,
+                                                           uint64_t n, uint32_t dim, uint32_t* __restrict__ out2) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  float m2 = 0.f, m1 = 0.f;
+  for (uint64_t row = warp0; row < n; row += nwarps) {
+    float s2 = 0.f, s1 = 0.f;
+    if constexpr (DT == kDtF16) {
+      const __half* r = reinterpret_cast<const __half*>(base) + row * dim;
+      for (uint32_t i = lane; i < dim; i += 32) {
+        const float v = __half2float(r[i]);
+        s2 = fmaf(v, v, s2);
+        s1 += fabsf(v);
+      }
+    } else if constexpr (DT == kDtI8) {
+      const int8_t* r = reinterpret_cast<const int8_t*>(base) + row * dim;
+      for (uint32_t i = lane; i < dim; i += 32) {
+        const float v = (float)r[i];
+        s2 = fmaf(v, v, s2);
+        s1 += fabsf(v);
+      }
+    } else {
+      const float* r = reinterpret_cast<const float*>(base) + row * dim;
+      for (uint32_t i = lane; i < dim; i += 32) {
+        const float v = r[i];
+        s2 = fmaf(v, v, s2);
+        s1 += fabsf(v);
+      }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+    }
+    float l2 = sqrtf(s2), l1 = s1;
+    if constexpr (DT == kDtI8) {
+      const float sc = fabsf(scales[row]);
+      l2 *= sc;
+      l1 *= sc;
+    }
+    m2 = fmaxf(m2, l2);
+    m1 = fmaxf(m1, l1);
+  }
+  if (lane == 0) {  // non-negative floats order like their bit patterns; NaN/inf propagate as "huge" -> always flagged
+    atomicMax(out2 + 0, __float_as_uint(m2 * 1.0001f));
+    atomicMax(out2 + 1, __float_as_uint(m1 * 1.0001f));
+  }
+}
+
+}  // namespace
+
+cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, cudaStream_t stream) {
+  if (nq == 0 || a.k == 0) return cudaSuccess;
+  const size_t smem = ((a.dim * 4u + 15u) & ~15u) + (size_t)next_pow2(a.kp) * 8u;
+  if (smem > 200u * 1024u) return cudaErrorInvalidValue;
+  auto launch = [&](auto kern) -> cudaError_t {
+    if (smem > 48u * 1024u) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    kern<<<nq, kRescoreThreads, smem, stream>>>(a);
+    count_launch();
+    return cudaGetLastError();
+  };
+  switch (dtype) {
+    case kDtF16: return launch(rescore_exact_kernel<kDtF16>);
+    case kDtI8: return launch(rescore_exact_kernel<kDtI8>);
+    case kDtF32: return launch(rescore_exact_kernel<kDtF32>);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t row_norm_max_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim, uint32_t* out2,
+                                int num_sms, cudaStream_t stream) {
+  cudaError_t e = cudaMemsetAsync(out2, 0, 8, stream);
+  if (e != cudaSuccess) return e;
+  const int grid = num_sms * 8;
+  switch (dtype) {
+    case kDtF16: row_norm_max_kernel<kDtF16><<<grid, 256, 0, stream>>>(base, scales, n, dim, out2); break;
+    case kDtI8: row_norm_max_kernel<kDtI8><<<grid, 256, 0, stream>>>(base, scales, n, dim, out2); break;
+    case kDtF32: row_norm_max_kernel<kDtF32><<<grid, 256, 0, stream>>>(base, scales, n, dim, out2); break;
+    default: return cudaErrorInvalidValue;
+  }
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace nvdb_b200

@@ -39,6 +39,10 @@ cudaError_t scan_gemv_launch(const ScanLaunch& l, const ScanArgs& a, int nq_temp
 // partial [nq][nlists][k] keys -> final ids / scores [nq][k]
 cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
                                   uint64_t row_offset, uint64_t* out_ids, float* out_scores, cudaStream_t stream);
+// same reduction, but the k best KEYS of query q go to out_keys + q * key_stride (e.g. one more list of a later pass)
+// and the score of the k-th best (-inf when fewer than k exist) to out_thr[q]: the seed of a later pass.
+cudaError_t merge_partials_seed_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
+                                       uint64_t* out_keys, size_t key_stride, float* out_thr, cudaStream_t stream);
 // per-shard results (global ids, scores), list l at ids + l*id_list_stride / scores + l*score_list_stride, each
 // [nq][k] -> [nq][k]
 cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, size_t id_list_stride,
@@ -57,12 +61,15 @@ struct MmaArgs {
   const float* scales;   // [n_rows] row scales (i8) or null
   const float* qscale;   // [mpad]  f16: 2^-e of the query prescale;  i8: s1
   const float* qscale2;  // [mpad]  i8: s2
-  uint64_t* partial;     // [nq][P][k] ordered keys (0 = empty)
+  uint64_t* partial;     // [nq][lists][k] ordered keys (0 = empty); CTA j of an M-tile writes list j
+  const float* thr_init; // [mpad] admission threshold seeds (a lower bound of each query's final k-th best) or null
   void* dbg;             // optional raw accumulators [NACC][mpad][n_rows] (tests only), else null
   uint32_t n_rows, dim, k, nq;
-  uint32_t num_tiles;    // ceil(n_rows / BLOCK_N)
+  uint32_t tile0;        // first base tile of this pass
+  uint32_t num_tiles;    // one past the last base tile of this pass (<= ceil(n_rows / BLOCK_N))
   uint32_t kchunks;      // ceil(dim * elem_size / 128)
   uint32_t G, P;         // M-tiles (128 queries each), CTAs per M-tile; grid = G * P
+  uint32_t lists;        // lists per query in `partial` (>= P)
   uint32_t mpad;         // G * 128
   uint32_t block_n;      // base rows per tile (template selector; the base tensor map's box rows)
   int stages;
@@ -74,6 +81,31 @@ cudaError_t scan_mma_prep_launch(int dtype, int limbs, const float* queries, uin
                                  void* A, float* qs1, float* qs2, cudaStream_t stream);
 cudaError_t scan_mma_launch(int dtype, int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
                             cudaStream_t stream);
+
+// ---- exact re-score + certificate of tensor-core candidates (rescore.cu)
+struct RescoreArgs {
+  const void* base;          // payload
+  const float* scales;       // [n_rows] (i8) or null
+  const float* queries;      // [nq][dim] f32
+  const uint64_t* cand_ids;  // [nq][kp] LOCAL rows ranked by approximate score (~0 = empty)
+  const float* cand_approx;  // [nq][kp] approximate scores
+  uint64_t* out_ids;         // [nq][k] row_offset + row
+  float* out_scores;         // [nq][k] exact (reference-order FP32) scores
+  uint32_t* flags;           // [nq] 1 = certificate failed, the query must be re-run on the exact scan
+  uint32_t* nflag;           // [1] number of flagged queries (caller zeroes it)
+  uint64_t row_offset;
+  uint32_t n_rows, dim, kp, k;
+  float max_l2, max_l1;      // max over rows of |row|_2, |row|_1 (times the row scale for i8), rounded up
+  float rel_err;             // bound on |approx - exact| / (|q|_2 * max_l2) excluding the i8 limb residual term
+};
+cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, cudaStream_t stream);
+cudaError_t row_norm_max_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim, uint32_t* out2,
+                                int num_sms, cudaStream_t stream);
+
+// CTA-pair variant (scan_mma2.cu): f16 only, a.G even, a.P = clusters per pair column, tmap_b with 128-row boxes
+bool scan_mma2_plan(int limbs, uint32_t k, int max_smem, int* stages);
+cudaError_t scan_mma2_launch(int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
+                             cudaStream_t stream);
 
 void count_launch(uint32_t n = 1);
 

@@ -27,16 +27,10 @@
 #include "common.cuh"
 #include "scan.h"
 #include "tc_common.cuh"
+#include "scan_mma_common.cuh"
 
 namespace nvdb_b200 {
 namespace {
-
-constexpr int kMmaThreads = 192;
-constexpr int kBlockM = 128;
-constexpr uint32_t kTmemCols = 512;
-constexpr int kMmaRegK = 16;  // k <= 16: per-thread top-k lists in registers, else in shared memory
-constexpr uint32_t kAccColsPerBuf = 256;
-constexpr uint64_t kSentinelKey = ((uint64_t)0x007FFFFFu << 32);  // (ordered(-inf), row 0xFFFFFFFF): below any real key
 
 // BLOCK_N (base rows per tile == accumulator columns): f16 256 (or 128 when shared memory is short: large k with two
 // limbs); i8 128 (two limb accumulators of 128 columns per buffer).
@@ -150,67 +144,6 @@ __global__ void __launch_bounds__(128) prep_queries_i8_kernel(const float* __res
 // the scan kernel
 // ---------------------------------------------------------------------------------------------------------------
 
-// private sorted (descending) top-k list of one epilogue thread; entry jj lives at list[jj * 128].
-// Returns the new threshold (score of the k-th best).
-__device__ __noinline__ float list_insert(uint64_t* list, uint32_t k, uint64_t key, float thr) {
-  if (key <= list[(k - 1) * kBlockM]) return thr;
-  uint32_t jj = k - 1;
-  while (jj > 0) {
-    const uint64_t p = list[(jj - 1) * kBlockM];
-    if (p >= key) break;
-    list[jj * kBlockM] = p;
-    --jj;
-  }
-  list[jj * kBlockM] = key;
-  return key_score(list[(k - 1) * kBlockM]);
-}
-
-// The per-thread top-k container. KREG == 0: list in shared memory (any k that fits). KREG > 0 (k <= KREG): the list
-// lives in registers — an insert is ~KREG compare/select pairs with no memory latency, which matters because a warp
-// runs the insert path whenever ANY of its 32 queries admits a row.
-template <int KREG>
-struct ThreadTopK {
-  // right-aligned: the best entry is e[KREG - k], the k-th best is ALWAYS e[KREG - 1] (a fixed register); the unused
-  // leading entries hold UINT64_MAX so nothing ever shifts into them. All indices below are compile-time constants.
-  uint64_t e[KREG];
-  uint32_t k;
-  __device__ __forceinline__ void init(uint64_t*, uint32_t k_) {
-    k = k_;
-#pragma unroll
-    for (int u = 0; u < KREG; ++u) e[u] = ((uint32_t)u + k >= (uint32_t)KREG) ? kSentinelKey : ~0ull;
-  }
-  __device__ __forceinline__ float insert(uint64_t key, float thr) {
-    if (key <= e[KREG - 1]) return thr;
-#pragma unroll
-    for (int u = KREG - 1; u >= 1; --u) e[u] = (e[u - 1] < key) ? e[u - 1] : ((e[u] < key) ? key : e[u]);
-    if (e[0] < key) e[0] = key;
-    return key_score(e[KREG - 1]);
-  }
-  // out[jj] = jj-th best, sentinel (row 0xFFFFFFFF) -> 0 (empty)
-  __device__ __forceinline__ void store(uint64_t* out) const {
-#pragma unroll
-    for (int u = 0; u < KREG; ++u)
-      if ((uint32_t)u + k >= (uint32_t)KREG) out[(uint32_t)u + k - (uint32_t)KREG] = ((uint32_t)e[u] == 0u) ? 0ull : e[u];
-  }
-};
-template <>
-struct ThreadTopK<0> {
-  uint64_t* list;
-  uint32_t k;
-  __device__ __forceinline__ void init(uint64_t* l, uint32_t k_) {
-    list = l;
-    k = k_;
-    for (uint32_t jj = 0; jj < k; ++jj) list[jj * kBlockM] = kSentinelKey;
-  }
-  __device__ __forceinline__ float insert(uint64_t key, float thr) { return list_insert(list, k, key, thr); }
-  __device__ __forceinline__ void store(uint64_t* out) const {
-    for (uint32_t jj = 0; jj < k; ++jj) {
-      const uint64_t key = list[jj * kBlockM];
-      out[jj] = ((uint32_t)key == 0u) ? 0ull : key;
-    }
-  }
-};
-
 template <int DT, int LIMBS, int BLOCK_N, int KREG>
 __global__ void __launch_bounds__(kMmaThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const MmaArgs a) {
@@ -252,7 +185,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       tma_prefetch_desc(&tmap_b);
       const uint64_t pol = l2_policy_evict_first();
       uint32_t stage = 0, phase = 0;
-      for (uint32_t tile = j; tile < a.num_tiles; tile += a.P) {
+      for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P) {
         for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + L.stages_off + stage * L.stage_bytes;
@@ -278,7 +211,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     if (lane == 0) {
       constexpr uint32_t idesc = kI8 ? tc::idesc_s8_s32(kBlockM, BLOCK_N) : tc::idesc_f16_f32(kBlockM, BLOCK_N);
       uint32_t stage = 0, phase = 0, it = 0;
-      for (uint32_t tile = j; tile < a.num_tiles; tile += a.P, ++it) {
+      for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P, ++it) {
         const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
         mbar_wait(&tempty[buf], bphase ^ 1);
         tc::fence_after_thread_sync();
@@ -319,12 +252,14 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     ThreadTopK<KREG> top;
     top.init(reinterpret_cast<uint64_t*>(smem + L.lists_off) + ql, a.k);  // smem variant: entry jj at list[jj * 128]
     float* rscale = reinterpret_cast<float*>(smem + L.rscale_off);          // [2][BLOCK_N] row scales (i8)
-    float thr = valid ? -INFINITY : INFINITY;      // score of the current k-th best; padding lanes never insert
+    // admission threshold: score of the current k-th best, optionally seeded with the k-th best of an earlier pass over
+    // other rows (a valid lower bound of the final k-th best); padding lanes never insert
+    float thr = valid ? (a.thr_init ? a.thr_init[qg] : -INFINITY) : INFINITY;
     const float qs1 = a.qscale[qg];
     const float qs2 = kI8 ? a.qscale2[qg] : 0.f;
     const uint32_t lane_addr = tmem_base + ((qd * 32u) << 16);
     uint32_t it = 0;
-    for (uint32_t tile = j; tile < a.num_tiles; tile += a.P, ++it) {
+    for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P, ++it) {
       const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
       const uint32_t row0 = tile * BLOCK_N;
       if constexpr (kI8) {
@@ -385,7 +320,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
           for (int u = 1; u < 32; ++u) sv = (i == u) ? s[u] : sv;
           const uint32_t row = row0 + c0 + (uint32_t)i;
-          if (sv >= thr && row < a.n_rows) thr = top.insert(make_key(sv, row), thr);
+          if (sv >= thr && row < a.n_rows) thr = fmaxf(thr, top.insert(make_key(sv, row), thr));
         }
       }
       tc::fence_before_thread_sync();
@@ -393,7 +328,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       if (lane == 0) mbar_arrive(&tempty[buf]);
     }
     if (valid) {
-      top.store(a.partial + ((size_t)qg * a.P + j) * a.k);
+      top.store(a.partial + ((size_t)qg * a.lists + j) * a.k);
     }
   }
 

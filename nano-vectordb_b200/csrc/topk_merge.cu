@@ -17,7 +17,8 @@ constexpr int kMergeThreads = 512;
 // UINT64_MAX / -inf when fewer than k candidates exist (k > n).
 __global__ void __launch_bounds__(kMergeThreads)
 merge_partials_kernel(const uint64_t* __restrict__ partial, uint32_t nlists, uint32_t k, uint32_t bufn,
-                      uint64_t row_offset, uint64_t* __restrict__ out_ids, float* __restrict__ out_scores) {
+                      uint64_t row_offset, uint64_t* __restrict__ out_ids, float* __restrict__ out_scores,
+                      uint64_t* __restrict__ out_keys, size_t key_stride, float* __restrict__ out_thr) {
   extern __shared__ uint64_t buf[];
   const uint32_t q = blockIdx.x, tid = threadIdx.x;
   const uint64_t* in = partial + (size_t)q * nlists * k;
@@ -31,6 +32,14 @@ merge_partials_kernel(const uint64_t* __restrict__ partial, uint32_t nlists, uin
     bitonic_sort_desc(buf, bufn, tid, kMergeThreads, sync);
     kept = k;
     pos += take;
+  }
+  if (out_keys) {  // seed mode: keys + threshold for a later pass
+    for (uint32_t j = tid; j < k; j += kMergeThreads) out_keys[(size_t)q * key_stride + j] = (total > 0) ? buf[j] : 0ull;
+    if (tid == 0) {
+      const uint64_t kth = (total > 0) ? buf[k - 1] : 0ull;
+      out_thr[q] = kth != 0ull ? key_score(kth) : -INFINITY;
+    }
+    return;
   }
   for (uint32_t j = tid; j < k; j += kMergeThreads) {
     const uint64_t key = (total > 0) ? buf[j] : 0ull;
@@ -84,8 +93,9 @@ merge_lists_kernel(const uint64_t* __restrict__ ids, const float* __restrict__ s
 
 }  // namespace
 
-cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
-                                  uint64_t row_offset, uint64_t* out_ids, float* out_scores, cudaStream_t stream) {
+static cudaError_t merge_partials_any(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
+                                      uint64_t row_offset, uint64_t* out_ids, float* out_scores, uint64_t* out_keys,
+                                      size_t key_stride, float* out_thr, cudaStream_t stream) {
   if (nq == 0 || k == 0) return cudaSuccess;
   // buffer: at least 2k (so every round makes progress), ideally everything in one round, capped at 16384 keys
   uint32_t bufn = next_pow2(nlists * k);
@@ -98,9 +108,20 @@ cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint
     cudaError_t e = cudaFuncSetAttribute(merge_partials_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, nlists, k, bufn, row_offset, out_ids, out_scores);
+  merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, nlists, k, bufn, row_offset, out_ids, out_scores,
+                                                             out_keys, key_stride, out_thr);
   count_launch();
   return cudaGetLastError();
+}
+
+cudaError_t merge_partials_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
+                                  uint64_t row_offset, uint64_t* out_ids, float* out_scores, cudaStream_t stream) {
+  return merge_partials_any(partial, nlists, nq, k, row_offset, out_ids, out_scores, nullptr, 0, nullptr, stream);
+}
+
+cudaError_t merge_partials_seed_launch(const uint64_t* partial, uint32_t nlists, uint32_t nq, uint32_t k,
+                                       uint64_t* out_keys, size_t key_stride, float* out_thr, cudaStream_t stream) {
+  return merge_partials_any(partial, nlists, nq, k, 0, nullptr, nullptr, out_keys, key_stride, out_thr, stream);
 }
 
 cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, size_t id_list_stride,

@@ -3,7 +3,7 @@
 // Same positional arguments and the same stdout keys as the reference harness (apps/nvdb_bench.cpp:254-432):
 //   nvdb_bench <base.vecbin> <query.vecbin> <k> [mode=cuda] [gpus=1] [warmup=5] [batch_q=1] [path=auto]
 // `threads` of the reference becomes `gpus` (row shards, one per device); `tile_vecs` / `prefetch_dist` have no
-// meaning on the GPU and are replaced by `path` = auto | gemv | mma | mma_fast. Per-query (or per-batch) latencies are
+// meaning on the GPU and are replaced by `path` = auto | gemv | mma | mma_fast | mma_exact. Per-query (or per-batch) latencies are
 // std::chrono::steady_clock around the host-buffer search call, i.e. end to end incl. H2D of the queries and D2H of
 // the results; percentiles use the reference's linear interpolation (:370-377); bytes_per_query /
 // payload_equiv_bandwidth_GBps as in :414-418. Extra keys: gt_match (when GT_PATH names a gtbin written by the
@@ -118,7 +118,7 @@ bool load_gtbin(const std::string& path, uint32_t* k, uint64_t* Q, std::vector<u
 int main(int argc, char** argv) {
   if (argc < 4) {
     std::cerr << "Usage: nvdb_bench <base.vecbin> <query.vecbin> <k> [mode=cuda] [gpus=1] [warmup=5] [batch_q=1] "
-                 "[path=auto|gemv|mma|mma_fast]\n";
+                 "[path=auto|gemv|mma|mma_fast|mma_exact]\n";
     return 1;
   }
   try {
@@ -137,6 +137,7 @@ int main(int argc, char** argv) {
     if (path_s == "gemv") path = NVDB_B200_PATH_GEMV;
     else if (path_s == "mma") path = NVDB_B200_PATH_MMA;
     else if (path_s == "mma_fast") path = NVDB_B200_PATH_MMA_FAST;
+    else if (path_s == "mma_exact") path = NVDB_B200_PATH_MMA_EXACT;
     else if (path_s != "auto") throw std::runtime_error("Unknown path: " + path_s);
     nvdb::VectorDataset base, query;
     base.load(base_path);

@@ -16,7 +16,7 @@ N = int(os.environ.get("NVDB_BENCH_ROWS", 2_903_054))
 D, K, SEED = 768, int(os.environ.get("NVDB_K", 10)), 20240229
 dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
-PATHS = os.environ.get("NVDB_PATHS", "gemv,mma,mma_fast").split(",")
+PATHS = os.environ.get("NVDB_PATHS", "gemv,mma,mma_fast,mma_exact").split(",")
 DTYPES = os.environ.get("NVDB_DTYPES", "f16,i8").split(",")
 BATCHES = [int(b) for b in os.environ.get("NVDB_BATCHES", "1,2,4,8,16,32,64,128,256,512,1024").split(",")]
 
@@ -47,7 +47,8 @@ for dtype, name, esz in ((nv.F16, "f16", 2), (nv.I8, "i8", 1)):
             nv.synth_fill_device(0, nv.F32, 1, D, SEED, (i * 104729 * 31) % N, qall[i].data_ptr(), None, stream.cuda_stream)
     stream.synchronize()
     qall += 1e-3 * torch.randn_like(qall)
-    for pname, path in (("gemv", nv.PATH_GEMV), ("mma", nv.PATH_MMA), ("mma_fast", nv.PATH_MMA_FAST)):
+    for pname, path in (("gemv", nv.PATH_GEMV), ("mma", nv.PATH_MMA), ("mma_fast", nv.PATH_MMA_FAST),
+                        ("mma_exact", nv.PATH_MMA_EXACT)):
         if (dtype == nv.I8 and pname == "mma_fast") or pname not in PATHS:
             continue
         idx.set_path(path)
@@ -56,10 +57,14 @@ for dtype, name, esz in ((nv.F16, "f16", 2), (nv.I8, "i8", 1)):
                 continue
             iters = max(3, min(50, int(200 / max(b / 8, 1)))) if pname == "gemv" else max(5, min(50, 4096 // b))
             ms = time_search(idx, qall, b, iters)
-            limbs = 2 if pname == "mma" else 1
+            limbs = 2 if (pname == "mma" or dtype == nv.I8) else 1
+            extra = {}
+            if pname == "mma_exact":
+                nqx, nfb = idx.exact_stats(reset=True)
+                extra["certificate_fallback_rate"] = round(nfb / max(nqx, 1), 4)
             print(json.dumps({"dtype": name, "path": pname, "batch": b, "k": K, "ms_per_batch": round(ms, 4),
                               "qps": round(b / ms * 1e3, 1), "base_GBps_one_pass": round(nbytes / ms / 1e6, 1),
                               "useful_TFLOPs": round(2.0 * b * N * D / ms / 1e9, 1),
                               "issued_TFLOPs": round(2.0 * ((b + 127) // 128 * 128) * N * D * limbs / ms / 1e9, 1)
-                              if pname != "gemv" else None}), flush=True)
+                              if pname != "gemv" else None, **extra}), flush=True)
     idx.close()

@@ -122,7 +122,9 @@ def test_auto_path_crossover_and_timing_path(nv, oracle):
         idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 1, rng), 10, t)
         assert t.path == nv.PATH_GEMV
         idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 2, rng), 10, t)
-        assert t.path == nv.PATH_MMA
+        assert t.path == nv.PATH_GEMV
+        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 3, rng), 10, t)
+        assert t.path == nv.PATH_MMA_EXACT
     f32 = oracle.synth_f32(2, 0, n, d)
     with nv.FlatIndexCuda.from_host(f32, None, F32) as idx:   # FP32 base: no tensor path (tf32 excluded), GEMV always
         t = nv.Timing()
@@ -145,3 +147,146 @@ def test_mma_adversarial_order_and_ties(nv, oracle):
         ids, sc = idx.search_topk_dot_batch(q, 10)
     oids, osc = oracle.search_batch(F16, base.view(np.uint16), None, q, 10)
     assert np.array_equal(ids, oids) and np.array_equal(sc, osc)
+
+
+# ---- PATH_MMA_EXACT: tensor-core candidates + exact re-score + certificate + streaming-scan fallback -------------
+# Bar: ids and FP32 score bits identical to the reference-order oracle (same bar as the streaming scan).
+
+def check_exact(nv, oracle, dtype, base, scales, queries, k, row_offset=0):
+    with nv.FlatIndexCuda.from_host(base, scales, dtype, row_offset=row_offset) as idx:
+        idx.set_path(nv.PATH_MMA_EXACT)
+        ids, sc = idx.search_topk_dot_batch(queries, k)
+        stats = idx.exact_stats()
+    oids, osc = oracle.search_batch(dtype, base, scales, queries, k)
+    kk = min(k, base.shape[0])
+    for qi in range(queries.shape[0]):
+        assert_topk_equal(ids[qi, :kk], sc[qi, :kk], oids[qi, :kk] + row_offset, osc[qi, :kk], what=f"q{qi}")
+        if kk < k:
+            assert np.all(ids[qi, kk:] == np.uint64(0xFFFFFFFFFFFFFFFF)) and np.all(np.isneginf(sc[qi, kk:]))
+    assert stats[0] == queries.shape[0]
+    return stats
+
+
+@pytest.mark.parametrize("dt", ["f16", "i8"])
+@pytest.mark.parametrize("n,d", [(5000, 768), (1000, 384), (257, 64), (40000, 128), (700, 80)])
+@pytest.mark.parametrize("k", [1, 10, 13, 100])
+def test_exact_path_bit_exact_vs_oracle(nv, oracle, dt, n, d, k):
+    dtype = F16 if dt == "f16" else I8
+    base, scales = oracle.synth(dtype, 11, 0, n, d)
+    rng = np.random.default_rng(5)
+    for nq in (1, 4, 127, 129):
+        queries = make_queries(oracle, 11, n, d, nq, rng)
+        check_exact(nv, oracle, dtype, base, scales, queries, k)
+
+
+@pytest.mark.parametrize("dt", ["f16", "i8"])
+def test_exact_path_duplicates_force_fallback(nv, oracle, dt):
+    """32 identical copies of every row: the candidate list cannot separate the k-th score from the excluded rows, so the
+    certificate must fail and the streaming-scan fallback must still return the canonical (score desc, id asc) answer."""
+    dtype = F16 if dt == "f16" else I8
+    b, s = oracle.synth(dtype, 9, 0, 300, 128)
+    base = np.concatenate([b] * 32)
+    scales = None if s is None else np.concatenate([s] * 32)
+    queries = oracle.synth_f32(9, 0, 300, 128)[[5, 77, 100, 299, 3]]
+    with nv.FlatIndexCuda.from_host(base, scales, dtype) as idx:
+        idx.set_path(nv.PATH_MMA_EXACT)
+        ids, sc = idx.search_topk_dot_batch(queries, 10)
+        nquery, nfall = idx.exact_stats()
+    oids, osc = oracle.search_batch(dtype, base, scales, queries, 10)
+    assert np.array_equal(ids, oids)
+    assert np.array_equal(sc.view(np.uint32), osc.view(np.uint32))
+    assert nquery == 5 and nfall == 5
+
+
+def test_exact_path_partial_fallback_and_row_offset(nv, oracle):
+    """a batch where only SOME queries hit duplicated rows: flagged ones are gathered, re-run and scattered back."""
+    n, d = 4000, 128
+    base, _ = oracle.synth(F16, 4, 0, n, d)
+    base = base.copy()
+    base[100:140] = base[100]            # 40 copies of row 100
+    f = oracle.synth_f32(4, 0, n, d)
+    queries = np.ascontiguousarray(f[[7, 100, 2000, 100, 3999, 50]])
+    nquery, nfall = check_exact(nv, oracle, F16, base, None, queries, 10, row_offset=5_000_000_000)
+    assert nfall == 2
+
+
+def test_exact_path_random_data_rarely_falls_back(nv, oracle):
+    n, d = 200_000, 128
+    with nv.FlatIndexCuda.synthetic(F16, n, d, 77) as idx:
+        base, _ = idx.read_rows(0, n)
+        rng = np.random.default_rng(3)
+        queries = make_queries(oracle, 77, n, d, 64, rng)
+        idx.set_path(nv.PATH_MMA_EXACT)
+        ids, sc = idx.search_topk_dot_batch(queries, 10)
+        nquery, nfall = idx.exact_stats()
+        idx.set_path(nv.PATH_GEMV)
+        gids, gsc = idx.search_topk_dot_batch(queries, 10)
+    assert np.array_equal(ids, gids) and np.array_equal(sc.view(np.uint32), gsc.view(np.uint32))
+    assert nquery == 64 and nfall <= 16, f"{nfall} of {nquery} queries fell back"
+
+
+def test_exact_path_adversarial_ascending_groups(nv, oracle):
+    n, d = 6000, 64
+    base = np.zeros((n, d), np.float16)
+    base[:, 0] = (np.arange(n) // 4).astype(np.float16)
+    q = np.zeros((5, d), np.float32)
+    q[:, 0] = 1.0
+    check_exact(nv, oracle, F16, base.view(np.uint16), None, q, 10)
+
+
+@pytest.mark.parametrize("dt", ["f16", "i8"])
+@pytest.mark.parametrize("k", [10, 100])
+def test_threshold_seeding_does_not_change_results(nv, oracle, dt, k):
+    """the seeded two-pass scan (first ~1/16 of the rows -> admission thresholds for the rest) must return exactly what
+    the single pass returns, on every tensor-core path; forced on here (knob = 2) because auto needs >= 32 tiles per CTA."""
+    dtype = F16 if dt == "f16" else I8
+    n, d = 100_000, 64
+    rng = np.random.default_rng(8)
+    with nv.FlatIndexCuda.synthetic(dtype, n, d, 5) as idx:
+        base, scales = idx.read_rows(0, n)
+        f = oracle.synth_f32(5, 0, n, d)
+        for nq in (4, 300):
+            queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
+            got = {}
+            for seed in (0, 2):
+                idx.set_tuning(nv.capi.TUNE_MMA_SEED, seed)
+                for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT) + ((nv.PATH_MMA_FAST,) if dtype == F16 else ()):
+                    idx.set_path(path)
+                    got[(seed, path)] = idx.search_topk_dot_batch(queries, k)
+            for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT) + ((nv.PATH_MMA_FAST,) if dtype == F16 else ()):
+                a, b = got[(0, path)], got[(2, path)]
+                assert np.array_equal(a[0], b[0]), f"ids differ: path {path} nq {nq}"
+                assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), f"scores differ: path {path} nq {nq}"
+            # and the exact path still equals the oracle on a few queries
+            pick = [0, nq // 2, nq - 1]
+            oids, osc = oracle.search_batch(dtype, base, scales, queries[pick], k)
+            for j, qi in enumerate(pick):
+                assert_topk_equal(got[(2, nv.PATH_MMA_EXACT)][0][qi], got[(2, nv.PATH_MMA_EXACT)][1][qi], oids[j], osc[j],
+                                  what=f"seeded exact q{qi}")
+
+
+@pytest.mark.parametrize("k", [10, 100])
+def test_cta_pair_kernel_matches_single_cta_kernel(nv, oracle, k):
+    """cta_group::2 scan (even number of 128-query tiles) against the single-CTA scan and the oracle."""
+    n, d = 60_000, 128
+    rng = np.random.default_rng(12)
+    with nv.FlatIndexCuda.synthetic(F16, n, d, 6) as idx:
+        base, _ = idx.read_rows(0, n)
+        f = oracle.synth_f32(6, 0, n, d)
+        for nq in (256, 200, 1000):       # G = 2, 2 (padded tile), 8
+            queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
+            got = {}
+            for pair in (0, 1):
+                idx.set_tuning(nv.capi.TUNE_MMA_2CTA, pair)
+                for path in (nv.PATH_MMA_EXACT, nv.PATH_MMA, nv.PATH_MMA_FAST):
+                    idx.set_path(path)
+                    got[(pair, path)] = idx.search_topk_dot_batch(queries, k)
+            a, b = got[(0, nv.PATH_MMA_EXACT)], got[(1, nv.PATH_MMA_EXACT)]
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), f"exact nq={nq}"
+            for path, rtol in ((nv.PATH_MMA, RTOL_F16), (nv.PATH_MMA_FAST, RTOL_F16_FAST)):
+                s0, s1 = got[(0, path)][1], got[(1, path)][1]
+                assert np.max(np.abs(s0 - s1)) <= rtol * np.abs(s0).max(), f"path {path} nq={nq}"
+            pick = [0, nq // 3, nq - 1]
+            oids, osc = oracle.search_batch(F16, base, None, queries[pick], k)
+            for j, qi in enumerate(pick):
+                assert_topk_equal(b[0][qi], b[1][qi], oids[j], osc[j], what=f"pair exact nq={nq} q{qi}")

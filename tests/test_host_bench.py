@@ -74,9 +74,9 @@ def test_nvdb_bench_cuda_matches_reference_gtbin(bench, oracle, tmp_path, dt):
     assert float(re.search(r"gt_match=([0-9.]+)", out).group(1)) == 1.0
     want = n * d * {F32: 4, F16: 2, I8: 1}[dtype] + (4 * n if dtype == I8 else 0)
     assert int(re.search(r"bytes_per_query=(\d+)", out).group(1)) == want
-    # batches of 8 -> tensor-core scan for f16 / i8 (tolerance mode): ids still match on this tie-free data
+    # batches of 8 -> exact tensor-core path for f16 / i8 (bit-identical to the streaming scan)
     r = run(bench, tmp_path / "b.vecbin", tmp_path / "q.raw12", k, "cuda", 1, 2, 8, env=env)
     assert r.returncode == 0, r.stderr
     assert "batch_samples=3" in r.stdout and "Avg_batch:" in r.stdout and "batch_p99:" in r.stdout
     assert float(re.search(r"gt_match=([0-9.]+)", r.stdout).group(1)) >= 0.99
-    assert f"path_used={1 if dtype == F32 else 2}" in r.stdout
+    assert f"path_used={1 if dtype == F32 else 4}" in r.stdout   # AUTO: exact tensor-core path for f16 / i8 batches
