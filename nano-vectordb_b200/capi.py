@@ -14,7 +14,7 @@ import numpy as np
 
 F32, F16, I8 = 1, 2, 3
 PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST, PATH_MMA_EXACT = 0, 1, 2, 3, 4
-TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA = 1, 2, 3
+TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA, TUNE_FUSED_MERGE = 1, 2, 3, 4
 _NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
 
 lib_path = Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"

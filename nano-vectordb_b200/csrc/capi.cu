@@ -43,8 +43,8 @@ struct nvdb_b200_index {
   const void* tmap_a_ptr = nullptr;
   uint32_t tmap_a_rows = 0;
   // grow-only workspaces
-  void* d_ws[16] = {};
-  size_t d_ws_bytes[16] = {};
+  void* d_ws[20] = {};
+  size_t d_ws_bytes[20] = {};
   void* h_pin[3] = {nullptr, nullptr, nullptr};
   size_t h_pin_bytes[3] = {0, 0, 0};
   // exact tensor-core path (rescore.cu): row-norm maxima of the base (lazy) and certificate statistics
@@ -53,8 +53,9 @@ struct nvdb_b200_index {
   uint64_t exact_queries = 0, exact_fallbacks = 0;
   // tuning knobs (nvdb_b200_index_set_tuning; defaults may be overridden by environment variables at creation)
   int tune_mma_seed = 1;   // 0 off, 1 auto (>= 256 queries and >= 32 tiles per CTA), 2 whenever there are >= 2 tiles per CTA
+  int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
-  int tune_mma_2cta = 1;   // 0 never, 1 auto: CTA-pair (cta_group::2) tensor-core scan where it applies
+  int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 auto (k > 16), 2 whenever the shape allows
   std::mutex mu;
   mutable std::string err;
   // optional per-kernel event timing (bench.py's roofline figure)
@@ -68,7 +69,7 @@ namespace {
 thread_local std::string t_err;
 enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5, WS_MMA_A = 6,
        WS_MMA_QS = 7, WS_DBG = 8, WS_X_IDS = 9, WS_X_APX = 10, WS_X_FLAGS = 11, WS_X_Q = 12, WS_X_OUT_IDS = 13,
-       WS_X_OUT_SC = 14, WS_SEED = 15 };
+       WS_X_OUT_SC = 14, WS_SEED = 15, WS_GEMV_CTR = 16 };
 
 int fail(const nvdb_b200_index* idx, int code, const std::string& msg) {
   t_err = msg;
@@ -197,6 +198,7 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
   if (const char* ev = getenv("NVDB_B200_MMA_SEED")) h->tune_mma_seed = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_GEMV_CTAS")) h->tune_gemv_ctas = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_MMA_2CTA")) h->tune_mma_2cta = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_FUSED_MERGE")) h->tune_fused_merge = atoi(ev);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
   if (e != cudaSuccess) {
@@ -494,7 +496,11 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
   // every pass handles up to 128 * num_sms queries; G M-tiles x P CTAs (or CTA pairs) each.
   // CTA-pair kernel (scan_mma2.cu): f16 bases, an even number of M-tiles, 256-row tiles, P = clusters per pair column.
   int stages2 = 0;
-  const bool pair_ok = idx->dtype == kDtF16 && idx->tune_mma_2cta && !dbg && scan_mma2_plan(limbs, k, idx->max_smem, &stages2);
+  // auto (1): only for k > 16 — with register lists the single-CTA kernel already runs at the power-limited tensor rate
+  // (3.39 vs 3.6-3.8 ms at batch 1024), with shared-memory lists it would fall back to 128-row tiles and the pair kernel
+  // wins (k = 100: 6.8 vs 8.2 ms; profiles/r1_ab_round8.jsonl). 2 = whenever the shape allows.
+  const bool pair_ok = idx->dtype == kDtF16 && !dbg && (idx->tune_mma_2cta == 2 || (idx->tune_mma_2cta == 1 && k > 16u)) &&
+                       scan_mma2_plan(limbs, k, idx->max_smem, &stages2);
   struct PassPlan {
     bool pair;
     uint32_t G, P, bn, tiles;
@@ -620,6 +626,22 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   a.num_tiles = (uint32_t)((idx->n + kScanRowsPerTile - 1) / kScanRowsPerTile);
   a.kchunks = (uint32_t)(((size_t)idx->dim * elem_size(idx->dtype) + 127) / 128);
   a.stages = plan.stages;
+  // fused final merge in the scan's last CTA when the survivors' buffer fits the TMA ring (tuning knob FUSED_MERGE)
+  // (auto: up to 4096 keys per query — beyond that one CTA sorting alone is slower than the 512-thread merge kernel:
+  // k = 100, 148 lists: 0.95 vs 0.86 ms, profiles/r1_ab_fused_merge.jsonl; 2 = whenever the buffer fits)
+  const size_t merge_keys = (size_t)next_pow2((uint32_t)plan.grid * k);
+  const bool fused = idx->tma_ok && idx->tune_fused_merge && merge_keys * 8u <= (size_t)plan.stages * 32768u &&
+                     (idx->tune_fused_merge == 2 || merge_keys <= 4096u);
+  a.done_counter = nullptr;
+  a.out_ids = nullptr;
+  a.out_scores = nullptr;
+  a.row_offset = idx->row_offset;
+  if (fused) {
+    const bool fresh = idx->d_ws[WS_GEMV_CTR] == nullptr;
+    if ((rc = ensure_ws(idx, WS_GEMV_CTR, 256))) return rc;
+    if (fresh) CK(cudaMemsetAsync(idx->d_ws[WS_GEMV_CTR], 0, 256, stream), "memset merge counter");
+    a.done_counter = (uint32_t*)idx->d_ws[WS_GEMV_CTR];
+  }
   cudaEvent_t* pev = nullptr;
   if ((rc = prof_begin(idx, stream, &pev))) return rc;
   for (uint32_t q0 = 0; q0 < nq; q0 += (uint32_t)plan.nq_template) {
@@ -630,15 +652,21 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
     a.nq = left < (uint32_t)t ? left : (uint32_t)t;
     a.queries = d_queries + (size_t)q0 * idx->dim;
     a.partial = partial + (size_t)q0 * plan.grid * k;
+    if (fused) {
+      a.out_ids = d_out_ids + (size_t)q0 * k;
+      a.out_scores = d_out_scores + (size_t)q0 * k;
+    }
     CK(scan_gemv_launch(L, a, t), "scan_gemv launch");
     count_launch();
     if (launches) ++*launches;
   }
   if (pev) CK(cudaEventRecord(pev[1], stream), "profile event record");
-  CK(merge_partials_launch(partial, (uint32_t)plan.grid, nq, k, idx->row_offset, d_out_ids, d_out_scores, stream),
-     "merge_partials launch");
+  if (!fused) {
+    CK(merge_partials_launch(partial, (uint32_t)plan.grid, nq, k, idx->row_offset, d_out_ids, d_out_scores, stream),
+       "merge_partials launch");
+    if (launches) ++*launches;
+  }
   if (pev) CK(cudaEventRecord(pev[2], stream), "profile event record");
-  if (launches) ++*launches;
   return NVDB_B200_OK;
 }
 
@@ -838,6 +866,7 @@ int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value) {
     case NVDB_B200_TUNE_MMA_SEED: idx->tune_mma_seed = value; break;
     case NVDB_B200_TUNE_GEMV_CTAS: idx->tune_gemv_ctas = value; break;
     case NVDB_B200_TUNE_MMA_2CTA: idx->tune_mma_2cta = value; break;
+    case NVDB_B200_TUNE_FUSED_MERGE: idx->tune_fused_merge = value; break;
     default: return fail(idx, NVDB_B200_ERR_ARG, "unknown tuning knob");
   }
   return NVDB_B200_OK;

@@ -15,6 +15,12 @@ struct ScanArgs {
   const float* scales;   // [n_rows] (i8) or null
   const void* base;      // payload (generic kernel only)
   uint64_t* partial;     // [nq][grid][k] ordered keys
+  // fused final merge (TMA kernel only): when done_counter != null the last CTA to finish writes the final top-k of this
+  // pass's queries to out_ids / out_scores ([nq][k]); needs next_pow2(grid * k) * 8 bytes <= stages * 32 KB
+  uint32_t* done_counter;  // zero-initialised; the merging CTA resets it
+  uint64_t* out_ids;
+  float* out_scores;
+  uint64_t row_offset;
   uint32_t n_rows;
   uint32_t dim;
   uint32_t k;

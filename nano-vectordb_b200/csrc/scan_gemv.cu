@@ -185,6 +185,60 @@ scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a)
   sel.compact(tid, kConsumers, csync);
   // partial layout: [query][cta][k]
   sel.store(a.partial + (size_t)blockIdx.x * a.k, (size_t)gridDim.x * a.k, a.nq, tid, kConsumers);
+
+  // ---- fused final merge: the CTA that finishes last reduces the gridDim.x lists of every query (replaces the serial
+  // heap merges of src/flat_index_omp.cpp:67-75 and a separate merge launch: ~25 us of a 680 us batch-1 step).
+  if (a.done_counter == nullptr) return;
+  __shared__ uint32_t s_ticket, s_cnt;
+  __shared__ uint64_t s_floor;
+  __threadfence();  // this thread's partial keys are visible device-wide before the ticket is taken
+  csync();
+  if (tid == 0) s_ticket = atomicAdd(a.done_counter, 1u);
+  csync();
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence();
+  // all TMA loads of this CTA were consumed, so the ring is free: it becomes the survivors' buffer
+  uint64_t* buf = reinterpret_cast<uint64_t*>(smem + L.stages_off);
+  const uint32_t nlists = gridDim.x, total = nlists * a.k;
+  for (uint32_t qi = 0; qi < a.nq; ++qi) {
+    const uint64_t* in = a.partial + (size_t)qi * total;
+    // every list is sorted descending, so the final k-th best is >= the best of the lists' own k-th entries
+    if (tid == 0) {
+      s_floor = 0ull;
+      s_cnt = 0u;
+    }
+    csync();
+    uint64_t fl = 0ull;
+    for (uint32_t l = tid; l < nlists; l += kConsumers) {
+      const uint64_t v = __ldcg(in + (size_t)l * a.k + (a.k - 1));
+      fl = v > fl ? v : fl;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const uint64_t o = __shfl_xor_sync(0xffffffffu, fl, off);
+      fl = o > fl ? o : fl;
+    }
+    if ((tid & 31u) == 0 && fl) atomicMax(reinterpret_cast<unsigned long long*>(&s_floor), (unsigned long long)fl);
+    csync();
+    const uint64_t floor_key = s_floor;
+    for (uint32_t i = tid; i < total; i += kConsumers) {
+      const uint64_t v = __ldcg(in + i);
+      if (v != 0ull && v >= floor_key) buf[atomicAdd(&s_cnt, 1u)] = v;
+    }
+    csync();
+    const uint32_t cnt = s_cnt, bufn = next_pow2(cnt < 2u ? 2u : cnt);
+    for (uint32_t i = cnt + tid; i < bufn; i += kConsumers) buf[i] = 0ull;
+    csync();
+    bitonic_sort_desc(buf, bufn, tid, kConsumers, csync);
+    for (uint32_t j = tid; j < a.k; j += kConsumers) {
+      const uint64_t key = j < cnt ? buf[j] : 0ull;
+      const bool ok = key != 0ull;
+      a.out_ids[(size_t)qi * a.k + j] = ok ? a.row_offset + (uint64_t)key_row(key) : ~0ull;
+      a.out_scores[(size_t)qi * a.k + j] = ok ? key_score(key) : -INFINITY;
+    }
+    csync();
+  }
+  if (tid == 0) *a.done_counter = 0u;  // ready for the next launch on this stream
 }
 
 // ---- generic fallback for shapes the tensor map cannot describe (row bytes not a multiple of 16, or dims with a

@@ -119,3 +119,23 @@ def test_device_synth_matches_oracle(nv, oracle, dt):
     assert np.array_equal(payload, op)
     if dtype == I8:
         assert np.array_equal(scales.view(np.uint32), osc.view(np.uint32))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "i8"])
+@pytest.mark.parametrize("n,d,k", [(40000, 128, 10), (40000, 128, 100), (5000, 768, 1), (300, 64, 50), (70000, 64, 700)])
+def test_fused_final_merge_equals_separate_merge_kernel(nv, oracle, dt, n, d, k):
+    """the merge done by the scan's last CTA (default) and the separate merge kernel must agree bit for bit, for
+    repeated launches on the same index (the completion counter is reset by the merging CTA)."""
+    dtype = DT[dt]
+    base, scales = make_base(oracle, dtype, n, d, seed=21)
+    rng = np.random.default_rng(2)
+    f = oracle.synth_f32(21, 0, n, d)
+    with nv.FlatIndexCuda.from_host(base, scales, dtype) as idx:
+        idx.set_path(nv.PATH_GEMV)
+        for nq in (1, 1, 5, 13, 1):
+            queries = np.ascontiguousarray(f[rng.integers(0, n, nq)])
+            idx.set_tuning(nv.capi.TUNE_FUSED_MERGE, 2)      # 2 = fuse whenever the survivors' buffer fits the ring
+            a = idx.search_topk_dot_batch(queries, k)
+            idx.set_tuning(nv.capi.TUNE_FUSED_MERGE, 0)
+            b = idx.search_topk_dot_batch(queries, k)
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), f"nq={nq}"

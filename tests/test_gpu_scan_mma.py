@@ -276,15 +276,15 @@ def test_cta_pair_kernel_matches_single_cta_kernel(nv, oracle, k):
         for nq in (256, 200, 1000):       # G = 2, 2 (padded tile), 8
             queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
             got = {}
-            for pair in (0, 1):
+            for pair in (0, 2):
                 idx.set_tuning(nv.capi.TUNE_MMA_2CTA, pair)
                 for path in (nv.PATH_MMA_EXACT, nv.PATH_MMA, nv.PATH_MMA_FAST):
                     idx.set_path(path)
                     got[(pair, path)] = idx.search_topk_dot_batch(queries, k)
-            a, b = got[(0, nv.PATH_MMA_EXACT)], got[(1, nv.PATH_MMA_EXACT)]
+            a, b = got[(0, nv.PATH_MMA_EXACT)], got[(2, nv.PATH_MMA_EXACT)]
             assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), f"exact nq={nq}"
             for path, rtol in ((nv.PATH_MMA, RTOL_F16), (nv.PATH_MMA_FAST, RTOL_F16_FAST)):
-                s0, s1 = got[(0, path)][1], got[(1, path)][1]
+                s0, s1 = got[(0, path)][1], got[(2, path)][1]
                 assert np.max(np.abs(s0 - s1)) <= rtol * np.abs(s0).max(), f"path {path} nq={nq}"
             pick = [0, nq // 3, nq - 1]
             oids, osc = oracle.search_batch(F16, base, None, queries[pick], k)
