@@ -25,14 +25,27 @@ $(LIBDIR)/libnvdb_b200.so: $(CU_OBJS)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(ARCH) -shared -ccbin $(CXX) -o $@ $^
 
-HOST_SRCS := $(wildcard $(PKG)/host/*.cpp)
-host: lib $(BINDIR)/nvdb_bench
+HOST_HDRS := $(wildcard $(PKG)/host/*.h) include/nvdb_b200.h
+HOST_BINS := $(BINDIR)/nvdb_bench $(BINDIR)/nvdb_gt_build $(BINDIR)/nvdb_convert_f16 $(BINDIR)/nvdb_quantize_i8
+HOST_CXX  := $(CXX) -std=c++17 -O2 -fopenmp -Iinclude -I$(PKG)/host
+HOST_LD   := -L$(LIBDIR) -lnvdb_b200 -Wl,-rpath,'$$ORIGIN/../lib' -lpthread
+host: lib $(HOST_BINS)
 
-$(BINDIR)/nvdb_bench: $(HOST_SRCS) $(wildcard $(PKG)/host/*.h) include/nvdb_b200.h
+$(BINDIR)/nvdb_bench: $(PKG)/host/nvdb_bench.cpp $(HOST_HDRS)
 	@mkdir -p $(BINDIR)
-	@if [ -n "$(HOST_SRCS)" ]; then \
-	  $(CXX) -std=c++17 -O2 -fopenmp -Iinclude -I$(PKG)/host -o $@ $(HOST_SRCS) -L$(LIBDIR) -lnvdb_b200 -Wl,-rpath,'$$ORIGIN/../lib' -lpthread; \
-	fi
+	$(HOST_CXX) -o $@ $< $(HOST_LD)
+
+$(BINDIR)/nvdb_gt_build: $(PKG)/host/nvdb_gt_build.cpp $(HOST_HDRS)
+	@mkdir -p $(BINDIR)
+	$(HOST_CXX) -o $@ $< $(HOST_LD)
+
+# one source, two names: the tool picks f32->f16 or ->i8 from argv[0] (the reference ships two separate tools)
+$(BINDIR)/nvdb_convert_f16: $(PKG)/host/nvdb_convert.cpp $(HOST_HDRS)
+	@mkdir -p $(BINDIR)
+	$(HOST_CXX) -o $@ $< $(HOST_LD)
+
+$(BINDIR)/nvdb_quantize_i8: $(BINDIR)/nvdb_convert_f16
+	cp $< $@
 
 clean:
 	rm -rf build $(LIBDIR) $(BINDIR)

@@ -156,6 +156,16 @@ int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, c
 int nvdb_b200_synth_fill_device(int device, uint32_t dtype, uint64_t n, uint32_t dim, uint64_t seed,
                                 uint64_t first_row, void* payload_dev, float* scales_dev, void* stream);
 
+/* ---- converters ------------------------------------------------------------------------------------------------
+ * The reference's fixture tools on the device, bit-identical outputs (tests/golden): f32 -> f16 is IEEE round-to-
+ * nearest-even (tools/nvdb_convert_f16.cpp:20-119); f32 | f16 -> i8 is scale = max|x|/127 (1 for an all-zero row),
+ * q = clamp(lrint(x * (1.0f/scale)), -127, 127) in FP32 with the scale stored per row (apps/nvdb_quantize_i8.cpp:57-85).
+ * The host-buffer form streams the rows through the device in pinned chunks; dst_scales is required for i8 only. */
+int nvdb_b200_convert(int device, uint32_t src_dtype, const void* src_host, uint32_t dst_dtype, uint64_t n, uint32_t dim,
+                      void* dst_payload_host, float* dst_scales_host);
+int nvdb_b200_convert_device(int device, uint32_t src_dtype, const void* src_dev, uint32_t dst_dtype, uint64_t n,
+                             uint32_t dim, void* dst_payload_dev, float* dst_scales_dev, void* stream);
+
 /* ---- introspection for the harness ------------------------------------------------------------------------ */
 /* kernels launched by this library in this process so far (bench.py's gpu_launches). */
 uint64_t nvdb_b200_launch_count(void);

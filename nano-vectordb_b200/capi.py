@@ -8,6 +8,7 @@ nvdb::cuda_l2_topk_batch (reference include/nvdb/cuda_refine.h:25-38).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
@@ -17,7 +18,7 @@ PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST, PATH_MMA_EXACT = 0, 1, 2, 3, 4
 TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA, TUNE_FUSED_MERGE = 1, 2, 3, 4
 _NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
 
-lib_path = Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"
+lib_path = Path(os.environ.get("NVDB_B200_LIB", Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"))
 if not lib_path.exists():
     raise ImportError(f"{lib_path} is not built (run `make lib` or __graft_entry__.build()); "
                       "there is no CPU fallback for this path")
@@ -60,6 +61,8 @@ _sig = {
     "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_refine_l2_device": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_synth_fill_device": (_i, [_i, _u32, _u64, _u32, _u64, _u64, _vp, _vp, _vp]),
+    "nvdb_b200_convert": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp]),
+    "nvdb_b200_convert_device": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp, _vp]),
     "nvdb_b200_launch_count": (_u64, []),
     "nvdb_b200_index_profile": (_i, [_vp, _i]),
     "nvdb_b200_index_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_u32)]),
@@ -222,3 +225,13 @@ class FlatIndexCuda:
     def refine_l2_device(self, queries_ptr, cand_ptr, Q, R, K, out_ids_ptr, out_dist_ptr, stream=None):
         _check(lib.nvdb_b200_refine_l2_device(self._h, queries_ptr, cand_ptr, Q, R, K, out_ids_ptr, out_dist_ptr,
                                               stream), self._h)
+
+
+def convert(src: np.ndarray, src_dtype: int, dst_dtype: int, device: int = 0):
+    """Reference converters on the device (nvdb_convert_f16 / nvdb_quantize_i8 semantics): returns (payload, scales)."""
+    src = np.ascontiguousarray(src)
+    n, dim = src.shape
+    out = np.empty((n, dim), _NP[dst_dtype])
+    scales = np.empty(n, np.float32) if dst_dtype == I8 else None
+    _check(lib.nvdb_b200_convert(device, src_dtype, _ptr(src), dst_dtype, n, dim, _ptr(out), _ptr(scales)))
+    return out, scales

@@ -334,6 +334,108 @@ int nvdb_b200_index_create_device(const void* payload_dev, const float* scales_d
   return rc;
 }
 
+int nvdb_b200_convert_device(int device, uint32_t src_dtype, const void* src_dev, uint32_t dst_dtype, uint64_t n,
+                             uint32_t dim, void* dst_payload_dev, float* dst_scales_dev, void* stream) {
+  const nvdb_b200_index* idx = nullptr;
+  const bool ok = (src_dtype == kDtF32 && dst_dtype == kDtF16) || ((src_dtype == kDtF32 || src_dtype == kDtF16) && dst_dtype == kDtI8);
+  if (!ok) return fail(nullptr, NVDB_B200_ERR_ARG, "convert: supported conversions are f32->f16 and f32|f16->i8");
+  if (n == 0 || dim == 0) return NVDB_B200_OK;
+  if (!src_dev || !dst_payload_dev || (dst_dtype == kDtI8 && !dst_scales_dev))
+    return fail(nullptr, NVDB_B200_ERR_ARG, "convert: NULL buffer");
+  CK(cudaSetDevice(device), "cudaSetDevice");
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+  CK(convert_launch((int)src_dtype, src_dev, (int)dst_dtype, n, dim, dst_payload_dev, dst_scales_dev, prop.multiProcessorCount,
+                    (cudaStream_t)stream),
+     "convert launch");
+  return NVDB_B200_OK;
+}
+
+// Host-buffer converter (what nvdb_convert_f16 / nvdb_quantize_i8 do on the CPU): rows stream through the device in
+// chunks — pinned staging, H2D, convert kernel, D2H — two chunks in flight.
+int nvdb_b200_convert(int device, uint32_t src_dtype, const void* src_host, uint32_t dst_dtype, uint64_t n, uint32_t dim,
+                      void* dst_payload_host, float* dst_scales_host) {
+  const nvdb_b200_index* idx = nullptr;
+  const bool ok = (src_dtype == kDtF32 && dst_dtype == kDtF16) || ((src_dtype == kDtF32 || src_dtype == kDtF16) && dst_dtype == kDtI8);
+  if (!ok) return fail(nullptr, NVDB_B200_ERR_ARG, "convert: supported conversions are f32->f16 and f32|f16->i8");
+  if (n == 0 || dim == 0) return NVDB_B200_OK;
+  if (!src_host || !dst_payload_host || (dst_dtype == kDtI8 && !dst_scales_host))
+    return fail(nullptr, NVDB_B200_ERR_ARG, "convert: NULL buffer");
+  CK(cudaSetDevice(device), "cudaSetDevice");
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+  const size_t ses = elem_size(src_dtype), des = elem_size(dst_dtype);
+  const size_t src_row = (size_t)dim * ses, dst_row = (size_t)dim * des;
+  uint64_t chunk = (64ull << 20) / src_row;  // ~64 MB of source rows per chunk
+  if (chunk == 0) chunk = 1;
+  if (chunk > n) chunk = n;
+  struct Slot {
+    void *h_src = nullptr, *h_dst = nullptr, *d_src = nullptr, *d_dst = nullptr;
+    float *h_sc = nullptr, *d_sc = nullptr;
+    cudaStream_t s = nullptr;
+    uint64_t row0 = 0, rows = 0;
+  } slot[2];
+  int rc = NVDB_B200_OK;
+  auto cleanup = [&] {
+    for (auto& sl : slot) {
+      if (sl.s) cudaStreamSynchronize(sl.s);
+      cudaFreeHost(sl.h_src);
+      cudaFreeHost(sl.h_dst);
+      cudaFreeHost(sl.h_sc);
+      cudaFree(sl.d_src);
+      cudaFree(sl.d_dst);
+      cudaFree(sl.d_sc);
+      if (sl.s) cudaStreamDestroy(sl.s);
+    }
+  };
+#define CKC(call, what)                      \
+  do {                                       \
+    cudaError_t _e = (call);                 \
+    if (_e != cudaSuccess) {                 \
+      rc = fail_cuda(idx, _e, what);         \
+      cleanup();                             \
+      return rc;                             \
+    }                                        \
+  } while (0)
+  for (auto& sl : slot) {
+    CKC(cudaStreamCreateWithFlags(&sl.s, cudaStreamNonBlocking), "convert stream");
+    CKC(cudaMallocHost(&sl.h_src, chunk * src_row), "convert pinned");
+    CKC(cudaMallocHost(&sl.h_dst, chunk * dst_row), "convert pinned");
+    CKC(cudaMallocHost((void**)&sl.h_sc, chunk * 4), "convert pinned");
+    CKC(cudaMalloc(&sl.d_src, chunk * src_row), "convert device buffer");
+    CKC(cudaMalloc(&sl.d_dst, chunk * dst_row), "convert device buffer");
+    CKC(cudaMalloc((void**)&sl.d_sc, chunk * 4), "convert device buffer");
+  }
+  auto drain = [&](Slot& sl) -> cudaError_t {
+    if (sl.rows == 0) return cudaSuccess;
+    cudaError_t e = cudaStreamSynchronize(sl.s);
+    if (e != cudaSuccess) return e;
+    std::memcpy((char*)dst_payload_host + sl.row0 * dst_row, sl.h_dst, sl.rows * dst_row);
+    if (dst_dtype == kDtI8) std::memcpy(dst_scales_host + sl.row0, sl.h_sc, sl.rows * 4);
+    sl.rows = 0;
+    return cudaSuccess;
+  };
+  int cur = 0;
+  for (uint64_t r0 = 0; r0 < n; r0 += chunk, cur ^= 1) {
+    Slot& sl = slot[cur];
+    CKC(drain(sl), "convert drain");
+    const uint64_t rows = n - r0 < chunk ? n - r0 : chunk;
+    std::memcpy(sl.h_src, (const char*)src_host + r0 * src_row, rows * src_row);
+    CKC(cudaMemcpyAsync(sl.d_src, sl.h_src, rows * src_row, cudaMemcpyHostToDevice, sl.s), "convert H2D");
+    CKC(convert_launch((int)src_dtype, sl.d_src, (int)dst_dtype, rows, dim, sl.d_dst, sl.d_sc, prop.multiProcessorCount, sl.s),
+        "convert launch");
+    CKC(cudaMemcpyAsync(sl.h_dst, sl.d_dst, rows * dst_row, cudaMemcpyDeviceToHost, sl.s), "convert D2H");
+    if (dst_dtype == kDtI8) CKC(cudaMemcpyAsync(sl.h_sc, sl.d_sc, rows * 4, cudaMemcpyDeviceToHost, sl.s), "convert D2H scales");
+    sl.row0 = r0;
+    sl.rows = rows;
+  }
+  CKC(drain(slot[0]), "convert drain");
+  CKC(drain(slot[1]), "convert drain");
+#undef CKC
+  cleanup();
+  return NVDB_B200_OK;
+}
+
 int nvdb_b200_synth_fill_device(int device, uint32_t dtype, uint64_t n, uint32_t dim, uint64_t seed,
                                 uint64_t first_row, void* payload_dev, float* scales_dev, void* stream) {
   const nvdb_b200_index* idx = nullptr;

@@ -24,6 +24,9 @@ struct Elem<kDtI8> { static constexpr int size = 1, per16 = 16; };
 // round-to-nearest FMA, so the chain values stay bit-identical to the scalar form while the FMA-pipe instruction
 // count halves. `c` is the 16-byte piece index inside the 128-byte chunk (compile-time after unrolling).
 
+#ifndef NVDB_DOT_PACKED_FMA
+#define NVDB_DOT_PACKED_FMA 1
+#endif
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
@@ -36,6 +39,18 @@ __device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
   uint64_t d;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   return d;
+}
+// Same two FMAs as scalar instructions (A/B knob: -DNVDB_DOT_PACKED_FMA=0 builds the f16 / f32 chains with FFMA).
+__device__ __forceinline__ uint64_t ffma_pair(uint64_t a, uint64_t b, uint64_t c) {
+#if NVDB_DOT_PACKED_FMA
+  return ffma2(a, b, c);
+#else
+  float a0, a1, b0, b1, c0, c1;
+  unpack2(a, a0, a1);
+  unpack2(b, b0, b1);
+  unpack2(c, c0, c1);
+  return pack2(__fmaf_rn(a0, b0, c0), __fmaf_rn(a1, b1, c1));
+#endif
 }
 __device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
   uint64_t d;
@@ -53,16 +68,23 @@ __device__ __forceinline__ float4 ldsq(uint32_t addr) {
 
 // x[p] = row elements of chains (2p, 2p+1); q = shared-memory byte address of the 8 query elements of the same
 // columns (query 0), qstride = bytes between consecutive queries.
-template <int NQ>
+template <int NQ, int PK = 1>
 __device__ __forceinline__ void fma8(uint64_t (&acc)[NQ][4], const uint64_t (&x)[4], uint32_t q, uint32_t qstride) {
 #pragma unroll
   for (int qi = 0; qi < NQ; ++qi) {
     const float4 qa = ldsq(q + qi * qstride);
     const float4 qb = ldsq(q + qi * qstride + 16u);
-    acc[qi][0] = ffma2(pack2(qa.x, qa.y), x[0], acc[qi][0]);
-    acc[qi][1] = ffma2(pack2(qa.z, qa.w), x[1], acc[qi][1]);
-    acc[qi][2] = ffma2(pack2(qb.x, qb.y), x[2], acc[qi][2]);
-    acc[qi][3] = ffma2(pack2(qb.z, qb.w), x[3], acc[qi][3]);
+    if constexpr (PK) {
+      acc[qi][0] = ffma2(pack2(qa.x, qa.y), x[0], acc[qi][0]);
+      acc[qi][1] = ffma2(pack2(qa.z, qa.w), x[1], acc[qi][1]);
+      acc[qi][2] = ffma2(pack2(qb.x, qb.y), x[2], acc[qi][2]);
+      acc[qi][3] = ffma2(pack2(qb.z, qb.w), x[3], acc[qi][3]);
+    } else {
+      acc[qi][0] = ffma_pair(pack2(qa.x, qa.y), x[0], acc[qi][0]);
+      acc[qi][1] = ffma_pair(pack2(qa.z, qa.w), x[1], acc[qi][1]);
+      acc[qi][2] = ffma_pair(pack2(qb.x, qb.y), x[2], acc[qi][2]);
+      acc[qi][3] = ffma_pair(pack2(qb.z, qb.w), x[3], acc[qi][3]);
+    }
   }
 }
 
@@ -77,7 +99,7 @@ __device__ __forceinline__ void consume16(uint64_t (&acc)[NQ][4], const uint4 v,
       const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));  // exact widening
       x[i] = pack2(f.x, f.y);
     }
-    fma8<NQ>(acc, x, q, qstride);
+    fma8<NQ, NVDB_DOT_PACKED_FMA>(acc, x, q, qstride);
   } else if constexpr (DT == kDtF32) {
     // 4 elements: chains 0..3 for even pieces, 4..7 for odd pieces
     const uint64_t x0 = pack2(__uint_as_float(v.x), __uint_as_float(v.y));
@@ -86,8 +108,8 @@ __device__ __forceinline__ void consume16(uint64_t (&acc)[NQ][4], const uint4 v,
 #pragma unroll
     for (int qi = 0; qi < NQ; ++qi) {
       const float4 qa = ldsq(q + qi * qstride);
-      acc[qi][p0 + 0] = ffma2(pack2(qa.x, qa.y), x0, acc[qi][p0 + 0]);
-      acc[qi][p0 + 1] = ffma2(pack2(qa.z, qa.w), x1, acc[qi][p0 + 1]);
+      acc[qi][p0 + 0] = ffma_pair(pack2(qa.x, qa.y), x0, acc[qi][p0 + 0]);
+      acc[qi][p0 + 1] = ffma_pair(pack2(qa.z, qa.w), x1, acc[qi][p0 + 1]);
     }
   } else {
     // 16 int8: elements 0..7 then 8..15 into the same 8 chains (src/simd_dot.cpp:175-187).

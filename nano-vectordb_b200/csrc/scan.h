@@ -113,6 +113,10 @@ bool scan_mma2_plan(int limbs, uint32_t k, int max_smem, int* stages);
 cudaError_t scan_mma2_launch(int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
                              cudaStream_t stream);
 
+// reference converters on the device (convert.cu): f32 -> f16 (RNE); f32 | f16 -> i8 + per-row scale
+cudaError_t convert_launch(int src_dtype, const void* src, int dst_dtype, uint64_t n, uint32_t dim, void* dst, float* scales,
+                           int num_sms, cudaStream_t stream);
+
 void count_launch(uint32_t n = 1);
 
 }  // namespace nvdb_b200

@@ -58,10 +58,14 @@ __host__ __device__ inline SmemLayout make_layout(int stages, int nq, uint32_t d
   return L;
 }
 
-// Single-query passes are compiled for two resident CTAs per SM (<= 113 registers); capi.cu decides per dtype
-// whether the launch actually uses one CTA with a deep ring or two with half the ring each.
+// Single-query passes can be compiled for two resident CTAs per SM (<= 113 registers; -DNVDB_GEMV_TWO_CTAS=1) so that
+// the TUNE_GEMV_CTAS knob has something to select; measured slower than one CTA with the deep ring for every dtype
+// (profiles/r1_gemv_ffma2_ctas.jsonl), so the default build does not constrain the register allocation.
+#ifndef NVDB_GEMV_TWO_CTAS
+#define NVDB_GEMV_TWO_CTAS 0
+#endif
 template <int DT, int NQ>
-__global__ void __launch_bounds__(kThreads, NQ == 1 ? 2 : 1)
+__global__ void __launch_bounds__(kThreads, (NQ == 1 && NVDB_GEMV_TWO_CTAS) ? 2 : 1)
 scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
