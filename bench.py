@@ -194,9 +194,34 @@ def run_reference(args):
     return 0
 
 
+_JSON_FD = None
+
+
+def _reserve_stdout():
+    """stdout carries exactly ONE JSON line: everything else a library prints to fd 1 (e.g. the NCCL version banner,
+    which ignores NCCL_DEBUG_FILE) goes to stderr; emit() writes the line to the real stdout."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, data)
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
+
+    _reserve_stdout()
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback")
@@ -346,7 +371,7 @@ def run_ours(args):
                                 "sample": r["sample"], "qps_equiv_full_base": r["value"] * 1e9 / nbytes}
     idx.close()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -804,8 +804,14 @@ bool mma_exact_supported(const nvdb_b200_index* idx, uint32_t k) {
   return idx->mma_ok && scan_mma_plan((int)idx->dtype, idx->dtype == kDtF16 ? 1 : 2, exact_kprime(k), idx->max_smem, &bn, &st);
 }
 
+int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                     float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* fallbacks);
+
+// `deferred` != null: only enqueue (scan, re-score, D2H of the flag count) and set *deferred; the caller synchronises the
+// stream together with its own copies and then calls mma_exact_finish (the host-buffer API does this, so the common
+// no-fallback case costs ONE stream sync per search). deferred == null: finish here (device-buffer API).
 int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
-                          float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
+                          float* d_out_scores, cudaStream_t stream, uint32_t* launches, bool* deferred) {
   if (!mma_exact_supported(idx, k))
     return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "exact tensor-core scan: unsupported base layout or k too large");
   const uint32_t kp = exact_kprime(k);
@@ -848,10 +854,25 @@ int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t
   if (launches) ++*launches;
   uint32_t* h = (uint32_t*)idx->h_pin[2];
   CK(cudaMemcpyAsync(h, nflag, 4, cudaMemcpyDeviceToHost, stream), "D2H flag count");
+  if (deferred) {
+    *deferred = true;
+    return NVDB_B200_OK;
+  }
   CK(cudaStreamSynchronize(stream), "exact scan sync");
+  return mma_exact_finish(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches, nullptr);
+}
+
+// After the stream has been synchronised: read the flag count and re-run flagged queries on the streaming scan
+// (asynchronous on `stream`; *fallbacks tells the caller whether the outputs were rewritten).
+int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                     float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* fallbacks) {
+  int rc;
+  uint32_t* h = (uint32_t*)idx->h_pin[2];
+  uint32_t* flags = (uint32_t*)idx->d_ws[WS_X_FLAGS] + 4;
   const uint32_t nf = h[0];
   idx->exact_queries += nq;
   idx->exact_fallbacks += nf;
+  if (fallbacks) *fallbacks = nf;
   if (nf == 0) return NVDB_B200_OK;
 
   // ---- fallback: flagged queries go through the streaming scan ------------------------------------------------
@@ -889,14 +910,15 @@ int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t
 constexpr uint32_t kMmaCrossover = 3;
 
 int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
-                       float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* path_used) {
+                       float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* path_used,
+                       bool* deferred = nullptr) {
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
     path = (nq >= kMmaCrossover && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
   if (path_used) *path_used = (uint32_t)path;
   if (path == NVDB_B200_PATH_GEMV) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
   if (path == NVDB_B200_PATH_MMA_EXACT)
-    return mma_exact_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
+    return mma_exact_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches, deferred);
   return mma_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches,
                          path == NVDB_B200_PATH_MMA_FAST ? 1 : 2, nullptr, idx->row_offset);
 }
@@ -939,8 +961,9 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
   CK(cudaEventRecord(idx->ev[1], s), "event");
   uint32_t launches = 0, path_used = 0;
+  bool deferred = false;
   rc = search_device_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, (uint64_t*)idx->d_ws[WS_OUT_IDS],
-                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches, &path_used);
+                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches, &path_used, &deferred);
   if (rc) return rc;
   CK(cudaEventRecord(idx->ev[2], s), "event");
   char* hp = (char*)idx->h_pin[1];
@@ -948,6 +971,19 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   CK(cudaMemcpyAsync(hp + ibytes, idx->d_ws[WS_OUT_SCORES], sbytes, cudaMemcpyDeviceToHost, s), "D2H scores");
   CK(cudaEventRecord(idx->ev[3], s), "event");
   CK(cudaEventSynchronize(idx->ev[3]), "search sync");
+  if (deferred) {  // exact tensor-core path: the certificate verdict arrived with the results
+    uint32_t nfall = 0;
+    rc = mma_exact_finish(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, (uint64_t*)idx->d_ws[WS_OUT_IDS],
+                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches, &nfall);
+    if (rc) return rc;
+    if (nfall) {  // flagged queries were re-run on the streaming scan: fetch the corrected results
+      CK(cudaEventRecord(idx->ev[2], s), "event");
+      CK(cudaMemcpyAsync(hp, idx->d_ws[WS_OUT_IDS], ibytes, cudaMemcpyDeviceToHost, s), "D2H ids");
+      CK(cudaMemcpyAsync(hp + ibytes, idx->d_ws[WS_OUT_SCORES], sbytes, cudaMemcpyDeviceToHost, s), "D2H scores");
+      CK(cudaEventRecord(idx->ev[3], s), "event");
+      CK(cudaEventSynchronize(idx->ev[3]), "search sync");
+    }
+  }
   std::memcpy(out_ids, hp, ibytes);
   std::memcpy(out_scores, hp + ibytes, sbytes);
   if (timing) {
