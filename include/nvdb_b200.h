@@ -124,6 +124,7 @@ enum {
   NVDB_B200_TUNE_MMA_SEED = 1,  /* threshold-seeding pass of the tensor-core scan: 0 off, 1 auto (default), 2 always */
   NVDB_B200_TUNE_GEMV_CTAS = 2, /* CTAs per SM of the single-query streaming scan: 1 (default) | 2 */
   NVDB_B200_TUNE_FUSED_MERGE = 4, /* final merge inside the streaming scan's last CTA: 0 never, 1 auto (default), 2 always */
+  NVDB_B200_TUNE_MMA_RESIDENT = 5, /* i8 tensor scan: first query limb resident in shared memory: 1 (default) | 0 */
   NVDB_B200_TUNE_MMA_2CTA = 3   /* CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 auto (default: k > 16), 2 always */
 };
 int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value);
@@ -131,6 +132,13 @@ int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value);
 /* Certificate statistics of NVDB_B200_PATH_MMA_EXACT since creation / the last reset: queries answered through it and
  * how many of them failed the certificate and were re-run on the streaming scan. */
 int nvdb_b200_index_exact_stats(nvdb_b200_index* idx, uint64_t* queries, uint64_t* fallbacks, int reset);
+
+/* Two-stage search (coarse scan + exact re-rank, both on the device): `coarse` and `fine` are two indexes over the SAME
+ * rows on one device (e.g. the INT8 and the FP16 copy of a base); the coarse scan keeps R >= k candidates per query
+ * (R <= 4096), which are re-ranked by their exact reference-order dot products over `fine`. Halves the bytes scanned at
+ * FP16-grade scores; approximate (recall < 1 is possible when a true neighbour falls below rank R in the coarse scan). */
+int nvdb_b200_search_two_stage(nvdb_b200_index* coarse, nvdb_b200_index* fine, const float* queries_host, uint32_t nq,
+                               uint32_t k, uint32_t R, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing);
 
 /* Test hook for the tensor-core scan: runs the NVDB_B200_PATH_MMA / _MMA_FAST scan of `nq` host queries (k = 1) and
  * returns the RAW accumulators of every (query, row) pair: f16 base -> out_acc[nq][n] float bit patterns (before

@@ -15,7 +15,7 @@ import numpy as np
 
 F32, F16, I8 = 1, 2, 3
 PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST, PATH_MMA_EXACT = 0, 1, 2, 3, 4
-TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA, TUNE_FUSED_MERGE = 1, 2, 3, 4
+TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA, TUNE_FUSED_MERGE, TUNE_MMA_RESIDENT = 1, 2, 3, 4, 5
 _NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
 
 lib_path = Path(os.environ.get("NVDB_B200_LIB", Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"))
@@ -53,6 +53,7 @@ _sig = {
     "nvdb_b200_index_read_rows": (_i, [_vp, _u64, _u64, _vp, _vp]),
     "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_search_device": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_search_two_stage": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_debug_mma_accumulators": (_i, [_vp, _vp, _u32, _i, _vp]),
     "nvdb_b200_index_set_tuning": (_i, [_vp, _i, _i]),
     "nvdb_b200_index_exact_stats": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), _i]),
@@ -235,3 +236,14 @@ def convert(src: np.ndarray, src_dtype: int, dst_dtype: int, device: int = 0):
     scales = np.empty(n, np.float32) if dst_dtype == I8 else None
     _check(lib.nvdb_b200_convert(device, src_dtype, _ptr(src), dst_dtype, n, dim, _ptr(out), _ptr(scales)))
     return out, scales
+
+
+def search_two_stage(coarse: "FlatIndexCuda", fine: "FlatIndexCuda", queries: np.ndarray, k: int, R: int, timing=None):
+    """coarse top-R scan (e.g. the INT8 copy) + exact re-rank over `fine` (e.g. the FP16 copy): (ids u64, scores f32)"""
+    queries = np.ascontiguousarray(queries, np.float32)
+    nq = queries.shape[0]
+    ids = np.empty((nq, k), np.uint64)
+    sc = np.empty((nq, k), np.float32)
+    _check(lib.nvdb_b200_search_two_stage(coarse._h, fine._h, _ptr(queries), nq, k, R, _ptr(ids), _ptr(sc),
+                                          C.byref(timing) if timing is not None else None), coarse._h)
+    return ids, sc

@@ -53,6 +53,7 @@ struct nvdb_b200_index {
   uint64_t exact_queries = 0, exact_fallbacks = 0;
   // tuning knobs (nvdb_b200_index_set_tuning; defaults may be overridden by environment variables at creation)
   int tune_mma_seed = 1;   // 0 off, 1 auto (>= 256 queries and >= 32 tiles per CTA), 2 whenever there are >= 2 tiles per CTA
+  int tune_mma_resident = 1; // i8 tensor scan: query limb 0 resident in shared memory (0: stream both limbs)
   int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
   int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 auto (k > 16), 2 whenever the shape allows
@@ -657,6 +658,8 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
     a.stages = pp.pair ? stages2 : stages;
     a.block_n = pp.bn;
     a.evict_first_base = (a.G == 1);
+    a.resident_a = idx->tune_mma_resident;
+    a.max_smem = idx->max_smem;
     const CUtensorMap* tmb = (pp.bn == 256 && !pp.pair) ? &idx->tmap : &idx->tmap_mma_b;
     auto launch_scan = [&](const MmaArgs& args) {
       return pp.pair ? scan_mma2_launch(limbs, &idx->tmap_mma_a, tmb, args, stream)
@@ -1005,6 +1008,7 @@ int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value) {
     case NVDB_B200_TUNE_GEMV_CTAS: idx->tune_gemv_ctas = value; break;
     case NVDB_B200_TUNE_MMA_2CTA: idx->tune_mma_2cta = value; break;
     case NVDB_B200_TUNE_FUSED_MERGE: idx->tune_fused_merge = value; break;
+    case NVDB_B200_TUNE_MMA_RESIDENT: idx->tune_mma_resident = value; break;
     default: return fail(idx, NVDB_B200_ERR_ARG, "unknown tuning knob");
   }
   return NVDB_B200_OK;
@@ -1016,6 +1020,92 @@ int nvdb_b200_index_exact_stats(nvdb_b200_index* idx, uint64_t* queries, uint64_
   if (queries) *queries = idx->exact_queries;
   if (fallbacks) *fallbacks = idx->exact_fallbacks;
   if (reset) idx->exact_queries = idx->exact_fallbacks = 0;
+  return NVDB_B200_OK;
+}
+
+// Two-stage search: coarse scan over a compact copy of the base (typically INT8) keeps R
+// candidates per query, which are re-ranked by their EXACT reference-order dot products over the fine copy (FP16 /
+// FP32) without leaving the device. Approximate by construction (a true neighbour the coarse scan ranks below R is
+// lost); scores of the returned ids are bit-identical to what the fine index's own scan would return for them.
+int nvdb_b200_search_two_stage(nvdb_b200_index* coarse, nvdb_b200_index* fine, const float* queries_host, uint32_t nq,
+                               uint32_t k, uint32_t R, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing) {
+  nvdb_b200_index* idx = coarse;
+  if (timing) *timing = nvdb_b200_timing{};
+  if (!coarse || !fine) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!queries_host) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if (!out_ids || !out_scores) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+  if (coarse == fine || coarse->device != fine->device || coarse->n != fine->n || coarse->dim != fine->dim ||
+      coarse->row_offset != fine->row_offset)
+    return fail(idx, NVDB_B200_ERR_ARG, "two_stage: coarse and fine must be two copies of the same rows on one device");
+  if (R < k) R = k;
+  if (R > 4096u) return fail(idx, NVDB_B200_ERR_ARG, "two_stage: R <= 4096");
+  std::scoped_lock g(coarse->mu, fine->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  const size_t qbytes = (size_t)nq * idx->dim * 4, ibytes = (size_t)nq * k * 8, sbytes = (size_t)nq * k * 4;
+  int rc;
+  if ((rc = ensure_ws(idx, WS_QUERIES, qbytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_IDS, ibytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_SCORES, sbytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_IDS, (size_t)nq * R * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_APX, (size_t)nq * R * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_FLAGS, ((size_t)nq + 4) * 4))) return rc;
+  if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
+  if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
+  cudaStream_t s = idx->stream;
+  std::memcpy(idx->h_pin[0], queries_host, qbytes);
+  CK(cudaEventRecord(idx->ev[0], s), "event");
+  CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
+  CK(cudaEventRecord(idx->ev[1], s), "event");
+  const float* dq = (const float*)idx->d_ws[WS_QUERIES];
+  uint64_t* cand = (uint64_t*)idx->d_ws[WS_X_IDS];
+  float* capx = (float*)idx->d_ws[WS_X_APX];
+  uint32_t launches = 0;
+  // stage 1: coarse top-R (tolerance-mode tensor scan for batches, streaming scan otherwise — no re-score needed here)
+  uint32_t bn;
+  int st;
+  const bool tensor = coarse->mma_ok && nq >= 3 && scan_mma_plan((int)coarse->dtype, 2, R, coarse->max_smem, &bn, &st);
+  rc = tensor ? mma_search_impl(coarse, dq, nq, R, cand, capx, s, &launches, coarse->dtype == kDtF16 ? 1 : 2, nullptr,
+                                coarse->row_offset)
+              : gemv_search_impl(coarse, dq, nq, R, cand, capx, s, &launches);
+  if (rc) return rc;
+  // stage 2: exact re-rank over the fine copy
+  RescoreArgs r{};
+  r.base = fine->payload;
+  r.scales = fine->scales;
+  r.queries = dq;
+  r.cand_ids = cand;
+  r.cand_approx = capx;
+  r.out_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
+  r.out_scores = (float*)idx->d_ws[WS_OUT_SCORES];
+  r.nflag = (uint32_t*)idx->d_ws[WS_X_FLAGS];
+  r.flags = r.nflag + 4;
+  r.row_offset = fine->row_offset;
+  r.cand_offset = coarse->row_offset;
+  r.n_rows = (uint32_t)fine->n;
+  r.dim = fine->dim;
+  r.kp = R;
+  r.k = k;
+  r.max_l2 = r.max_l1 = INFINITY;  // no certificate: every query is "flagged", the flags are ignored
+  r.rel_err = 0.f;
+  CK(rescore_exact_launch((int)fine->dtype, r, nq, s), "rescore launch");
+  ++launches;
+  CK(cudaEventRecord(idx->ev[2], s), "event");
+  char* hp = (char*)idx->h_pin[1];
+  CK(cudaMemcpyAsync(hp, idx->d_ws[WS_OUT_IDS], ibytes, cudaMemcpyDeviceToHost, s), "D2H ids");
+  CK(cudaMemcpyAsync(hp + ibytes, idx->d_ws[WS_OUT_SCORES], sbytes, cudaMemcpyDeviceToHost, s), "D2H scores");
+  CK(cudaEventRecord(idx->ev[3], s), "event");
+  CK(cudaEventSynchronize(idx->ev[3]), "search sync");
+  std::memcpy(out_ids, hp, ibytes);
+  std::memcpy(out_scores, hp + ibytes, sbytes);
+  if (timing) {
+    cudaEventElapsedTime(&timing->h2d_ms, idx->ev[0], idx->ev[1]);
+    cudaEventElapsedTime(&timing->kernel_ms, idx->ev[1], idx->ev[2]);
+    cudaEventElapsedTime(&timing->d2h_ms, idx->ev[2], idx->ev[3]);
+    cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
+    timing->kernel_launches = launches;
+    timing->path = tensor ? NVDB_B200_PATH_MMA : NVDB_B200_PATH_GEMV;
+  }
   return NVDB_B200_OK;
 }
 

@@ -115,8 +115,9 @@ rescore_exact_kernel(const RescoreArgs a) {
   for (uint32_t c = tid; c < bufn; c += kRescoreThreads) {
     uint64_t key = 0ull;
     if (c < a.kp) {
-      const uint64_t row64 = cid[c];
-      if (row64 != ~0ull && row64 < (uint64_t)a.n_rows) {
+      const uint64_t raw = cid[c];
+      const uint64_t row64 = raw - a.cand_offset;
+      if (raw != ~0ull && raw >= a.cand_offset && row64 < (uint64_t)a.n_rows) {
         const uint32_t row = (uint32_t)row64;
         float s = exact_dot_row<DT>(reinterpret_cast<const uint8_t*>(a.base) + (size_t)row * row_bytes, row_bytes, sq_u32);
         if constexpr (DT == kDtI8) s = __fmul_rn(s, __ldg(a.scales + row));  // src/simd_dot.cpp:198

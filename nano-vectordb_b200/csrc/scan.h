@@ -80,6 +80,8 @@ struct MmaArgs {
   uint32_t block_n;      // base rows per tile (template selector; the base tensor map's box rows)
   int stages;
   int evict_first_base;  // base tiles are read once (G == 1): keep them out of L2
+  int resident_a;        // i8: keep query limb 0 resident in shared memory when it fits (tuning knob)
+  int max_smem;          // opt-in shared memory per CTA
 };
 
 bool scan_mma_plan(int dtype, int limbs, uint32_t k, int max_smem, uint32_t* block_n, int* stages);
@@ -100,6 +102,7 @@ struct RescoreArgs {
   uint32_t* flags;           // [nq] 1 = certificate failed, the query must be re-run on the exact scan
   uint32_t* nflag;           // [1] number of flagged queries (caller zeroes it)
   uint64_t row_offset;
+  uint64_t cand_offset;      // subtracted from cand_ids before use (candidates produced with a row_offset)
   uint32_t n_rows, dim, kp, k;
   float max_l2, max_l1;      // max over rows of |row|_2, |row|_1 (times the row scale for i8), rounded up
   float rel_err;             // bound on |approx - exact| / (|q|_2 * max_l2) excluding the i8 limb residual term

@@ -36,23 +36,27 @@ namespace {
 // limbs); i8 128 (two limb accumulators of 128 columns per buffer).
 
 struct MmaSmem {
-  uint32_t stages_off, lists_off, rscale_off, bars_off, tmem_off, total, stage_bytes, a_limb_bytes, b_bytes;
+  uint32_t stages_off, res_off, lists_off, rscale_off, bars_off, tmem_off, total, stage_bytes, a_limb_bytes, b_bytes;
 };
 
-__host__ __device__ inline MmaSmem mma_layout(uint32_t block_n, int limbs, int stages, uint32_t k) {
+// res_chunks > 0: limb 0 of the query operand stays RESIDENT in shared memory for the whole kernel (res_chunks K chunks of
+// 16 KB, loaded once); the ring then carries only the remaining limb(s) and the base tile.
+__host__ __device__ inline MmaSmem mma_layout(uint32_t block_n, int limbs, int stages, uint32_t k, uint32_t res_chunks = 0) {
   MmaSmem L;
   L.a_limb_bytes = kBlockM * 128u;
   L.b_bytes = block_n * 128u;
-  L.stage_bytes = (uint32_t)limbs * L.a_limb_bytes + L.b_bytes;
+  L.stage_bytes = (uint32_t)(limbs - (res_chunks ? 1 : 0)) * L.a_limb_bytes + L.b_bytes;
   uint32_t off = 0;
   L.stages_off = off;
   off += (uint32_t)stages * L.stage_bytes;
+  L.res_off = off;
+  off += res_chunks * L.a_limb_bytes;
   L.lists_off = off;
   off += k * kBlockM * 8u;
   L.rscale_off = off;
   off += 2u * block_n * 4u;
   L.bars_off = off;
-  off += (2u * (uint32_t)stages + 4u) * 8u;
+  off += (2u * (uint32_t)stages + 5u) * 8u;  // full[], empty[], tfull[2], tempty[2], resident-operand barrier
   L.tmem_off = off;
   off += 16u;
   L.total = off + 1024u;  // slack for the 1024-byte alignment of the swizzled stages
@@ -144,18 +148,20 @@ __global__ void __launch_bounds__(128) prep_queries_i8_kernel(const float* __res
 // the scan kernel
 // ---------------------------------------------------------------------------------------------------------------
 
-template <int DT, int LIMBS, int BLOCK_N, int KREG>
+template <int DT, int LIMBS, int BLOCK_N, int KREG, int RES = 0>
 __global__ void __launch_bounds__(kMmaThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const MmaArgs a) {
   constexpr int ES = (DT == kDtF16) ? 2 : 1, EPC = 128 / ES;  // elements per 128-byte chunk
   constexpr bool kI8 = (DT == kDtI8);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, KREG > 0 ? 0u : a.k);
+  static_assert(RES == 0 || LIMBS == 2, "resident limb 0 + streamed limb 1");
+  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, KREG > 0 ? 0u : a.k, RES ? a.kchunks : 0u);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars_off);
   uint64_t* empty = full + a.stages;
   uint64_t* tfull = empty + a.stages;   // [2] accumulator buffer ready for the epilogue
   uint64_t* tempty = tfull + 2;         // [2] accumulator buffer drained by the epilogue
+  uint64_t* resbar = tempty + 2;        // resident query limb landed (RES)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
 
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -170,6 +176,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       mbar_init(&tfull[b], 1);
       mbar_init(&tempty[b], 4);  // one arrival per epilogue warp
     }
+    mbar_init(resbar, 1);
     mbar_fence_init();
   }
   if (warp == 2) tc::tmem_alloc(tmem_slot, kTmemCols);
@@ -184,6 +191,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       tma_prefetch_desc(&tmap_a);
       tma_prefetch_desc(&tmap_b);
       const uint64_t pol = l2_policy_evict_first();
+      if constexpr (RES) {  // limb 0 of this M-tile: all K chunks, once
+        mbar_arrive_expect_tx(resbar, a.kchunks * L.a_limb_bytes);
+        for (uint32_t kc = 0; kc < a.kchunks; ++kc)
+          tma_load_2d(smem + L.res_off + kc * L.a_limb_bytes, &tmap_a, resbar, (int)(kc * EPC), (int)(m_tile * kBlockM));
+      }
       uint32_t stage = 0, phase = 0;
       for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P) {
         for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
@@ -191,10 +203,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           uint8_t* st = smem + L.stages_off + stage * L.stage_bytes;
           mbar_arrive_expect_tx(&full[stage], L.stage_bytes);
 #pragma unroll
-          for (int l = 0; l < LIMBS; ++l)
-            tma_load_2d(st + l * L.a_limb_bytes, &tmap_a, &full[stage], (int)(kc * EPC),
+          for (int l = RES; l < LIMBS; ++l)
+            tma_load_2d(st + (l - RES) * L.a_limb_bytes, &tmap_a, &full[stage], (int)(kc * EPC),
                         (int)(l * a.mpad + m_tile * kBlockM));
-          uint8_t* sb = st + LIMBS * L.a_limb_bytes;
+          uint8_t* sb = st + (LIMBS - RES) * L.a_limb_bytes;
           if (a.evict_first_base)
             tma_load_2d_hint(sb, &tmap_b, &full[stage], (int)(kc * EPC), (int)(tile * BLOCK_N), pol);
           else
@@ -211,6 +223,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     if (lane == 0) {
       constexpr uint32_t idesc = kI8 ? tc::idesc_s8_s32(kBlockM, BLOCK_N) : tc::idesc_f16_f32(kBlockM, BLOCK_N);
       uint32_t stage = 0, phase = 0, it = 0;
+      if constexpr (RES) {
+        mbar_wait(resbar, 0);
+        tc::fence_after_thread_sync();
+      }
+      const uint32_t res_u32 = smem_u32(smem + L.res_off);
       for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P, ++it) {
         const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
         mbar_wait(&tempty[buf], bphase ^ 1);
@@ -219,10 +236,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           mbar_wait(&full[stage], phase);
           tc::fence_after_thread_sync();
           const uint32_t st = smem_u32(smem + L.stages_off + stage * L.stage_bytes);
-          const uint64_t bdesc = tc::smem_desc_k128(st + LIMBS * L.a_limb_bytes);
+          const uint64_t bdesc = tc::smem_desc_k128(st + (LIMBS - RES) * L.a_limb_bytes);
 #pragma unroll
           for (int l = 0; l < LIMBS; ++l) {
-            const uint64_t adesc = tc::smem_desc_k128(st + l * L.a_limb_bytes);
+            const uint64_t adesc = (RES && l == 0) ? tc::smem_desc_k128(res_u32 + kc * L.a_limb_bytes)
+                                                   : tc::smem_desc_k128(st + (l - RES) * L.a_limb_bytes);
             const uint32_t acc = tmem_base + buf * kAccColsPerBuf + (kI8 ? (uint32_t)l * BLOCK_N : 0u);
 #pragma unroll
             for (uint32_t k4 = 0; k4 < 4; ++k4) {  // 4 x 32 bytes of K per 128-byte chunk (UMMA_K = 16 f16 / 32 i8)
@@ -337,10 +355,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   if (warp == 2) tc::tmem_dealloc(tmem_base, kTmemCols);
 }
 
-template <int DT, int LIMBS, int BLOCK_N, int KREG>
+template <int DT, int LIMBS, int BLOCK_N, int KREG, int RES = 0>
 cudaError_t launch_mma_k(const CUtensorMap* ta, const CUtensorMap* tb, const MmaArgs& a, cudaStream_t stream) {
-  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, KREG > 0 ? 0u : a.k);
-  auto kern = scan_mma_kernel<DT, LIMBS, BLOCK_N, KREG>;
+  const MmaSmem L = mma_layout(BLOCK_N, LIMBS, a.stages, KREG > 0 ? 0u : a.k, RES ? a.kchunks : 0u);
+  auto kern = scan_mma_kernel<DT, LIMBS, BLOCK_N, KREG, RES>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
   if (e != cudaSuccess) return e;
   kern<<<a.G * a.P, kMmaThreads, L.total, stream>>>(*ta, *tb, a);
@@ -389,7 +407,19 @@ cudaError_t scan_mma_launch(int dtype, int limbs, const CUtensorMap* tmap_a, con
   if (dtype == kDtF16 && limbs == 2 && a.block_n == 256) return launch_mma<kDtF16, 2, 256>(tmap_a, tmap_b, a, stream);
   if (dtype == kDtF16 && limbs == 1 && a.block_n == 128) return launch_mma<kDtF16, 1, 128>(tmap_a, tmap_b, a, stream);
   if (dtype == kDtF16 && limbs == 2 && a.block_n == 128) return launch_mma<kDtF16, 2, 128>(tmap_a, tmap_b, a, stream);
-  if (dtype == kDtI8 && limbs == 2 && a.block_n == 128) return launch_mma<kDtI8, 2, 128>(tmap_a, tmap_b, a, stream);
+  if (dtype == kDtI8 && limbs == 2 && a.block_n == 128) {
+    // resident first query limb (per-step operand traffic 48 -> 32 KB; the i8 scan is L2->SM feed-bound, ncu: tensor pipe
+    // 52 % busy at 13.9 TB/s of operand traffic) whenever it fits next to a >= 4-deep ring and register lists
+    if (a.resident_a && a.k <= (uint32_t)kMmaRegK) {
+      for (int st = 6; st >= 4; --st)
+        if (mma_layout(128, 2, st, 0u, a.kchunks).total <= (uint32_t)a.max_smem) {
+          MmaArgs b = a;
+          b.stages = st;
+          return launch_mma_k<kDtI8, 2, 128, kMmaRegK, 1>(tmap_a, tmap_b, b, stream);
+        }
+    }
+    return launch_mma<kDtI8, 2, 128>(tmap_a, tmap_b, a, stream);
+  }
   return cudaErrorInvalidValue;
 }
 

@@ -24,8 +24,8 @@ dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 PATHS = {"gemv": nv.PATH_GEMV, "mma": nv.PATH_MMA, "mma_fast": nv.PATH_MMA_FAST, "mma_exact": nv.PATH_MMA_EXACT,
          "auto": nv.PATH_AUTO}
-KNOBS = {"seed": nv.capi.TUNE_MMA_SEED, "ctas": nv.capi.TUNE_GEMV_CTAS, "pair": nv.capi.TUNE_MMA_2CTA, "fuse": nv.capi.TUNE_FUSED_MERGE}
-DEFAULTS = {"seed": 1, "ctas": 1, "pair": 1, "fuse": 1}
+KNOBS = {"seed": nv.capi.TUNE_MMA_SEED, "ctas": nv.capi.TUNE_GEMV_CTAS, "pair": nv.capi.TUNE_MMA_2CTA, "fuse": nv.capi.TUNE_FUSED_MERGE, "res": nv.capi.TUNE_MMA_RESIDENT}
+DEFAULTS = {"seed": 1, "ctas": 1, "pair": 1, "fuse": 1, "res": 1}
 DT = {"f16": nv.F16, "i8": nv.I8, "f32": nv.F32}
 
 spec = os.environ.get("NVDB_AB", "f16:mma_fast:1024:10:seed=1;f16:mma_fast:1024:10:seed=0")

@@ -290,3 +290,22 @@ def test_cta_pair_kernel_matches_single_cta_kernel(nv, oracle, k):
             oids, osc = oracle.search_batch(F16, base, None, queries[pick], k)
             for j, qi in enumerate(pick):
                 assert_topk_equal(b[0][qi], b[1][qi], oids[j], osc[j], what=f"pair exact nq={nq} q{qi}")
+
+
+def test_i8_resident_query_limb_equals_streamed_limbs(nv, oracle):
+    """i8 tensor scan with query limb 0 resident in shared memory (default, k <= 16) vs both limbs streamed."""
+    n, d = 50_000, 768
+    rng = np.random.default_rng(4)
+    with nv.FlatIndexCuda.synthetic(I8, n, d, 8) as idx:
+        f = oracle.synth_f32(8, 0, n, d)
+        for nq in (5, 300):
+            queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
+            got = {}
+            for res in (0, 1):
+                idx.set_tuning(nv.capi.TUNE_MMA_RESIDENT, res)
+                for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT):
+                    idx.set_path(path)
+                    got[(res, path)] = idx.search_topk_dot_batch(queries, 10)
+            for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT):
+                a, b = got[(0, path)], got[(1, path)]
+                assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), (path, nq)
