@@ -183,24 +183,32 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   tc::fence_before_thread_sync();
   __syncthreads();
   tc::fence_after_thread_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  // broadcast through a shuffle so that the compiler keeps the TMEM base in a uniform register: a value it cannot
+  // prove warp-uniform costs an ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall around EVERY tcgen05.mma issue
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
-      tma_prefetch_desc(&tmap_a);
-      tma_prefetch_desc(&tmap_b);
+    {
+      if (lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+      }
       const uint64_t pol = l2_policy_evict_first();
       if constexpr (RES) {  // limb 0 of this M-tile: all K chunks, once
-        mbar_arrive_expect_tx(resbar, a.kchunks * L.a_limb_bytes);
-        for (uint32_t kc = 0; kc < a.kchunks; ++kc)
-          tma_load_2d(smem + L.res_off + kc * L.a_limb_bytes, &tmap_a, resbar, (int)(kc * EPC), (int)(m_tile * kBlockM));
+        if (lane == 0) {
+          mbar_arrive_expect_tx(resbar, a.kchunks * L.a_limb_bytes);
+          for (uint32_t kc = 0; kc < a.kchunks; ++kc)
+            tma_load_2d(smem + L.res_off + kc * L.a_limb_bytes, &tmap_a, resbar, (int)(kc * EPC), (int)(m_tile * kBlockM));
+        }
+        __syncwarp();
       }
       uint32_t stage = 0, phase = 0;
       for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P) {
         for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + L.stages_off + stage * L.stage_bytes;
+          if (tc::elect_one_sync()) {
           mbar_arrive_expect_tx(&full[stage], L.stage_bytes);
 #pragma unroll
           for (int l = RES; l < LIMBS; ++l)
@@ -211,6 +219,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             tma_load_2d_hint(sb, &tmap_b, &full[stage], (int)(kc * EPC), (int)(tile * BLOCK_N), pol);
           else
             tma_load_2d(sb, &tmap_b, &full[stage], (int)(kc * EPC), (int)(tile * BLOCK_N));
+          }
+          __syncwarp();
           if (++stage == (uint32_t)a.stages) {
             stage = 0;
             phase ^= 1;
@@ -219,8 +229,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====
+    {
       constexpr uint32_t idesc = kI8 ? tc::idesc_s8_s32(kBlockM, BLOCK_N) : tc::idesc_f16_f32(kBlockM, BLOCK_N);
       uint32_t stage = 0, phase = 0, it = 0;
       if constexpr (RES) {
@@ -237,6 +247,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           tc::fence_after_thread_sync();
           const uint32_t st = smem_u32(smem + L.stages_off + stage * L.stage_bytes);
           const uint64_t bdesc = tc::smem_desc_k128(st + (LIMBS - RES) * L.a_limb_bytes);
+          if (tc::elect_one_sync()) {
 #pragma unroll
           for (int l = 0; l < LIMBS; ++l) {
             const uint64_t adesc = (RES && l == 0) ? tc::smem_desc_k128(res_u32 + kc * L.a_limb_bytes)
@@ -252,12 +263,14 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
           }
           tc::mma_commit(&empty[stage]);  // frees the smem slot when these MMAs have read it
+          if (kc + 1 == a.kchunks) tc::mma_commit(&tfull[buf]);  // accumulator complete -> epilogue
+          }
+          __syncwarp();
           if (++stage == (uint32_t)a.stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tc::mma_commit(&tfull[buf]);  // accumulator complete -> epilogue
       }
     }
   } else {
@@ -269,7 +282,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const bool valid = qg < a.nq;
     ThreadTopK<KREG> top;
     top.init(reinterpret_cast<uint64_t*>(smem + L.lists_off) + ql, a.k);  // smem variant: entry jj at list[jj * 128]
-    float* rscale = reinterpret_cast<float*>(smem + L.rscale_off);          // [2][BLOCK_N] row scales (i8)
+    const uint32_t rscale_u32 = smem_u32(smem + L.rscale_off);              // [2][BLOCK_N] row scales (i8)
     // admission threshold: score of the current k-th best, optionally seeded with the k-th best of an earlier pass over
     // other rows (a valid lower bound of the final k-th best); padding lanes never insert
     float thr = valid ? (a.thr_init ? a.thr_init[qg] : -INFINITY) : INFINITY;
@@ -282,7 +295,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const uint32_t row0 = tile * BLOCK_N;
       if constexpr (kI8) {
         static_assert(!kI8 || BLOCK_N == 128, "one row scale per epilogue thread");
-        rscale[buf * BLOCK_N + et] = (row0 + et < a.n_rows) ? __ldg(a.scales + row0 + et) : 0.f;
+        const float rs_mine = (row0 + et < a.n_rows) ? __ldg(a.scales + row0 + et) : 0.f;
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(rscale_u32 + (buf * BLOCK_N + et) * 4u), "f"(rs_mine) : "memory");
       }
       mbar_wait(&tfull[buf], bphase);
       tc::fence_after_thread_sync();
@@ -296,10 +310,13 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           uint32_t w[32];
           tc::tmem_ld32(lane_addr + buf * kAccColsPerBuf + BLOCK_N + c0, w);
           tc::tmem_ld_wait();
-          const float4* rs4 = reinterpret_cast<const float4*>(rscale + buf * BLOCK_N + c0);
+          const uint32_t rs4 = rscale_u32 + (buf * BLOCK_N + c0) * 4u;
 #pragma unroll
           for (int i4 = 0; i4 < 8; ++i4) {
-            const float4 r = rs4[i4];  // warp-broadcast LDS.128
+            float4 r;  // warp-broadcast LDS.128 (explicit: the aligned smem base has lost its address space)
+            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                         : "r"(rs4 + (uint32_t)i4 * 16u));
             const float rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
             for (int u = 0; u < 4; ++u) {

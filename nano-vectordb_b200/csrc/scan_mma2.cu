@@ -130,25 +130,32 @@ scan_mma2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   tc::fence_before_thread_sync();
   cluster_sync_all();  // barrier inits + TMEM allocation visible to both CTAs before any remote arrive / multicast
   tc::fence_after_thread_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  // broadcast through a shuffle so that the compiler keeps the TMEM base in a uniform register: a value it cannot
+  // prove warp-uniform costs an ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall around EVERY tcgen05.mma issue
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     // ===== TMA producer (both CTAs): own A tile(s) + own half of the base tile; bytes land on the leader's barrier =====
-    if (lane == 0) {
-      tma_prefetch_desc(&tmap_a);
-      tma_prefetch_desc(&tmap_b);
+    {
+      if (lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+      }
       uint32_t stage = 0, phase = 0;
       for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P) {
         for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + L.stages_off + stage * L.stage_bytes;
-          if (leader) mbar_arrive_expect_tx(&full[stage], 2u * L.stage_bytes);
           const uint32_t bar = mapa_shared(smem_u32(&full[stage]), 0);
+          if (tc::elect_one_sync()) {
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2u * L.stage_bytes);
 #pragma unroll
           for (int l = 0; l < LIMBS; ++l)
             tma_load_2d_pair(st + l * L.a_limb_bytes, &tmap_a, bar, (int)(kc * EPC), (int)(l * a.mpad + m_tile * kBlockM));
           tma_load_2d_pair(st + LIMBS * L.a_limb_bytes, &tmap_b, bar, (int)(kc * EPC),
                            (int)(tile * kPairN + rank * kHalfN));
+          }
+          __syncwarp();
           if (++stage == (uint32_t)a.stages) {
             stage = 0;
             phase ^= 1;
@@ -157,8 +164,8 @@ scan_mma2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: one thread of the LEADER CTA drives the tensor cores of both SMs =====
-    if (leader && lane == 0) {
+    // ===== MMA issuer: one elected lane of the LEADER CTA's warp drives the tensor cores of both SMs =====
+    if (leader) {
       constexpr uint32_t idesc = tc::idesc_f16_f32(2 * kBlockM, kPairN);
       uint32_t stage = 0, phase = 0, it = 0;
       for (uint32_t tile = a.tile0 + j; tile < a.num_tiles; tile += a.P, ++it) {
@@ -170,6 +177,7 @@ scan_mma2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           tc::fence_after_thread_sync();
           const uint32_t st = smem_u32(smem + L.stages_off + stage * L.stage_bytes);
           const uint64_t bdesc = tc::smem_desc_k128(st + LIMBS * L.a_limb_bytes);
+          if (tc::elect_one_sync()) {
 #pragma unroll
           for (int l = 0; l < LIMBS; ++l) {
             const uint64_t adesc = tc::smem_desc_k128(st + l * L.a_limb_bytes);
@@ -179,12 +187,14 @@ scan_mma2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                           (uint32_t)(kc > 0 || l > 0 || k4 > 0));
           }
           mma2_commit_both(&empty[stage]);
+          if (kc + 1 == a.kchunks) mma2_commit_both(&tfull[buf]);
+          }
+          __syncwarp();
           if (++stage == (uint32_t)a.stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        mma2_commit_both(&tfull[buf]);
       }
     }
   } else {

@@ -20,27 +20,39 @@ constexpr uint64_t kSentinelKey = ((uint64_t)0x007FFFFFu << 32);  // (ordered(-i
 // <= log2(k) steps (an insertion-sorted list paid k/2 shifts per insert, which dominated the scan at k = 100).
 // Unfilled slots hold the sentinel (smaller than any real key), so the heap needs no size counter.
 // Returns the score of the new k-th best (-inf while the heap still holds sentinels).
-__device__ __noinline__ float heap_insert(uint64_t* list, uint32_t k, uint64_t key, float thr) {
-  if (key <= list[0]) return thr;
+// Lists are addressed as 32-bit shared-window addresses (explicit ld/st.shared: the kernels' 1024-byte-aligned
+// dynamic-smem base has lost its address space, and generic LD.E/ST.E pay the window check on every heap step).
+__device__ __forceinline__ uint64_t lds_u64(uint32_t addr) {
+  uint64_t v;
+  asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u64(uint32_t addr, uint64_t v) {
+  asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+}
+constexpr uint32_t kHeapStride = kBlockM * 8;  // bytes between consecutive entries of one thread's list
+
+__device__ __noinline__ float heap_insert(uint32_t list, uint32_t k, uint64_t key, float thr) {
+  if (key <= lds_u64(list)) return thr;
   uint32_t i = 0;
   for (;;) {
     const uint32_t l = 2 * i + 1;
     if (l >= k) break;
     uint32_t c = l;
-    uint64_t cv = list[l * kBlockM];
+    uint64_t cv = lds_u64(list + l * kHeapStride);
     if (l + 1 < k) {
-      const uint64_t cr = list[(l + 1) * kBlockM];
+      const uint64_t cr = lds_u64(list + (l + 1) * kHeapStride);
       if (cr < cv) {
         cv = cr;
         c = l + 1;
       }
     }
     if (cv >= key) break;
-    list[i * kBlockM] = cv;
+    sts_u64(list + i * kHeapStride, cv);
     i = c;
   }
-  list[i * kBlockM] = key;
-  return key_score(list[0]);
+  sts_u64(list + i * kHeapStride, key);
+  return key_score(lds_u64(list));
 }
 
 // The per-thread top-k container. KREG == 0: min-heap in shared memory (any k that fits; stored UNSORTED — the merge
@@ -74,17 +86,17 @@ struct ThreadTopK {
 };
 template <>
 struct ThreadTopK<0> {
-  uint64_t* list;
+  uint32_t list;  // shared-window address of this thread's entry 0
   uint32_t k;
   __device__ __forceinline__ void init(uint64_t* l, uint32_t k_) {
-    list = l;
+    list = smem_u32(l);
     k = k_;
-    for (uint32_t jj = 0; jj < k; ++jj) list[jj * kBlockM] = kSentinelKey;
+    for (uint32_t jj = 0; jj < k; ++jj) sts_u64(list + jj * kHeapStride, kSentinelKey);
   }
   __device__ __forceinline__ float insert(uint64_t key, float thr) { return heap_insert(list, k, key, thr); }
   __device__ __forceinline__ void store(uint64_t* out) const {
     for (uint32_t jj = 0; jj < k; ++jj) {
-      const uint64_t key = list[jj * kBlockM];
+      const uint64_t key = lds_u64(list + jj * kHeapStride);
       out[jj] = ((uint32_t)key == 0u) ? 0ull : key;
     }
   }

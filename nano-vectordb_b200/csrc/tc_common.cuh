@@ -41,6 +41,14 @@ __host__ __device__ constexpr uint32_t idesc_s8_s32(uint32_t M, uint32_t N) {
 }
 
 // ---- MMA: D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread ---------------------------------------------
+// one lane of a CONVERGED warp. The compiler recognises the elect.sync predicate: tcgen05 instructions under it are
+// issued straight from uniform registers, whereas under an ordinary divergent branch (`if (lane == 0)`) every
+// tcgen05.mma / commit is wrapped in an ELECT / PLOP3 / BRA.U.ANY "once per active thread" loop.
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void mma_f16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                            uint32_t accumulate) {
   asm volatile(
