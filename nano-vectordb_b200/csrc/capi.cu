@@ -38,6 +38,7 @@ struct nvdb_b200_index {
   CUtensorMap tmap;
   // tensor-core scan: base tensor map with box rows = scan_mma_block_n(dtype); query (A operand) tensor map cache
   bool mma_ok = false;
+  CUtensorMap tmap_mma_b64; // box rows 64: the half tile each CTA of an i8 CTA pair loads
   CUtensorMap tmap_mma_b;   // box rows 128 (the streaming scan's `tmap` has 256-row boxes and serves the 256-row tiles)
   CUtensorMap tmap_mma_a;
   const void* tmap_a_ptr = nullptr;
@@ -56,7 +57,7 @@ struct nvdb_b200_index {
   int tune_mma_resident = 1; // i8 tensor scan: query limb 0 resident in shared memory (0: stream both limbs)
   int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
-  int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 auto (k > 16), 2 whenever the shape allows
+  int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 (default) / 2 whenever the shape allows
   std::mutex mu;
   mutable std::string err;
   // optional per-kernel event timing (bench.py's roofline figure)
@@ -169,6 +170,8 @@ int build_tmap(nvdb_b200_index* idx) {
   idx->tma_ok = true;
   if (idx->dtype == kDtF16 || idx->dtype == kDtI8) {
     rc = encode_2d(idx, &idx->tmap_mma_b, idx->dtype, idx->payload, idx->n, idx->dim, 128u);
+    if (rc) return rc;
+    rc = encode_2d(idx, &idx->tmap_mma_b64, idx->dtype, idx->payload, idx->n, idx->dim, 64u);
     if (rc) return rc;
     idx->mma_ok = true;
   }
@@ -597,13 +600,13 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
   int rc = prof_begin(idx, stream, &pev);
   if (rc) return rc;
   // every pass handles up to 128 * num_sms queries; G M-tiles x P CTAs (or CTA pairs) each.
-  // CTA-pair kernel (scan_mma2.cu): f16 bases, an even number of M-tiles, 256-row tiles, P = clusters per pair column.
+  // CTA-pair kernel (scan_mma2.cu): an even number of M-tiles, P = clusters per pair column; f16: 256-row tiles,
+  // i8: 128-row tiles (two limb accumulators), each CTA loading half a tile. The pair halves the base-tile bytes every
+  // SM writes to and reads from shared memory per MMA step; both single-CTA kernels are bound by that shared-memory
+  // traffic, not by the tensor pipe (profiles/README.md). Knob MMA_2CTA: 0 never, 1 / 2 whenever the shape allows.
   int stages2 = 0;
-  // auto (1): only for k > 16 — with register lists the single-CTA kernel already runs at the power-limited tensor rate
-  // (3.39 vs 3.6-3.8 ms at batch 1024), with shared-memory lists it would fall back to 128-row tiles and the pair kernel
-  // wins (k = 100: 6.8 vs 8.2 ms; profiles/r1_ab_round8.jsonl). 2 = whenever the shape allows.
-  const bool pair_ok = idx->dtype == kDtF16 && !dbg && (idx->tune_mma_2cta == 2 || (idx->tune_mma_2cta == 1 && k > 16u)) &&
-                       scan_mma2_plan(limbs, k, idx->max_smem, &stages2);
+  const bool pair_ok = !dbg && idx->tune_mma_2cta != 0 && scan_mma2_plan((int)idx->dtype, limbs, k, idx->max_smem, &stages2);
+  const uint32_t pair_bn = 2u * scan_mma2_half_n((int)idx->dtype);
   struct PassPlan {
     bool pair;
     uint32_t G, P, bn, tiles;
@@ -612,7 +615,7 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
     PassPlan pp;
     pp.G = (nqp + 127u) / 128u;
     pp.pair = pair_ok && pp.G >= 2u && (pp.G % 2u) == 0u;
-    pp.bn = pp.pair ? 256u : block_n;
+    pp.bn = pp.pair ? pair_bn : block_n;
     pp.tiles = (uint32_t)((idx->n + pp.bn - 1) / pp.bn);
     pp.P = pp.pair ? ((uint32_t)idx->num_sms / 2u) / (pp.G / 2u) : (uint32_t)idx->num_sms / pp.G;
     if (pp.P > pp.tiles) pp.P = pp.tiles;
@@ -660,9 +663,10 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
     a.evict_first_base = (a.G == 1);
     a.resident_a = idx->tune_mma_resident;
     a.max_smem = idx->max_smem;
-    const CUtensorMap* tmb = (pp.bn == 256 && !pp.pair) ? &idx->tmap : &idx->tmap_mma_b;
+    const CUtensorMap* tmb = pp.pair ? (idx->dtype == kDtI8 ? &idx->tmap_mma_b64 : &idx->tmap_mma_b)
+                                     : (pp.bn == 256 ? &idx->tmap : &idx->tmap_mma_b);
     auto launch_scan = [&](const MmaArgs& args) {
-      return pp.pair ? scan_mma2_launch(limbs, &idx->tmap_mma_a, tmb, args, stream)
+      return pp.pair ? scan_mma2_launch((int)idx->dtype, limbs, &idx->tmap_mma_a, tmb, args, stream)
                      : scan_mma_launch((int)idx->dtype, limbs, &idx->tmap_mma_a, tmb, args, stream);
     };
     uint64_t* partial = (uint64_t*)idx->d_ws[WS_PARTIAL];

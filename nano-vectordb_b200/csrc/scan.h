@@ -80,7 +80,7 @@ struct MmaArgs {
   uint32_t block_n;      // base rows per tile (template selector; the base tensor map's box rows)
   int stages;
   int evict_first_base;  // base tiles are read once (G == 1): keep them out of L2
-  int resident_a;        // i8: keep query limb 0 resident in shared memory when it fits (tuning knob)
+  int resident_a;        // i8: query limbs resident in shared memory (knob: 0 none, 1 the first, 2 both if they fit — pair kernel)
   int max_smem;          // opt-in shared memory per CTA
 };
 
@@ -111,9 +111,11 @@ cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, c
 cudaError_t row_norm_max_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim, uint32_t* out2,
                                 int num_sms, cudaStream_t stream);
 
-// CTA-pair variant (scan_mma2.cu): f16 only, a.G even, a.P = clusters per pair column, tmap_b with 128-row boxes
-bool scan_mma2_plan(int limbs, uint32_t k, int max_smem, int* stages);
-cudaError_t scan_mma2_launch(int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
+// CTA-pair variant (scan_mma2.cu): a.G even, a.P = clusters per pair column, tmap_b with scan_mma2_half_n(dtype)-row
+// boxes (f16: 128 of a 256-row tile; i8: 64 of a 128-row tile). Tile rows = 2 * scan_mma2_half_n(dtype).
+uint32_t scan_mma2_half_n(int dtype);
+bool scan_mma2_plan(int dtype, int limbs, uint32_t k, int max_smem, int* stages);
+cudaError_t scan_mma2_launch(int dtype, int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
                              cudaStream_t stream);
 
 // reference converters on the device (convert.cu): f32 -> f16 (RNE); f32 | f16 -> i8 + per-row scale

@@ -309,3 +309,34 @@ def test_i8_resident_query_limb_equals_streamed_limbs(nv, oracle):
             for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT):
                 a, b = got[(0, path)], got[(1, path)]
                 assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), (path, nq)
+
+
+@pytest.mark.parametrize("k", [10, 40])
+def test_i8_cta_pair_kernel_matches_single_cta_kernel(nv, oracle, k):
+    """i8 cta_group::2 scan (128-row tiles, two limb accumulators, each CTA loads 64 rows) vs the single-CTA scan:
+    same integer accumulators and the same FP32 combine, so ids and score bits must be identical — with the first query
+    limb resident or streamed, dims with 1 and 6 K-chunks, ragged last tile."""
+    rng = np.random.default_rng(21)
+    for n, d in ((60_001, 128), (20_011, 768)):
+        with nv.FlatIndexCuda.synthetic(I8, n, d, 9) as idx:
+            base, scales = idx.read_rows(0, n)
+            f = oracle.synth_f32(9, 0, n, d)
+            for nq in (256, 130, 1024):   # G = 2, 2 (padded tile), 8
+                queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
+                got = {}
+                for pair, res in ((0, 1), (2, 1), (2, 2), (2, 0)):   # res 1: first limb resident, 2: both, 0: none
+                    idx.set_tuning(nv.capi.TUNE_MMA_2CTA, pair)
+                    idx.set_tuning(nv.capi.TUNE_MMA_RESIDENT, res)
+                    for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT):
+                        idx.set_path(path)
+                        got[(pair, res, path)] = idx.search_topk_dot_batch(queries, k)
+                for path in (nv.PATH_MMA, nv.PATH_MMA_EXACT):
+                    a = got[(0, 1, path)]
+                    for key in ((2, 1, path), (2, 2, path), (2, 0, path)):
+                        b = got[key]
+                        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), (key, nq, n, d)
+                pick = [0, nq // 2, nq - 1]
+                b = got[(2, 1, nv.PATH_MMA_EXACT)]
+                oids, osc = oracle.search_batch(I8, base, scales, queries[pick], k)
+                for j, qi in enumerate(pick):
+                    assert_topk_equal(b[0][qi], b[1][qi], oids[j], osc[j], what=f"i8 pair exact nq={nq} q{qi}")
