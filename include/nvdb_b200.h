@@ -158,6 +158,37 @@ int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, c
                                uint32_t Q, uint32_t R, uint32_t K, uint32_t* out_ids_dev, float* out_dist_dev,
                                void* stream);
 
+/* ---- IVF-PQ candidate generation ---------------------------------------------------------
+ * The stage in front of the refine: replaces the FAISS calls of the reference's apps — build:
+ * apps/nvdb_ivfpq_build.cpp:78-135 (IndexIVFPQ(IndexFlatL2, d, nlist, PQ_M, PQ_BITS, METRIC_L2), train on the first
+ * IVF_TRAIN rows, add all rows); search: apps/nvdb_ivf_eval.cpp:398-408,482 (ivf->nprobe, idx->search(1, q, k_search)).
+ * FAISS is not vendored by the reference and not present here: parity is UNPINNED; the algorithm is the
+ * published IVFADC with residual encoding, checked against oracle/ivfpq_ref.py. OPQ (USE_OPQ=1) is not implemented.
+ * All kernels run on `base`'s device; base rows are read from its device-resident payload (f32 / f16 / i8+scale). */
+typedef struct nvdb_b200_ivfpq nvdb_b200_ivfpq;
+/* pq_bits must be 8; pq_m must divide dim (exit code 2 of nvdb_ivfpq_build); ntrain = 0 -> all rows (the tool's
+ * IVF_TRAIN=200000 default is the caller's); niter <= 0 -> 25 Lloyd iterations. Deterministic for a given seed. */
+int nvdb_b200_ivfpq_build(nvdb_b200_index* base, uint32_t nlist, uint32_t pq_m, uint32_t pq_bits, uint64_t ntrain,
+                          int niter, uint64_t seed, nvdb_b200_ivfpq** out);
+int nvdb_b200_ivfpq_destroy(nvdb_b200_ivfpq* ivf);
+const char* nvdb_b200_ivfpq_last_error(const nvdb_b200_ivfpq* ivf);
+int nvdb_b200_ivfpq_info(const nvdb_b200_ivfpq* ivf, uint64_t* n, uint32_t* dim, uint32_t* nlist, uint32_t* pq_m,
+                         uint64_t* index_bytes);
+/* Trained parameters and inverted lists to the host (any pointer may be NULL): coarse [nlist*dim], codebooks
+ * [pq_m*256*(dim/pq_m)], list_off [nlist+1], ids [n] (row id of every grouped position), codes [n*pq_m] (grouped). */
+int nvdb_b200_ivfpq_export(const nvdb_b200_ivfpq* ivf, float* coarse, float* codebooks, uint32_t* list_off, uint32_t* ids,
+                           uint8_t* codes);
+/* R best candidates per query by ADC distance over the nprobe nearest lists, ordered (distance asc, id asc); unfilled
+ * slots id = 0xFFFFFFFF, dist = 1e30f (what the refine stage skips). 1 <= R <= 2048. out_dist may be NULL. */
+int nvdb_b200_ivfpq_search(nvdb_b200_ivfpq* ivf, const float* queries_host, uint32_t nq, uint32_t nprobe, uint32_t R,
+                           uint32_t* out_ids, float* out_dist);
+int nvdb_b200_ivfpq_search_device(nvdb_b200_ivfpq* ivf, const float* queries_dev, uint32_t nq, uint32_t nprobe, uint32_t R,
+                                  uint32_t* cand_ids_dev, float* cand_dist_dev, void* stream);
+/* candidates -> exact L2 refine against `base` -> k best, with the candidates never leaving the device (the reference
+ * moves them host -> device per batch: src/cuda_refine.cu:926-929). Output as nvdb_b200_refine_l2. */
+int nvdb_b200_ivfpq_search_refine(nvdb_b200_ivfpq* ivf, nvdb_b200_index* base, const float* queries_host, uint32_t nq,
+                                  uint32_t nprobe, uint32_t R, uint32_t k, uint32_t* out_ids, float* out_dist);
+
 /* ---- synthetic data on the device ----------------------------------------------------------------------------
  * Fill caller-owned device buffers with global rows [first_row, first_row+n) of the synthetic generator in
  * `dtype` (payload n*dim elements; scales n floats for i8, else NULL). Asynchronous on `stream`. */

@@ -8,11 +8,11 @@ built library raises.
 The directory name contains a hyphen (it follows the reference's repo name), so import it with
 `importlib.import_module("nano-vectordb_b200")`.
 """
-from .capi import (F16, F32, I8, PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_EXACT, PATH_MMA_FAST, FlatIndexCuda, NvdbError, Timing, launch_count,
+from .capi import (F16, F32, I8, PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_EXACT, PATH_MMA_FAST, FlatIndexCuda, IvfPqIndex, NvdbError, Timing, launch_count,
                    lib, lib_path, merge_topk_device, merge_topk_packed_device, synth_fill_device)
 from . import capi  # noqa: F401
 from .sharded import ShardedFlatIndex, packed_words, shard_rows
 
-__all__ = ["F32", "F16", "I8", "PATH_AUTO", "PATH_GEMV", "PATH_MMA", "PATH_MMA_FAST", "PATH_MMA_EXACT", "FlatIndexCuda", "NvdbError", "Timing",
+__all__ = ["F32", "F16", "I8", "PATH_AUTO", "PATH_GEMV", "PATH_MMA", "PATH_MMA_FAST", "PATH_MMA_EXACT", "FlatIndexCuda", "IvfPqIndex", "NvdbError", "Timing",
            "launch_count", "lib", "lib_path", "merge_topk_device", "merge_topk_packed_device", "synth_fill_device",
            "ShardedFlatIndex", "packed_words", "shard_rows"]

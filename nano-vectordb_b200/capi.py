@@ -64,6 +64,14 @@ _sig = {
     "nvdb_b200_synth_fill_device": (_i, [_i, _u32, _u64, _u32, _u64, _u64, _vp, _vp, _vp]),
     "nvdb_b200_convert": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp]),
     "nvdb_b200_convert_device": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_ivfpq_build": (_i, [_vp, _u32, _u32, _u32, _u64, _i, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_ivfpq_destroy": (_i, [_vp]),
+    "nvdb_b200_ivfpq_last_error": (C.c_char_p, [_vp]),
+    "nvdb_b200_ivfpq_info": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u64)]),
+    "nvdb_b200_ivfpq_export": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "nvdb_b200_ivfpq_search": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp]),
+    "nvdb_b200_ivfpq_search_device": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_ivfpq_search_refine": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
     "nvdb_b200_launch_count": (_u64, []),
     "nvdb_b200_index_profile": (_i, [_vp, _i]),
     "nvdb_b200_index_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_u32)]),
@@ -247,3 +255,66 @@ def search_two_stage(coarse: "FlatIndexCuda", fine: "FlatIndexCuda", queries: np
     _check(lib.nvdb_b200_search_two_stage(coarse._h, fine._h, _ptr(queries), nq, k, R, _ptr(ids), _ptr(sc),
                                           C.byref(timing) if timing is not None else None), coarse._h)
     return ids, sc
+
+
+class IvfPqIndex:
+    """IVF-PQ candidate generator over a device-resident base (reference: FAISS IndexIVFPQ as used by
+    apps/nvdb_ivfpq_build.cpp:78-135 and apps/nvdb_ivf_eval.cpp:398-408,482). Parity unpinned (no FAISS here)."""
+
+    def __init__(self, base: "FlatIndexCuda", nlist=4096, pq_m=48, pq_bits=8, ntrain=200_000, niter=25, seed=1234):
+        h = _vp()
+        st = lib.nvdb_b200_ivfpq_build(base._h, nlist, pq_m, pq_bits, ntrain, niter, seed, C.byref(h))
+        if st != 0:
+            raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(None) or b"").decode())
+        self._h = h
+        self.base = base
+        n, dim, nl, m, nbytes = _u64(), _u32(), _u32(), _u32(), _u64()
+        self._ck(lib.nvdb_b200_ivfpq_info(h, C.byref(n), C.byref(dim), C.byref(nl), C.byref(m), C.byref(nbytes)))
+        self.n, self.dim, self.nlist, self.pq_m, self.index_bytes = n.value, dim.value, nl.value, m.value, nbytes.value
+
+    def _ck(self, st):
+        if st != 0:
+            raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(self._h) or b"").decode())
+
+    def close(self):
+        if self._h:
+            lib.nvdb_b200_ivfpq_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def export(self):
+        """(coarse [nlist,d], codebooks [M,256,dsub], list_off [nlist+1], ids [n], codes [n,M]) as host arrays"""
+        dsub = self.dim // self.pq_m
+        coarse = np.empty((self.nlist, self.dim), np.float32)
+        cb = np.empty((self.pq_m, 256, dsub), np.float32)
+        off = np.empty(self.nlist + 1, np.uint32)
+        ids = np.empty(self.n, np.uint32)
+        codes = np.empty((self.n, self.pq_m), np.uint8)
+        self._ck(lib.nvdb_b200_ivfpq_export(self._h, _ptr(coarse), _ptr(cb), _ptr(off), _ptr(ids), _ptr(codes)))
+        return coarse, cb, off, ids, codes
+
+    def search(self, queries: np.ndarray, nprobe: int, R: int, return_dist=True):
+        """R candidates per query by ADC distance: (ids u32 [nq,R], dist f32 [nq,R]); empty slots 0xFFFFFFFF / 1e30"""
+        queries = np.ascontiguousarray(queries, np.float32).reshape(-1, self.dim)
+        nq = queries.shape[0]
+        ids = np.empty((nq, R), np.uint32)
+        dist = np.empty((nq, R), np.float32) if return_dist else None
+        self._ck(lib.nvdb_b200_ivfpq_search(self._h, _ptr(queries), nq, nprobe, R, _ptr(ids), _ptr(dist)))
+        return ids, dist
+
+    def search_device(self, queries_ptr, nq, nprobe, R, cand_ids_ptr, cand_dist_ptr=None, stream=None):
+        self._ck(lib.nvdb_b200_ivfpq_search_device(self._h, queries_ptr, nq, nprobe, R, cand_ids_ptr, cand_dist_ptr, stream))
+
+    def search_refine(self, queries: np.ndarray, nprobe: int, R: int, k: int):
+        """candidates + exact L2 refine on the device: (ids u32 [nq,k], squared L2 f32 [nq,k]) ascending"""
+        queries = np.ascontiguousarray(queries, np.float32).reshape(-1, self.dim)
+        nq = queries.shape[0]
+        ids = np.empty((nq, k), np.uint32)
+        dist = np.empty((nq, k), np.float32)
+        self._ck(lib.nvdb_b200_ivfpq_search_refine(self._h, self.base._h, _ptr(queries), nq, nprobe, R, k, _ptr(ids), _ptr(dist)))
+        return ids, dist

@@ -1,0 +1,185 @@
+"""IVF-PQ candidate generation on the device against oracle/ivfpq_ref.py.
+
+PARITY UNPINNED (no FAISS in the reference tree or the image, no fixtures for this stage): the oracle restates the
+published IVFADC algorithm in float64. The kernels accumulate in float32 in a fixed order, so the bar is tolerance:
+  * encode: list ids / code bytes equal to the oracle's on the exported parameters except at near-ties
+    (relative distance gap < 1e-5), and there must be few of those;
+  * search: every returned (id, distance) pair matches the oracle's float64 ADC distance of that id within
+    rtol 2e-5, the list is ordered, and no unreturned vector of the probed lists beats the R-th returned distance by
+    more than that tolerance;
+  * training: deterministic for a seed; objective within 5 % of the oracle's Lloyd run from the same initial rows.
+"""
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from _oracle import F16, F32, I8
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent / "oracle"))
+import ivfpq_ref as ref  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+RTOL = 2e-5
+
+
+def clustered(n, d, nclusters, seed, spread=0.35):
+    rng = np.random.default_rng(seed)
+    centers = rng.standard_normal((nclusters, d)).astype(np.float32)
+    x = centers[rng.integers(0, nclusters, n)] + spread * rng.standard_normal((n, d)).astype(np.float32)
+    return np.ascontiguousarray(x, np.float32)
+
+
+def build(nv, x, dtype=F32, **kw):
+    if dtype == F32:
+        base = nv.FlatIndexCuda.from_host(x, None, F32)
+        rows = x
+    elif dtype == F16:
+        h = x.astype(np.float16)
+        base = nv.FlatIndexCuda.from_host(h.view(np.uint16), None, F16)
+        rows = h.astype(np.float32)
+    else:
+        q8, sc = nv.capi.convert(x, F32, I8)
+        base = nv.FlatIndexCuda.from_host(q8, sc, I8)
+        rows = (q8.astype(np.float32) * sc[:, None]).astype(np.float32)
+    return base, rows, nv.IvfPqIndex(base, **kw)
+
+
+@pytest.mark.parametrize("dtype", [F32, F16, I8])
+def test_build_layout_and_encoding_match_oracle(nv, dtype):
+    n, d, nlist, M = 20_000, 48, 64, 8   # dsub = 6, the reference's m=64 / D=384 sub-vector length
+    x = clustered(n, d, 40, 3)
+    base, rows, ivf = build(nv, x, dtype, nlist=nlist, pq_m=M, ntrain=8000, niter=10, seed=5)
+    with base, ivf:
+        assert (ivf.n, ivf.dim, ivf.nlist, ivf.pq_m) == (n, d, nlist, M)
+        coarse, cb, off, ids, codes = ivf.export()
+    assert off[0] == 0 and off[-1] == n and np.all(np.diff(off.astype(np.int64)) >= 0)
+    assert np.array_equal(np.sort(ids), np.arange(n, dtype=np.uint32))
+    lists_gpu = np.empty(n, np.uint32)
+    for l in range(nlist):
+        seg = ids[off[l]:off[l + 1]]
+        assert np.all(np.diff(seg.astype(np.int64)) > 0), "row ids ascend inside a list"
+        lists_gpu[seg] = l
+    codes_gpu = np.empty_like(codes)
+    codes_gpu[ids] = codes
+    lists_ref, codes_ref = ref.encode(rows, coarse, cb)
+    # list ids: mismatches only at near-ties between two centroids
+    bad = np.flatnonzero(lists_gpu != lists_ref)
+    assert len(bad) <= n // 500
+    d2 = ref.sq_dists(rows[bad], coarse) if len(bad) else np.zeros((0, nlist))
+    for j, r in enumerate(bad):
+        a, b = d2[j, lists_gpu[r]], d2[j, lists_ref[r]]
+        assert abs(a - b) <= 1e-5 * max(abs(a), abs(b), 1e-12), (r, a, b)
+    # codes of rows whose list agrees: mismatches only at near-ties between two codewords
+    same = lists_gpu == lists_ref
+    diff = (codes_gpu != codes_ref) & same[:, None]
+    assert diff.sum() <= n * M // 500
+    res = rows - coarse[lists_ref]
+    dsub = d // M
+    for r, m in zip(*np.nonzero(diff)):
+        dd = ref.sq_dists(res[r:r + 1, m * dsub:(m + 1) * dsub], cb[m])[0]
+        a, b = dd[codes_gpu[r, m]], dd[codes_ref[r, m]]
+        assert abs(a - b) <= 1e-5 * max(abs(a), abs(b), 1e-12), (r, m, a, b)
+
+
+def test_training_is_deterministic_and_as_good_as_lloyd(nv):
+    n, d, nlist, M = 12_000, 32, 32, 4
+    x = clustered(n, d, 50, 8)
+    outs = []
+    for _ in range(2):
+        base, rows, ivf = build(nv, x, F32, nlist=nlist, pq_m=M, ntrain=6000, niter=12, seed=77)
+        with base, ivf:
+            outs.append(ivf.export())
+    for a, b in zip(outs[0], outs[1]):
+        assert np.array_equal(a, b), "same seed -> same index, bit for bit"
+    coarse = outs[0][0]
+    want = ref.kmeans(x[:6000], nlist, 12, 77)
+    o_gpu, o_ref = ref.objective(x[:6000], coarse), ref.objective(x[:6000], want)
+    o_init = ref.objective(x[:6000], x[ref.init_rows(6000, nlist, 77)])
+    assert o_gpu <= 1.05 * o_ref and o_gpu < 0.9 * o_init, (o_gpu, o_ref, o_init)
+    # first Lloyd step from the shared initial rows: means agree to float32 accuracy
+    base, rows, ivf1 = build(nv, x, F32, nlist=nlist, pq_m=M, ntrain=6000, niter=1, seed=77)
+    with base, ivf1:
+        c1 = ivf1.export()[0]
+    w1 = ref.kmeans(x[:6000], nlist, 1, 77)
+    assert np.allclose(c1, w1, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("M,nprobe,R", [(8, 1, 10), (8, 8, 50), (16, 64, 256), (12, 5, 1000)])
+def test_search_matches_oracle_adc(nv, M, nprobe, R):
+    n, d, nlist = 30_000, 48, 64
+    x = clustered(n, d, 60, 4)
+    rng = np.random.default_rng(9)
+    queries = np.ascontiguousarray(x[rng.integers(0, n, 24)] + 0.05 * rng.standard_normal((24, d)).astype(np.float32))
+    base, rows, ivf = build(nv, x, F16, nlist=nlist, pq_m=M, ntrain=10_000, niter=8, seed=2)
+    with base, ivf:
+        coarse, cb, off, ids, codes = ivf.export()
+        gi, gd = ivf.search(queries, nprobe, R)
+        gi1, gd1 = ivf.search(queries[:1], nprobe, R)          # batch of one: same answer
+        gi2, _ = ivf.search(queries, nprobe, R, return_dist=False)
+    assert np.array_equal(gi[:1], gi1) and np.array_equal(gd[:1], gd1) and np.array_equal(gi, gi2)
+    for qi, q in enumerate(queries):
+        vid, vd, _ = ref.adc_distances(q, coarse, cb, off, ids, codes, nprobe)
+        truth = dict(zip(vid.tolist(), vd.tolist()))
+        valid = gi[qi] != 0xFFFFFFFF
+        nvalid = int(valid.sum())
+        assert nvalid == min(R, len(vid)), (qi, nvalid, len(vid))
+        assert np.all(valid[:nvalid]) and np.all(gd[qi][nvalid:] == np.float32(1e30))
+        got_ids, got_d = gi[qi][:nvalid], gd[qi][:nvalid].astype(np.float64)
+        assert len(set(got_ids.tolist())) == nvalid
+        want_d = np.array([truth[int(i)] for i in got_ids])        # KeyError = a row outside the probed lists
+        assert np.allclose(got_d, want_d, rtol=RTOL, atol=1e-7), qi
+        assert np.all(np.diff(gd[qi][:nvalid]) >= 0), "ascending distances"
+        same = np.flatnonzero(np.diff(gd[qi][:nvalid]) == 0)
+        assert np.all(got_ids[same] < got_ids[same + 1]), "id ascending inside equal distances"
+        if nvalid < len(vid):   # nothing better was left behind
+            rest = np.setdiff1d(vid, got_ids)
+            best_rest = min(truth[int(i)] for i in rest)
+            assert best_rest >= got_d[-1] * (1 - RTOL) - 1e-7, qi
+
+
+def test_recall_grows_with_nprobe_and_refine_recovers_exact_neighbours(nv):
+    """Shape of the reference's nprobe x REFINE_K surface (Performance.md:673-687): candidate recall rises with nprobe,
+    exact refine of R >= 50 candidates lifts Recall@10 far above the raw ADC ranking, and probing every list with a
+    large R returns the exact neighbours."""
+    n, d, nlist, M, k = 40_000, 64, 128, 16, 10
+    x = clustered(n, d, 300, 6, spread=0.6)
+    rng = np.random.default_rng(1)
+    queries = np.ascontiguousarray(x[rng.integers(0, n, 200)] + 0.2 * rng.standard_normal((200, d)).astype(np.float32))
+    base, rows, ivf = build(nv, x, F16, nlist=nlist, pq_m=M, ntrain=20_000, niter=10, seed=3)
+    truth = ref.exact_l2_topk(rows, queries, k)
+    with base, ivf:
+        raw, refined = [], []
+        for nprobe in (1, 4, 16, 64):
+            ci, _ = ivf.search(queries, nprobe, k)
+            raw.append(ref.recall_at_k(ci, truth))
+            ri, rd = ivf.search_refine(queries, nprobe, 50, k)
+            refined.append(ref.recall_at_k(ri, truth))
+            assert np.all(np.diff(rd, axis=1) >= 0)
+        full_i, full_d = ivf.search_refine(queries, nlist, 1000, k)
+        # refine distances are the exact squared L2 of the returned rows (the refine kernel's own parity tests pin bits)
+        want = ((queries[:, None, :].astype(np.float64) - rows[full_i].astype(np.float64)) ** 2).sum(2)
+        assert np.allclose(full_d, want, rtol=1e-4, atol=1e-5)
+    assert all(b >= a - 0.01 for a, b in zip(raw, raw[1:])), raw
+    assert all(b >= a - 0.01 for a, b in zip(refined, refined[1:])), refined
+    assert refined[-1] > raw[-1] + 0.05 and refined[-1] > 0.9, (raw, refined)
+    assert ref.recall_at_k(full_i, truth) > 0.995
+
+
+def test_argument_errors(nv):
+    x = clustered(3000, 32, 10, 1)
+    with nv.FlatIndexCuda.from_host(x, None, F32) as base:
+        with pytest.raises(nv.NvdbError):
+            nv.IvfPqIndex(base, nlist=16, pq_m=5)          # PQ_M must divide dim (nvdb_ivfpq_build.cpp:54)
+        with pytest.raises(nv.NvdbError):
+            nv.IvfPqIndex(base, nlist=16, pq_m=4, pq_bits=4)
+        with pytest.raises(nv.NvdbError):
+            nv.IvfPqIndex(base, nlist=5000, pq_m=4)        # more lists than training rows
+        with nv.IvfPqIndex(base, nlist=16, pq_m=4, ntrain=0, niter=4) as ivf:
+            with pytest.raises(nv.NvdbError):
+                ivf.search(x[:2], 0, 10)
+            with pytest.raises(nv.NvdbError):
+                ivf.search_refine(x[:2], 4, 10, 20)          # k > R
+            ids, dist = ivf.search(x[:2], 10_000, 5)          # nprobe clamps to nlist
+            assert ids.shape == (2, 5) and np.all(ids != 0xFFFFFFFF)
