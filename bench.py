@@ -473,6 +473,32 @@ def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
         gb = (Q * R * DIM * 2 + Q * DIM * 4 + Q * R * 4 + Q * Kr * 8) / 1e9
         ex["refine_f16_1M_Q10000_R256_K10"] = {"kernel_ms": ms, "us_per_query": ms * 1e3 / Q, "gather_GBps": gb / (ms * 1e-3),
                                                "roofline_frac": gb / (ms * 1e-3) / peak}
+        # the stage in front of it: IVF-PQ candidates from this repo's own index, refine on the
+        # device; reference grid point nlist=4096, m=64, nprobe=64, REFINE_K=50 (Performance.md:673-687). The synthetic
+        # base has no cluster structure, so only build time, latency and throughput are reported here — recall on
+        # structured data is in profiles/r1_ivfpq_1M_*.jsonl (scripts/bench_ivfpq.py).
+        if not args.no_ivfpq:
+            import time as _time
+            t0 = _time.perf_counter()
+            ivf = nv.IvfPqIndex(idxr, nlist=4096, pq_m=64, ntrain=200_000, niter=10, seed=SEED)
+            build_s = _time.perf_counter() - t0
+            qh = qs[:1000].cpu().numpy()
+            for _ in range(3):
+                ivf.search_refine(qh[:1], 64, 50, Kr)
+                ivf.search_refine(qh, 64, 50, Kr)
+            t0 = _time.perf_counter()
+            for i in range(200):
+                ivf.search_refine(qh[i:i + 1], 64, 50, Kr)
+            lat_ms = (_time.perf_counter() - t0) * 1e3 / 200
+            t0 = _time.perf_counter()
+            for _ in range(5):
+                ivf.search_refine(qh, 64, 50, Kr)
+            b_ms = (_time.perf_counter() - t0) * 1e3 / 5
+            ex["ivfpq_1M_nlist4096_m64_nprobe64_R50_K10"] = {
+                "build_s_niter10": build_s, "index_MB": ivf.index_bytes / 1e6, "e2e_latency_ms_per_query": lat_ms,
+                "e2e_batch1000_ms": b_ms, "e2e_batch_qps": 1000 / b_ms * 1e3,
+                "note": "host buffers in/out; candidates never leave the device; parity unpinned (no FAISS)"}
+            ivf.close()
     # bandwidth-bound streaming scans of the other dtypes / k before any tensor sweep
     idx16.set_path(nv.PATH_GEMV)
     ms, kms = _time_search(torch, idx16, stream, q_dev, 1, 100, iters=20)
@@ -509,6 +535,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extras", action="store_true", help="skip the other configs (int8 / fp32 / batch sweep / refine)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-ivfpq", action="store_true", help="skip the IVF-PQ extra (index build ~2 s)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

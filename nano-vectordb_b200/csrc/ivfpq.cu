@@ -9,10 +9,10 @@
 //   build : coarse k-means (nlist centroids) on the first ntrain rows; PQ codebooks (M sub-spaces x 256 codewords)
 //           by k-means on the training residuals x - c(x); every row -> (list, M code bytes); rows grouped by list
 //           (stable: ascending row id inside a list).
-//   search: per query the nprobe nearest centroids; per (query, probed list) one CTA builds the M x 256 look-up table
-//           of squared sub-distances between the query residual q - c and the codewords in shared memory, streams the
-//           list's codes (M byte look-ups + adds per vector, fixed m order) through the CTA top-R selector
-//           (topk_select.cuh); the nprobe lists are merged (topk_merge.cu) into R candidates ordered by
+//   search: per query the nprobe nearest centroids; a CTA per (query, group of probed lists) builds the M x 256 table
+//           of inner products q_m . codeword in shared memory and streams its lists' codes (M byte look-ups + adds
+//           per vector, fixed m order; distance = |q|^2 - 2 q.c + |y|^2 - 2 sum) through the CTA top-R selector
+//           (topk_select.cuh); the groups are merged (topk_merge.cu) into R candidates ordered by
 //           (distance asc, id asc). Candidates stay on the device for nvdb_b200_refine_l2_device.
 //
 // Checked against oracle/ivfpq_ref.py (numpy restatement fed with the trained parameters exported from here).
@@ -41,6 +41,7 @@ struct nvdb_b200_ivfpq {
   float* cb_hn = nullptr;      // [M x 256]
   uint8_t* codes = nullptr;    // [n x M], grouped by list
   uint32_t* ids = nullptr;     // [n] row id of every grouped position
+  float* rnorm = nullptr;      // [n] |c + reconstruction|^2 of every grouped position
   uint32_t* list_off = nullptr;  // [nlist + 1]
   cudaStream_t stream = nullptr;
   // grow-only search workspaces
@@ -142,16 +143,19 @@ __global__ void gather_codes_kernel(const uint8_t* __restrict__ src, const uint3
 // ---- search kernels ----------------------------------------------------------------------------------------------
 
 // probes[q][0..nprobe) = the nprobe best-scoring lists of query q (score desc == L2 asc, id asc among equals)
-__global__ void __launch_bounds__(256)
+constexpr int kProbeThreads = 1024;
+__global__ void __launch_bounds__(kProbeThreads)
 select_probes_kernel(const float* __restrict__ scores, uint32_t nlist, uint32_t bufn, uint32_t nprobe,
                      uint32_t* __restrict__ probes) {
   extern __shared__ uint64_t pk[];
   const uint32_t q = blockIdx.x, tid = threadIdx.x;
-  for (uint32_t j = tid; j < bufn; j += 256) pk[j] = j < nlist ? make_key(scores[(size_t)q * nlist + j], j) : 0ull;
+  for (uint32_t j = tid; j < bufn; j += kProbeThreads)
+    pk[j] = j < nlist ? make_key(scores[(size_t)q * nlist + j], j) : 0ull;
   __syncthreads();
   auto sync = [] { __syncthreads(); };
-  bitonic_sort_desc(pk, bufn, tid, 256, sync);
-  for (uint32_t p = tid; p < nprobe; p += 256) probes[(size_t)q * nprobe + p] = pk[p] ? key_row(pk[p]) : 0xFFFFFFFFu;
+  bitonic_sort_desc(pk, bufn, tid, kProbeThreads, sync);
+  for (uint32_t p = tid; p < nprobe; p += kProbeThreads)
+    probes[(size_t)q * nprobe + p] = pk[p] ? key_row(pk[p]) : 0xFFFFFFFFu;
 }
 
 constexpr int kScanThreads = 256;
@@ -162,73 +166,137 @@ struct IvfScanArgs {
   const float* codebooks; // [M x 256 x dsub]
   const uint8_t* codes;
   const uint32_t* ids;
+  const float* rnorm;     // [n] |c + reconstruction|^2 of every grouped position
   const uint32_t* list_off;
   const uint32_t* probes; // [nq x nprobe]
-  uint64_t* partial;      // [nq x nprobe x R] ordered keys (score = -distance)
-  uint32_t d, M, dsub, nprobe, R, cap;
+  uint64_t* partial;      // [nq x G x R] ordered keys (score = -distance)
+  uint32_t d, M, dsub, nprobe, R, cap, G;
 };
 
-// one CTA per (probe, query): LUT in shared memory, then the list's codes through the top-R selector
+// sum over the CTA in a fixed order (shuffle tree per warp, then the 8 warp sums left to right): every thread returns
+// the same bits, independent of the batch the query came in
+__device__ __forceinline__ float block_sum(float v, float* red, uint32_t tid) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, off));
+  __syncthreads();
+  if ((tid & 31u) == 0) red[tid >> 5] = v;
+  __syncthreads();
+  float s = 0.f;
+#pragma unroll
+  for (int w = 0; w < kScanThreads / 32; ++w) s = __fadd_rn(s, red[w]);
+  return s;
+}
+
+// One CTA per (probe group g, query q). ADC distance of a stored vector y = c + reconstruction:
+//   |q - y|^2 = |q|^2 - 2 q.c + |y|^2 - 2 sum_m q_m . codeword_m[code_m]
+// so the look-up table T[m][j] = q_m . codeword_m[j] depends on the query only: it is built once per CTA and serves all
+// the lists of the group (p = g, g + G, ...); |y|^2 is stored per vector at build time, q.c is one block reduction per
+// list. (A table of squared residual sub-distances would have to be rebuilt for every probed list: M x 256 x dsub
+// codebook reads per (query, probe) — measured 14 ms for 1000 queries x 64 probes, profiles/r1_ivfpq_1M_v1.jsonl.)
 __global__ void __launch_bounds__(kScanThreads) ivfpq_scan_kernel(const IvfScanArgs a) {
   extern __shared__ __align__(16) uint8_t sm[];
   float* lut = reinterpret_cast<float*>(sm);                    // [M x 256]
-  float* res = lut + (size_t)a.M * 256;                         // [d]
-  uint64_t* keys = reinterpret_cast<uint64_t*>(res + ((a.d + 3u) & ~3u));  // [cap]
+  float* qv = lut + (size_t)a.M * 256;                          // [d]
+  uint64_t* keys = reinterpret_cast<uint64_t*>(qv + ((a.d + 3u) & ~3u));  // [cap]
   uint32_t* cnt = reinterpret_cast<uint32_t*>(keys + a.cap);
   float* thr = reinterpret_cast<float*>(cnt + 1);
-  const uint32_t tid = threadIdx.x, p = blockIdx.x, q = blockIdx.y;
+  float* red = thr + 1;                                         // [8]
+  const uint32_t tid = threadIdx.x, g = blockIdx.x, q = blockIdx.y;
   auto sync = [] { __syncthreads(); };
   TopKSelect<1> sel;
   sel.init(keys, cnt, thr, a.cap, a.R, tid);
-  uint64_t* out = a.partial + ((size_t)q * a.nprobe + p) * a.R;
-  const uint32_t list = a.probes[(size_t)q * a.nprobe + p];
-  if (list == 0xFFFFFFFFu) {  // nprobe > nlist
-    for (uint32_t j = tid; j < a.R; j += kScanThreads) out[j] = 0ull;
-    return;
+  float qpart = 0.f;
+  for (uint32_t t = tid; t < a.d; t += kScanThreads) {
+    const float v = a.queries[(size_t)q * a.d + t];
+    qv[t] = v;
+    qpart = __fmaf_rn(v, v, qpart);
   }
-  for (uint32_t t = tid; t < a.d; t += kScanThreads)
-    res[t] = __fsub_rn(a.queries[(size_t)q * a.d + t], a.coarse[(size_t)list * a.d + t]);
-  __syncthreads();
-  // look-up table: thread j owns codeword j of every sub-space
-  for (uint32_t m = 0; m < a.M; ++m) {
-    const float* cw = a.codebooks + ((size_t)m * 256 + tid) * a.dsub;
-    const float* r = res + m * a.dsub;
-    float s = 0.f;
-    for (uint32_t t = 0; t < a.dsub; ++t) {
-      const float df = __fsub_rn(r[t], cw[t]);
-      s = __fmaf_rn(df, df, s);
-    }
-    lut[m * 256 + tid] = s;
-  }
-  __syncthreads();
-  const uint32_t begin = a.list_off[list], end = a.list_off[list + 1];
-  const bool vec16 = (a.M & 15u) == 0;
-  for (uint32_t base = begin; base < end; base += kScanThreads) {
-    const uint32_t i = base + tid;
-    bool pushed = false;
-    if (i < end) {
-      const uint8_t* code = a.codes + (size_t)i * a.M;
-      float dist = 0.f;
-      if (vec16) {
-        for (uint32_t m0 = 0; m0 < a.M; m0 += 16) {
-          const uint4 w = *reinterpret_cast<const uint4*>(code + m0);
-          const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-          for (int u = 0; u < 16; ++u)
-            dist = __fadd_rn(dist, lut[(m0 + u) * 256 + ((ww[u >> 2] >> ((u & 3) * 8)) & 0xFFu)]);
-        }
-      } else {
-        for (uint32_t m = 0; m < a.M; ++m) dist = __fadd_rn(dist, lut[m * 256 + code[m]]);
+  const float qq = block_sum(qpart, red, tid);  // (its barriers also publish qv and the selector state)
+  // thread j owns codeword j of every sub-space. The table build is pure load latency (M x dsub codebook words per
+  // thread from L2), so sub-spaces are unrolled 4 deep with 16-byte loads to keep ~12 requests per thread in flight.
+  if ((a.dsub & 3u) == 0) {
+    const uint32_t v4 = a.dsub >> 2;
+#pragma unroll 4
+    for (uint32_t m = 0; m < a.M; ++m) {
+      const float4* cw = reinterpret_cast<const float4*>(a.codebooks + ((size_t)m * 256 + tid) * a.dsub);
+      const float* qm = qv + m * a.dsub;
+      float s = 0.f;
+      for (uint32_t t = 0; t < v4; ++t) {
+        const float4 w = __ldg(cw + t);
+        s = __fmaf_rn(qm[4 * t + 0], w.x, s);
+        s = __fmaf_rn(qm[4 * t + 1], w.y, s);
+        s = __fmaf_rn(qm[4 * t + 2], w.z, s);
+        s = __fmaf_rn(qm[4 * t + 3], w.w, s);
       }
-      const float score = -dist;
-      if (score >= thr[0]) pushed = sel.offer(0, score, a.ids[i]);
+      lut[m * 256 + tid] = s;
     }
-    const uint32_t pushed_threads = (uint32_t)__syncthreads_count(pushed);
-    sel.end_tile(pushed_threads, kScanThreads, tid, kScanThreads, sync);
+  } else {
+#pragma unroll 4
+    for (uint32_t m = 0; m < a.M; ++m) {
+      const float* cw = a.codebooks + ((size_t)m * 256 + tid) * a.dsub;
+      const float* qm = qv + m * a.dsub;
+      float s = 0.f;
+      for (uint32_t t = 0; t < a.dsub; ++t) s = __fmaf_rn(qm[t], __ldg(cw + t), s);
+      lut[m * 256 + tid] = s;
+    }
+  }
+  __syncthreads();
+  const bool vec16 = (a.M & 15u) == 0;
+  for (uint32_t p = g; p < a.nprobe; p += a.G) {
+    const uint32_t list = a.probes[(size_t)q * a.nprobe + p];
+    if (list == 0xFFFFFFFFu) continue;  // nprobe > nlist (uniform over the CTA)
+    float cpart = 0.f;
+    for (uint32_t t = tid; t < a.d; t += kScanThreads) cpart = __fmaf_rn(qv[t], a.coarse[(size_t)list * a.d + t], cpart);
+    const float qc = block_sum(cpart, red, tid);
+    const float base_term = __fmaf_rn(-2.f, qc, qq);
+    const uint32_t begin = a.list_off[list], end = a.list_off[list + 1];
+    for (uint32_t base = begin; base < end; base += kScanThreads) {
+      const uint32_t i = base + tid;
+      bool pushed = false;
+      if (i < end) {
+        const uint8_t* code = a.codes + (size_t)i * a.M;
+        float acc = 0.f;
+        if (vec16) {
+          for (uint32_t m0 = 0; m0 < a.M; m0 += 16) {
+            const uint4 w = *reinterpret_cast<const uint4*>(code + m0);
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int u = 0; u < 16; ++u)
+              acc = __fadd_rn(acc, lut[(m0 + u) * 256 + ((ww[u >> 2] >> ((u & 3) * 8)) & 0xFFu)]);
+          }
+        } else {
+          for (uint32_t m = 0; m < a.M; ++m) acc = __fadd_rn(acc, lut[m * 256 + code[m]]);
+        }
+        const float dist = __fmaf_rn(-2.f, acc, __fadd_rn(base_term, a.rnorm[i]));
+        const float score = -dist;
+        if (score >= thr[0]) pushed = sel.offer(0, score, a.ids[i]);
+      }
+      const uint32_t pushed_threads = (uint32_t)__syncthreads_count(pushed);
+      sel.end_tile(pushed_threads, kScanThreads, tid, kScanThreads, sync);
+    }
   }
   __syncthreads();
   sel.compact(tid, kScanThreads, sync);
+  uint64_t* out = a.partial + ((size_t)q * a.G + g) * a.R;
   for (uint32_t j = tid; j < a.R; j += kScanThreads) out[j] = j < cnt[0] ? keys[j] : 0ull;
+}
+
+// |c_list + reconstruction|^2 of every grouped position (thread per vector, fixed order)
+__global__ void recon_norms_kernel(const uint8_t* __restrict__ codes, const uint32_t* __restrict__ sorted_lists,
+                                   const float* __restrict__ coarse, const float* __restrict__ codebooks, uint32_t n, uint32_t d,
+                                   uint32_t M, uint32_t dsub, float* __restrict__ rnorm) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* c = coarse + (size_t)sorted_lists[i] * d;
+  float s = 0.f;
+  for (uint32_t m = 0; m < M; ++m) {
+    const float* cw = codebooks + ((size_t)m * 256 + codes[(size_t)i * M + m]) * dsub;
+    for (uint32_t t = 0; t < dsub; ++t) {
+      const float v = __fadd_rn(c[m * dsub + t], cw[t]);
+      s = __fmaf_rn(v, v, s);
+    }
+  }
+  rnorm[i] = s;
 }
 
 // merged (u64 id, score = -dist) -> (u32 id, dist); empty slots as the refine kernel expects them
@@ -257,6 +325,7 @@ void ivf_free(nvdb_b200_ivfpq* h) {
   cudaFree(h->cb_hn);
   cudaFree(h->codes);
   cudaFree(h->ids);
+  cudaFree(h->rnorm);
   cudaFree(h->list_off);
   for (void* w : h->ws) cudaFree(w);
   if (h->h_pin) cudaFreeHost(h->h_pin);
@@ -284,6 +353,7 @@ int build_impl(nvdb_b200_ivfpq* h, const void* payload, const float* scales, uin
   ICK(cudaMalloc(&h->cb_hn, (size_t)M * 256 * 4), "cudaMalloc codebook norms");
   ICK(cudaMalloc(&h->codes, (size_t)n * M), "cudaMalloc codes");
   ICK(cudaMalloc(&h->ids, (size_t)n * 4), "cudaMalloc ids");
+  ICK(cudaMalloc(&h->rnorm, (size_t)n * 4), "cudaMalloc reconstruction norms");
   ICK(cudaMalloc(&h->list_off, (size_t)(nlist + 1) * 4), "cudaMalloc list offsets");
 
   const uint32_t chunk = 131072;
@@ -351,7 +421,9 @@ int build_impl(nvdb_b200_ivfpq* h, const void* payload, const float* scales, uin
       "radix sort");
   list_offsets_kernel<<<(nlist + 1 + 255) / 256, 256, 0, st>>>(sorted_lists.as<uint32_t>(), n, nlist, h->list_off);
   gather_codes_kernel<<<fill_grid, 256, 0, st>>>(codes_tmp.as<uint8_t>(), h->ids, n, M, h->codes);
-  count_launch(2);
+  recon_norms_kernel<<<(n + 255) / 256, 256, 0, st>>>(h->codes, sorted_lists.as<uint32_t>(), h->coarse, h->codebooks, n, d, M,
+                                                      dsub, h->rnorm);
+  count_launch(3);
   ICK(cudaGetLastError(), "ivfpq build kernels");
   ICK(cudaStreamSynchronize(st), "ivfpq build");
   return NVDB_B200_OK;
@@ -368,7 +440,13 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   int rc;
   if ((rc = iws(h, IWS_SCORES, (size_t)nq * h->nlist * 4))) return rc;
   if ((rc = iws(h, IWS_PROBES, (size_t)nq * nprobe * 4))) return rc;
-  if ((rc = iws(h, IWS_PARTIAL, (size_t)nq * nprobe * R * 8))) return rc;
+  // probe groups per query: enough CTAs to fill the machine for a few queries, one CTA per query for big batches
+  uint32_t G = ((uint32_t)h->num_sms * 2u + nq - 1u) / nq;
+  if (G > nprobe) G = nprobe;
+  const uint32_t g_merge = 4096u / R > 8u ? 4096u / R : 8u;  // one CTA merges G x R keys per query: keep that a few thousand
+  if (G > g_merge) G = g_merge;
+  if (G < 1u) G = 1u;
+  if ((rc = iws(h, IWS_PARTIAL, (size_t)nq * G * R * 8))) return rc;
   if ((rc = iws(h, IWS_IDS64, (size_t)nq * R * 8))) return rc;
   if ((rc = iws(h, IWS_SC, (size_t)nq * R * 4))) return rc;
   float* scores = (float*)h->ws[IWS_SCORES];
@@ -376,7 +454,7 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   ICK(dot_bias_scores_launch(dq, h->d, nq, h->coarse, h->d, h->coarse_hn, h->nlist, h->d, scores, st), "coarse scores");
   if ((size_t)bufn * 8 > 48u * 1024u)
     ICK(cudaFuncSetAttribute(select_probes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bufn * 8)), "smem attr");
-  select_probes_kernel<<<nq, 256, (size_t)bufn * 8, st>>>(scores, h->nlist, bufn, nprobe, probes);
+  select_probes_kernel<<<nq, kProbeThreads, (size_t)bufn * 8, st>>>(scores, h->nlist, bufn, nprobe, probes);
   count_launch();
   IvfScanArgs a;
   a.queries = dq;
@@ -384,6 +462,8 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   a.codebooks = h->codebooks;
   a.codes = h->codes;
   a.ids = h->ids;
+  a.rnorm = h->rnorm;
+  a.G = G;
   a.list_off = h->list_off;
   a.probes = probes;
   a.partial = (uint64_t*)h->ws[IWS_PARTIAL];
@@ -393,7 +473,7 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   a.nprobe = nprobe;
   a.R = R;
   a.cap = next_pow2(R + kScanThreads);
-  const size_t smem = (size_t)h->M * 1024 + (size_t)((h->d + 3u) & ~3u) * 4 + (size_t)a.cap * 8 + 16;
+  const size_t smem = (size_t)h->M * 1024 + (size_t)((h->d + 3u) & ~3u) * 4 + (size_t)a.cap * 8 + 8 + 32 + 8;
   if (smem > (size_t)h->max_smem) return ifail(h, NVDB_B200_ERR_UNSUPPORTED, "PQ look-up table does not fit shared memory");
   ICK(cudaFuncSetAttribute(ivfpq_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr");
   for (uint32_t q0 = 0; q0 < nq; q0 += 65535u) {  // grid.y limit
@@ -401,11 +481,11 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
     IvfScanArgs b = a;
     b.queries = dq + (size_t)q0 * h->d;
     b.probes = probes + (size_t)q0 * nprobe;
-    b.partial = a.partial + (size_t)q0 * nprobe * R;
-    ivfpq_scan_kernel<<<dim3(nprobe, nqp), kScanThreads, smem, st>>>(b);
+    b.partial = a.partial + (size_t)q0 * G * R;
+    ivfpq_scan_kernel<<<dim3(G, nqp), kScanThreads, smem, st>>>(b);
     count_launch();
   }
-  ICK(merge_partials_launch(a.partial, nprobe, nq, R, 0, (uint64_t*)h->ws[IWS_IDS64], (float*)h->ws[IWS_SC], st),
+  ICK(merge_partials_launch(a.partial, G, nq, R, 0, (uint64_t*)h->ws[IWS_IDS64], (float*)h->ws[IWS_SC], st),
       "candidate merge");
   const size_t total = (size_t)nq * R;
   finalize_candidates_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const uint64_t*)h->ws[IWS_IDS64],
@@ -493,7 +573,7 @@ int nvdb_b200_ivfpq_info(const nvdb_b200_ivfpq* h, uint64_t* n, uint32_t* dim, u
   if (nlist) *nlist = h->nlist;
   if (pq_m) *pq_m = h->M;
   if (index_bytes)
-    *index_bytes = (uint64_t)h->nlist * h->d * 4 + (uint64_t)h->M * 256 * h->dsub * 4 + h->n * h->M + h->n * 4 +
+    *index_bytes = (uint64_t)h->nlist * h->d * 4 + (uint64_t)h->M * 256 * h->dsub * 4 + h->n * h->M + h->n * 8 +
                    (uint64_t)(h->nlist + 1) * 4;
   return NVDB_B200_OK;
 }
@@ -530,13 +610,18 @@ int nvdb_b200_ivfpq_search(nvdb_b200_ivfpq* h, const float* queries_host, uint32
   if ((rc = iws(h, IWS_Q, qb))) return rc;
   if ((rc = iws(h, IWS_CAND, ob))) return rc;
   if ((rc = iws(h, IWS_OUT, ob))) return rc;
-  ICK(cudaMemcpyAsync(h->ws[IWS_Q], queries_host, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
+  if ((rc = pin(h, qb + 2 * ob))) return rc;
+  memcpy(h->h_pin, queries_host, qb);  // pinned staging: asynchronous copies, one sync per call
+  ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
   if ((rc = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND],
                                out_dist ? (float*)h->ws[IWS_OUT] : nullptr, h->stream)))
     return rc;
-  ICK(cudaMemcpyAsync(out_ids, h->ws[IWS_CAND], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate ids");
-  if (out_dist) ICK(cudaMemcpyAsync(out_dist, h->ws[IWS_OUT], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate distances");
+  uint8_t* hp = (uint8_t*)h->h_pin + qb;
+  ICK(cudaMemcpyAsync(hp, h->ws[IWS_CAND], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate ids");
+  if (out_dist) ICK(cudaMemcpyAsync(hp + ob, h->ws[IWS_OUT], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate distances");
   ICK(cudaStreamSynchronize(h->stream), "ivfpq search");
+  memcpy(out_ids, hp, ob);
+  if (out_dist) memcpy(out_dist, hp + ob, ob);
   return NVDB_B200_OK;
 }
 

@@ -142,6 +142,33 @@ dot_bias_kernel(const float* __restrict__ x, size_t ldx, uint32_t n, const float
   }
 }
 
+// few points (queries): a CTA takes 32 centroids x up to 8 points; thread (centroid, point) runs the SAME sequential
+// fmaf chain over the dimensions as the tile kernel above, so a query scores bit-identically in a batch of 1 or 1000.
+constexpr int kSmallN = 8;
+__global__ void __launch_bounds__(256)
+dot_bias_small_kernel(const float* __restrict__ x, size_t ldx, uint32_t n, const float* __restrict__ c, size_t ldc,
+                      const float* __restrict__ hn, uint32_t k, uint32_t d, float* __restrict__ scores) {
+  extern __shared__ float xs[];  // [n][d]
+  __shared__ float cs[32][33];
+  const uint32_t tid = threadIdx.x, cj = tid & 31u, qi = tid >> 5, j0 = blockIdx.x * 32u;
+  for (uint32_t e = tid; e < n * d; e += 256) xs[e] = x[(size_t)(e / d) * ldx + (e % d)];
+  float acc = 0.f;
+  for (uint32_t k0 = 0; k0 < d; k0 += 32) {
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t r = qi + 8u * u, col = k0 + cj;
+      cs[r][cj] = (j0 + r < k && col < d) ? c[(size_t)(j0 + r) * ldc + col] : 0.f;
+    }
+    __syncthreads();
+    if (qi < n) {
+      const uint32_t lim = min(32u, d - k0);
+      for (uint32_t t = 0; t < lim; ++t) acc = __fmaf_rn(xs[qi * d + k0 + t], cs[cj][t], acc);
+    }
+  }
+  if (qi < n && j0 + cj < k) scores[(size_t)qi * k + j0 + cj] = __fsub_rn(acc, hn[j0 + cj]);
+}
+
 __global__ void argmax_splits_kernel(const float* __restrict__ best_s, const uint32_t* __restrict__ best_j, uint32_t n,
                                      uint32_t splits, uint32_t* __restrict__ assign) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -285,6 +312,11 @@ cudaError_t half_norms_launch(const float* c, size_t ldc, uint32_t k, uint32_t d
 cudaError_t dot_bias_scores_launch(const float* x, size_t ldx, uint32_t n, const float* c, size_t ldc, const float* hn,
                                    uint32_t k, uint32_t d, float* scores, cudaStream_t stream) {
   if (n == 0 || k == 0) return cudaSuccess;
+  if (n <= (uint32_t)kSmallN && (size_t)n * d * 4 <= 48u * 1024u) {
+    dot_bias_small_kernel<<<(k + 31u) / 32u, 256, (size_t)n * d * 4, stream>>>(x, ldx, n, c, ldc, hn, k, d, scores);
+    count_launch();
+    return cudaGetLastError();
+  }
   // a few CTAs per point tile so that a handful of queries still spreads over the SMs
   const uint32_t col_tiles = (k + BN - 1) / BN;
   const uint32_t row_tiles = (n + BM - 1) / BM;

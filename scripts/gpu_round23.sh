@@ -1,0 +1,7 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_ivfpq.py -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -30 gpurun_out/pytest_gpu.log
+timeout 1700 python scripts/bench_ivfpq.py > gpurun_out/ivfpq_1M.jsonl 2> gpurun_out/ivfpq_1M.err; echo "rc=$?"
+cut -c1-330 gpurun_out/ivfpq_1M.jsonl; tail -5 gpurun_out/ivfpq_1M.err
+echo done
