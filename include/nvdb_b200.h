@@ -178,6 +178,12 @@ int nvdb_b200_ivfpq_info(const nvdb_b200_ivfpq* ivf, uint64_t* n, uint32_t* dim,
  * [pq_m*256*(dim/pq_m)], list_off [nlist+1], ids [n] (row id of every grouped position), codes [n*pq_m] (grouped). */
 int nvdb_b200_ivfpq_export(const nvdb_b200_ivfpq* ivf, float* coarse, float* codebooks, uint32_t* list_off, uint32_t* ids,
                            uint8_t* codes);
+/* The inverse of export: an index from host arrays (e.g. loaded from a file the caller wrote from an export, or trained
+ * elsewhere). Rows are NOT re-encoded; list_off must ascend from 0 to n. This is how an index is saved and re-loaded:
+ * the reference's faiss::write_index / read_index file format belongs to FAISS and is not reproduced. */
+int nvdb_b200_ivfpq_import(int device, uint32_t dim, uint32_t nlist, uint32_t pq_m, uint64_t n, const float* coarse,
+                           const float* codebooks, const uint32_t* list_off, const uint32_t* ids, const uint8_t* codes,
+                           nvdb_b200_ivfpq** out);
 /* R best candidates per query by ADC distance over the nprobe nearest lists, ordered (distance asc, id asc); unfilled
  * slots id = 0xFFFFFFFF, dist = 1e30f (what the refine stage skips). 1 <= R <= 2048. out_dist may be NULL. */
 int nvdb_b200_ivfpq_search(nvdb_b200_ivfpq* ivf, const float* queries_host, uint32_t nq, uint32_t nprobe, uint32_t R,

@@ -69,6 +69,7 @@ _sig = {
     "nvdb_b200_ivfpq_last_error": (C.c_char_p, [_vp]),
     "nvdb_b200_ivfpq_info": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u64)]),
     "nvdb_b200_ivfpq_export": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "nvdb_b200_ivfpq_import": (_i, [_i, _u32, _u32, _u32, _u64, _vp, _vp, _vp, _vp, _vp, C.POINTER(_vp)]),
     "nvdb_b200_ivfpq_search": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp]),
     "nvdb_b200_ivfpq_search_device": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_ivfpq_search_refine": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
@@ -261,13 +262,35 @@ class IvfPqIndex:
     """IVF-PQ candidate generator over a device-resident base (reference: FAISS IndexIVFPQ as used by
     apps/nvdb_ivfpq_build.cpp:78-135 and apps/nvdb_ivf_eval.cpp:398-408,482). Parity unpinned (no FAISS here)."""
 
-    def __init__(self, base: "FlatIndexCuda", nlist=4096, pq_m=48, pq_bits=8, ntrain=200_000, niter=25, seed=1234):
-        h = _vp()
-        st = lib.nvdb_b200_ivfpq_build(base._h, nlist, pq_m, pq_bits, ntrain, niter, seed, C.byref(h))
-        if st != 0:
-            raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(None) or b"").decode())
+    def __init__(self, base: "FlatIndexCuda", nlist=4096, pq_m=48, pq_bits=8, ntrain=200_000, niter=25, seed=1234, _handle=None):
+        h = _handle
+        if h is None:
+            h = _vp()
+            st = lib.nvdb_b200_ivfpq_build(base._h, nlist, pq_m, pq_bits, ntrain, niter, seed, C.byref(h))
+            if st != 0:
+                raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(None) or b"").decode())
         self._h = h
         self.base = base
+        self._fill_info()
+
+    @classmethod
+    def from_arrays(cls, base, coarse, codebooks, list_off, ids, codes, device=0):
+        """index from exported / externally trained parameters (nvdb_b200_ivfpq_import); `base` is only used by search_refine"""
+        coarse = np.ascontiguousarray(coarse, np.float32)
+        codebooks = np.ascontiguousarray(codebooks, np.float32)
+        list_off = np.ascontiguousarray(list_off, np.uint32)
+        ids = np.ascontiguousarray(ids, np.uint32)
+        codes = np.ascontiguousarray(codes, np.uint8)
+        nlist, dim = coarse.shape
+        h = _vp()
+        st = lib.nvdb_b200_ivfpq_import(device, dim, nlist, codebooks.shape[0], len(ids), _ptr(coarse), _ptr(codebooks),
+                                        _ptr(list_off), _ptr(ids), _ptr(codes), C.byref(h))
+        if st != 0:
+            raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(None) or b"").decode())
+        return cls(base, _handle=h)
+
+    def _fill_info(self):
+        h = self._h
         n, dim, nl, m, nbytes = _u64(), _u32(), _u32(), _u32(), _u64()
         self._ck(lib.nvdb_b200_ivfpq_info(h, C.byref(n), C.byref(dim), C.byref(nl), C.byref(m), C.byref(nbytes)))
         self.n, self.dim, self.nlist, self.pq_m, self.index_bytes = n.value, dim.value, nl.value, m.value, nbytes.value

@@ -281,6 +281,20 @@ __global__ void __launch_bounds__(kScanThreads) ivfpq_scan_kernel(const IvfScanA
   for (uint32_t j = tid; j < a.R; j += kScanThreads) out[j] = j < cnt[0] ? keys[j] : 0ull;
 }
 
+// sorted_lists[pos] = list that owns grouped position pos (inverse of list_offsets_kernel)
+__global__ void expand_lists_kernel(const uint32_t* __restrict__ list_off, uint32_t nlist, uint32_t n,
+                                    uint32_t* __restrict__ sorted_lists) {
+  const uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= n) return;
+  uint32_t lo = 0, hi = nlist;  // last l with list_off[l] <= pos
+  while (lo + 1 < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (list_off[mid] <= pos) lo = mid;
+    else hi = mid;
+  }
+  sorted_lists[pos] = lo;
+}
+
 // |c_list + reconstruction|^2 of every grouped position (thread per vector, fixed order)
 __global__ void recon_norms_kernel(const uint8_t* __restrict__ codes, const uint32_t* __restrict__ sorted_lists,
                                    const float* __restrict__ coarse, const float* __restrict__ codebooks, uint32_t n, uint32_t d,
@@ -575,6 +589,70 @@ int nvdb_b200_ivfpq_info(const nvdb_b200_ivfpq* h, uint64_t* n, uint32_t* dim, u
   if (index_bytes)
     *index_bytes = (uint64_t)h->nlist * h->d * 4 + (uint64_t)h->M * 256 * h->dsub * 4 + h->n * h->M + h->n * 8 +
                    (uint64_t)(h->nlist + 1) * 4;
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_ivfpq_import(int device, uint32_t dim, uint32_t nlist, uint32_t pq_m, uint64_t n, const float* coarse,
+                           const float* codebooks, const uint32_t* list_off, const uint32_t* ids, const uint8_t* codes,
+                           nvdb_b200_ivfpq** out) {
+  nvdb_b200_ivfpq* h = nullptr;
+  if (!out) return ifail(nullptr, NVDB_B200_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  if (!coarse || !codebooks || !list_off || !ids || !codes) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: NULL array");
+  if (pq_m == 0 || dim == 0 || dim % pq_m != 0 || nlist == 0 || n == 0 || n > 0xFFFFFFF0ull)
+    return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: bad shape");
+  if (list_off[0] != 0 || list_off[nlist] != n) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: list offsets do not cover n");
+  for (uint32_t l = 0; l < nlist; ++l)
+    if (list_off[l] > list_off[l + 1]) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: list offsets not ascending");
+  h = new nvdb_b200_ivfpq();
+  h->device = device;
+  h->d = dim;
+  h->nlist = nlist;
+  h->M = pq_m;
+  h->dsub = dim / pq_m;
+  h->n = n;
+  auto bail = [&](int rc) {
+    t_ivf_err = h->err;
+    ivf_free(h);
+    return rc;
+  };
+  auto body = [&]() -> int {
+    ICK(cudaSetDevice(device), "cudaSetDevice");
+    ICK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    cudaDeviceProp prop;
+    ICK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    h->num_sms = prop.multiProcessorCount;
+    h->max_smem = (int)prop.sharedMemPerBlockOptin;
+    const size_t cb = (size_t)nlist * dim * 4, pb = (size_t)pq_m * 256 * h->dsub * 4;
+    ICK(cudaMalloc(&h->coarse, cb), "cudaMalloc coarse centroids");
+    ICK(cudaMalloc(&h->coarse_hn, (size_t)nlist * 4), "cudaMalloc coarse norms");
+    ICK(cudaMalloc(&h->codebooks, pb), "cudaMalloc codebooks");
+    ICK(cudaMalloc(&h->cb_hn, (size_t)pq_m * 256 * 4), "cudaMalloc codebook norms");
+    ICK(cudaMalloc(&h->codes, (size_t)n * pq_m), "cudaMalloc codes");
+    ICK(cudaMalloc(&h->ids, (size_t)n * 4), "cudaMalloc ids");
+    ICK(cudaMalloc(&h->rnorm, (size_t)n * 4), "cudaMalloc reconstruction norms");
+    ICK(cudaMalloc(&h->list_off, (size_t)(nlist + 1) * 4), "cudaMalloc list offsets");
+    ICK(cudaMemcpy(h->coarse, coarse, cb, cudaMemcpyHostToDevice), "H2D coarse");
+    ICK(cudaMemcpy(h->codebooks, codebooks, pb, cudaMemcpyHostToDevice), "H2D codebooks");
+    ICK(cudaMemcpy(h->codes, codes, (size_t)n * pq_m, cudaMemcpyHostToDevice), "H2D codes");
+    ICK(cudaMemcpy(h->ids, ids, (size_t)n * 4, cudaMemcpyHostToDevice), "H2D ids");
+    ICK(cudaMemcpy(h->list_off, list_off, (size_t)(nlist + 1) * 4, cudaMemcpyHostToDevice), "H2D list offsets");
+    DevBuf sl;
+    ICK(sl.alloc((size_t)n * 4), "cudaMalloc list ids");
+    ICK(half_norms_launch(h->coarse, dim, nlist, dim, h->coarse_hn, h->stream), "coarse norms");
+    ICK(half_norms_launch(h->codebooks, h->dsub, pq_m * 256, h->dsub, h->cb_hn, h->stream), "codebook norms");
+    const uint32_t n32 = (uint32_t)n;
+    expand_lists_kernel<<<(n32 + 255) / 256, 256, 0, h->stream>>>(h->list_off, nlist, n32, sl.as<uint32_t>());
+    recon_norms_kernel<<<(n32 + 255) / 256, 256, 0, h->stream>>>(h->codes, sl.as<uint32_t>(), h->coarse, h->codebooks, n32, dim,
+                                                                 pq_m, h->dsub, h->rnorm);
+    count_launch(2);
+    ICK(cudaGetLastError(), "ivfpq import kernels");
+    ICK(cudaStreamSynchronize(h->stream), "ivfpq import");
+    return NVDB_B200_OK;
+  };
+  const int rc = body();
+  if (rc != NVDB_B200_OK) return bail(rc);
+  *out = h;
   return NVDB_B200_OK;
 }
 

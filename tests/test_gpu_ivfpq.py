@@ -186,3 +186,44 @@ def test_argument_errors(nv):
                 ivf.search_refine(x[:2], 4, 10, 20)          # k > R
             ids, dist = ivf.search(x[:2], 10_000, 5)          # nprobe clamps to nlist
             assert ids.shape == (2, 5) and np.all(ids != 0xFFFFFFFF)
+
+
+def test_import_of_an_oracle_trained_index_and_export_round_trip(nv):
+    """An index trained, encoded and grouped entirely by the numpy oracle, imported with nvdb_b200_ivfpq_import: the
+    device search must rank exactly what the oracle ranks (this separates the search kernels from device training);
+    then export -> import reproduces the same answers bit for bit (the save / load path)."""
+    n, d, nlist, M, nprobe, R = 6000, 32, 16, 8, 6, 40
+    x = clustered(n, d, 30, 12)
+    coarse, cb = ref.train(x[:3000], nlist, M, 6, 21)
+    lists, codes = ref.encode(x, coarse, cb)
+    off, ids, gcodes = ref.group(lists, codes, nlist)
+    rng = np.random.default_rng(2)
+    queries = np.ascontiguousarray(x[rng.integers(0, n, 16)] + 0.05 * rng.standard_normal((16, d)).astype(np.float32))
+    want_i, want_d = ref.search(queries, coarse, cb, off, ids, gcodes, nprobe, R)
+    with nv.FlatIndexCuda.from_host(x, None, F32) as base:
+        with nv.IvfPqIndex.from_arrays(base, coarse, cb, off, ids, gcodes) as ivf:
+            assert (ivf.n, ivf.dim, ivf.nlist, ivf.pq_m) == (n, d, nlist, M)
+            gi, gd = ivf.search(queries, nprobe, R)
+            exported = ivf.export()
+            ri, rd = ivf.search_refine(queries, nprobe, R, 5)
+        for a, b in zip(exported, (coarse, cb, off, ids, gcodes)):
+            assert np.array_equal(a, b)
+        with nv.IvfPqIndex.from_arrays(base, *exported) as ivf2:
+            gi2, gd2 = ivf2.search(queries, nprobe, R)
+        assert np.array_equal(gi, gi2) and np.array_equal(gd, gd2)
+        with pytest.raises(nv.NvdbError):
+            bad = off.copy()
+            bad[-1] -= 1
+            nv.IvfPqIndex.from_arrays(base, coarse, cb, bad, ids, gcodes)
+    ynorm_max = float(((np.abs(coarse).max(0) + np.abs(cb).max(1).reshape(-1)) ** 2).sum())
+    for qi in range(len(queries)):
+        atol = 2e-6 * (float((queries[qi].astype(np.float64) ** 2).sum()) + ynorm_max)
+        assert np.max(np.abs(gd[qi].astype(np.float64) - want_d[qi])) <= atol
+        # same ranking except where two oracle distances are closer than the tolerance
+        for j in np.flatnonzero(gi[qi] != want_i[qi]):
+            assert abs(want_d[qi][j] - gd[qi][j]) <= atol and gi[qi][j] in want_i[qi][max(0, j - 3):j + 4] or \
+                abs(want_d[qi][min(j + 1, R - 1)] - want_d[qi][max(j - 1, 0)]) <= 4 * atol, (qi, j)
+        # refine output = exact squared L2 of candidate rows, ascending, drawn from the candidates
+        assert set(ri[qi].tolist()) <= set(gi[qi].tolist())
+        exact = ((queries[qi][None, :].astype(np.float64) - x[ri[qi]].astype(np.float64)) ** 2).sum(1)
+        assert np.allclose(rd[qi], exact, rtol=1e-5, atol=1e-6) and np.all(np.diff(rd[qi]) >= 0)
