@@ -45,8 +45,8 @@ struct nvdb_b200_ivfpq {
   uint32_t* list_off = nullptr;  // [nlist + 1]
   cudaStream_t stream = nullptr;
   // grow-only search workspaces
-  void* ws[8] = {};
-  size_t ws_bytes[8] = {};
+  void* ws[9] = {};
+  size_t ws_bytes[9] = {};
   void* h_pin = nullptr;
   size_t h_pin_bytes = 0;
   std::mutex mu;
@@ -56,7 +56,7 @@ struct nvdb_b200_ivfpq {
 namespace {
 
 thread_local std::string t_ivf_err;
-enum { IWS_Q = 0, IWS_SCORES = 1, IWS_PROBES = 2, IWS_PARTIAL = 3, IWS_IDS64 = 4, IWS_SC = 5, IWS_CAND = 6, IWS_OUT = 7 };
+enum { IWS_Q = 0, IWS_SCORES = 1, IWS_PROBES = 2, IWS_PARTIAL = 3, IWS_IDS64 = 4, IWS_SC = 5, IWS_CAND = 6, IWS_OUT = 7, IWS_LUT = 8 };
 
 int ifail(const nvdb_b200_ivfpq* h, int code, const std::string& msg) {
   t_ivf_err = msg;
@@ -144,21 +144,91 @@ __global__ void gather_codes_kernel(const uint8_t* __restrict__ src, const uint3
 
 // probes[q][0..nprobe) = the nprobe best-scoring lists of query q (score desc == L2 asc, id asc among equals)
 constexpr int kProbeThreads = 1024;
+constexpr uint32_t kProbeBuf = 1024;  // survivors of the radix select that are sorted exactly
+// Top-nprobe of nlist scores without sorting all of them: a 4 x 8-bit radix select on the ordered score finds the
+// nprobe-th largest score value, the (few) keys at or above it are compacted and bitonic-sorted on the full
+// (score, id) key. A full sort of 4096 keys cost 38 us per query (78 barrier-separated stages); this is ~4 histogram
+// passes + a sort of next_pow2(nprobe + ties) keys. Falls back to the full sort when more than kProbeBuf keys survive
+// (nprobe >= 1024, or a pathological number of equal scores).
 __global__ void __launch_bounds__(kProbeThreads)
 select_probes_kernel(const float* __restrict__ scores, uint32_t nlist, uint32_t bufn, uint32_t nprobe,
                      uint32_t* __restrict__ probes) {
-  extern __shared__ uint64_t pk[];
-  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  extern __shared__ uint64_t pk[];              // [bufn] all keys, then [kProbeBuf] survivors
+  uint64_t* top = pk + bufn;
+  __shared__ uint32_t hist[256];
+  __shared__ uint32_t s_prefix, s_remaining, s_count, s_ties;
+  const uint32_t q = blockIdx.x, tid = threadIdx.x, lane = tid & 31u;
+  auto sync = [] { __syncthreads(); };
   for (uint32_t j = tid; j < bufn; j += kProbeThreads)
     pk[j] = j < nlist ? make_key(scores[(size_t)q * nlist + j], j) : 0ull;
-  __syncthreads();
-  auto sync = [] { __syncthreads(); };
+  if (tid == 0) {
+    s_prefix = 0;
+    s_remaining = nprobe;
+    s_count = 0;
+  }
+  uint32_t mask = 0;
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
+    const uint32_t prefix = s_prefix;
+    for (uint32_t j = tid; j < nlist; j += kProbeThreads) {
+      const uint32_t sc = (uint32_t)(pk[j] >> 32);
+      if ((sc & mask) == prefix) atomicAdd(&hist[(sc >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {  // bins 8*lane .. 8*lane+7; find the bin where the count from the top reaches `remaining`
+      uint32_t local[8], sum = 0;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        local[u] = hist[lane * 8 + u];
+        sum += local[u];
+      }
+      uint32_t above = 0;  // keys in the bins of higher lanes (exclusive suffix sum over the warp)
+#pragma unroll
+      for (int l2 = 31; l2 > 0; --l2) {
+        const uint32_t v = __shfl_sync(0xffffffffu, sum, l2);
+        if ((int)lane < l2) above += v;
+      }
+      const uint32_t remaining = s_remaining;
+      if (above < remaining && remaining <= above + sum) {
+        uint32_t acc = above;
+        for (int u = 7; u >= 0; --u) {
+          if (acc + local[u] >= remaining) {
+            s_prefix = prefix | ((uint32_t)(lane * 8 + u) << shift);
+            s_remaining = remaining - acc;  // still to take among the keys of this bin
+            s_ties = local[u];
+            break;
+          }
+          acc += local[u];
+        }
+      }
+    }
+    mask |= 0xFFu << shift;
+    __syncthreads();
+  }
+  // s_prefix = the nprobe-th largest score; keys above it: nprobe - s_remaining, keys equal to it: s_ties
+  const uint32_t thr = s_prefix, total = nprobe - s_remaining + s_ties;
+  if (nprobe <= nlist && total <= kProbeBuf) {
+    for (uint32_t j = tid; j < nlist; j += kProbeThreads) {
+      const uint64_t key = pk[j];
+      if ((uint32_t)(key >> 32) >= thr) top[atomicAdd(&s_count, 1u)] = key;
+    }
+    __syncthreads();
+    if (tid < total) {  // rank counting: total <= kProbeBuf == kProbeThreads keys, all distinct
+      const uint64_t key = top[tid];
+      uint32_t rank = 0;
+      for (uint32_t i = 0; i < total; ++i) rank += (top[i] > key) ? 1u : 0u;
+      if (rank < nprobe) probes[(size_t)q * nprobe + rank] = key_row(key);
+    }
+    return;
+  }
   bitonic_sort_desc(pk, bufn, tid, kProbeThreads, sync);
   for (uint32_t p = tid; p < nprobe; p += kProbeThreads)
     probes[(size_t)q * nprobe + p] = pk[p] ? key_row(pk[p]) : 0xFFFFFFFFu;
 }
 
 constexpr int kScanThreads = 256;
+constexpr uint32_t kScanVecs = 4;  // stored vectors per thread between two barriers of the list scan
 
 struct IvfScanArgs {
   const float* queries;   // [nq x d]
@@ -169,6 +239,7 @@ struct IvfScanArgs {
   const float* rnorm;     // [n] |c + reconstruction|^2 of every grouped position
   const uint32_t* list_off;
   const uint32_t* probes; // [nq x nprobe]
+  const float* lut;       // [nq x M x 256] q_m . codeword (ivfpq_lut_kernel)
   uint64_t* partial;      // [nq x G x R] ordered keys (score = -distance)
   uint32_t d, M, dsub, nprobe, R, cap, G;
 };
@@ -187,98 +258,241 @@ __device__ __forceinline__ float block_sum(float v, float* red, uint32_t tid) {
   return s;
 }
 
+// T[q][m][j] = q_m . codeword_m[j]: one CTA per (sub-space, query), thread j owns codeword j. The table depends on the
+// query only (see ivfpq_scan_kernel), so it is built ONCE per query here — M x nq small CTAs that each read 256 x dsub
+// codebook words — instead of once per scan CTA (the whole M x 256 x dsub codebook through one SM: 33 us of L2 latency).
+__global__ void __launch_bounds__(256)
+ivfpq_lut_kernel(const float* __restrict__ queries, const float* __restrict__ codebooks, uint32_t d, uint32_t M, uint32_t dsub,
+                 float* __restrict__ lut) {
+  const uint32_t m = blockIdx.x, q = blockIdx.y, j = threadIdx.x;
+  const float* qm = queries + (size_t)q * d + (size_t)m * dsub;  // warp-uniform loads
+  const float* cw = codebooks + ((size_t)m * 256 + j) * dsub;
+  float s = 0.f;
+  for (uint32_t t = 0; t < dsub; ++t) s = __fmaf_rn(__ldg(qm + t), __ldg(cw + t), s);
+  lut[((size_t)q * M + m) * 256 + j] = s;
+}
+
+// CTA-level running top-R for the list scan. Same admission idea as topk_select.cuh (compare against the current R-th
+// best, append survivors with a shared-memory atomic), but compaction is by RANK COUNTING instead of a bitonic sort:
+// every held key counts the keys that beat it (broadcast shared-memory reads, no barriers inside) and, if fewer than R
+// do, drops itself at its rank in the other half of a double buffer. Keys are unique ((distance, row id), every row is
+// visited once), so ranks are a permutation. For the few hundred keys a CTA holds this is one barrier and ~c compares
+// per thread; the bitonic network needs log^2(c)/2 barrier-separated stages at ~0.2 us each — it was 40 % of the scan
+// kernel and most of the merge (profiles/r1_ivfpq_latency_breakdown.txt).
+struct RankTopR {
+  uint64_t* keys;  // [2][cap]
+  uint32_t* cnt;
+  float* thr;
+  uint32_t cap, R, cur, bound;  // bound: uniform upper bound on *cnt
+  bool have_thr;
+
+  __device__ __forceinline__ void init(uint64_t* k, uint32_t* c, float* t, uint32_t cap_, uint32_t R_, uint32_t tid) {
+    keys = k;
+    cnt = c;
+    thr = t;
+    cap = cap_;
+    R = R_;
+    cur = 0;
+    bound = 0;
+    have_thr = false;
+    if (tid == 0) {
+      *cnt = 0;
+      *thr = -INFINITY;
+    }
+  }
+  __device__ __forceinline__ bool offer(float score, uint32_t id) {
+    if (score >= *thr) {
+      const uint32_t pos = atomicAdd(cnt, 1u);
+      keys[cur * cap + pos] = make_key(score, id);
+      return true;
+    }
+    return false;
+  }
+  // all threads of the CTA; ends with the survivors (best first) in the current half
+  __device__ void compact(uint32_t tid, uint32_t nthreads) {
+    __syncthreads();
+    const uint32_t c = *cnt;
+    const uint64_t* src = keys + cur * cap;
+    uint64_t* dst = keys + (cur ^ 1u) * cap;
+    if (tid == 0 && (c & 1u)) keys[cur * cap + c] = 0ull;  // pad to a whole 16-byte pair (cap is even)
+    __syncthreads();
+    const ulonglong2* src2 = reinterpret_cast<const ulonglong2*>(src);
+    const uint32_t pairs = (c + 1u) >> 1;
+    for (uint32_t j = tid; j < c; j += nthreads) {
+      const uint64_t key = src[j];
+      uint32_t rank = 0;
+#pragma unroll 4
+      for (uint32_t i = 0; i < pairs; ++i) {  // broadcast 16-byte loads: two held keys per shared-memory wavefront
+        const ulonglong2 o = src2[i];
+        rank += (o.x > key ? 1u : 0u) + (o.y > key ? 1u : 0u);
+      }
+      if (rank < R) {
+        dst[rank] = key;
+        if (rank == R - 1) *thr = key_score(key);
+      }
+    }
+    __syncthreads();
+    if (tid == 0) *cnt = c < R ? c : R;
+    cur ^= 1u;
+    bound = c < R ? c : R;
+    have_thr = c >= R;
+    __syncthreads();
+  }
+  // after a round of offers (all threads): refresh the exact count; compact when the next round of up to `next` offers
+  // could overflow, or — the first time R keys exist — to install the threshold that makes later pushes rare
+  __device__ __forceinline__ void after_offers(uint32_t next, uint32_t tid, uint32_t nthreads) {
+    __syncthreads();
+    bound = *cnt;
+    if (bound + next > cap || (!have_thr && bound >= R)) compact(tid, nthreads);
+  }
+};
+
 // One CTA per (probe group g, query q). ADC distance of a stored vector y = c + reconstruction:
 //   |q - y|^2 = |q|^2 - 2 q.c + |y|^2 - 2 sum_m q_m . codeword_m[code_m]
-// so the look-up table T[m][j] = q_m . codeword_m[j] depends on the query only: it is built once per CTA and serves all
-// the lists of the group (p = g, g + G, ...); |y|^2 is stored per vector at build time, q.c is one block reduction per
-// list. (A table of squared residual sub-distances would have to be rebuilt for every probed list: M x 256 x dsub
-// codebook reads per (query, probe) — measured 14 ms for 1000 queries x 64 probes, profiles/r1_ivfpq_1M_v1.jsonl.)
+// The table T (ivfpq_lut_kernel) is copied into shared memory once and serves all the lists of the group
+// (p = g, g + G, ...); |y|^2 is stored per vector at build time, q.c is one block reduction per list.
+// (A table of squared residual sub-distances would have to be rebuilt for every probed list: measured 14 ms for
+// 1000 queries x 64 probes, profiles/r1_ivfpq_1M_v1.jsonl.)
 __global__ void __launch_bounds__(kScanThreads) ivfpq_scan_kernel(const IvfScanArgs a) {
   extern __shared__ __align__(16) uint8_t sm[];
   float* lut = reinterpret_cast<float*>(sm);                    // [M x 256]
   float* qv = lut + (size_t)a.M * 256;                          // [d]
-  uint64_t* keys = reinterpret_cast<uint64_t*>(qv + ((a.d + 3u) & ~3u));  // [cap]
-  uint32_t* cnt = reinterpret_cast<uint32_t*>(keys + a.cap);
+  uint64_t* keys = reinterpret_cast<uint64_t*>(qv + ((a.d + 3u) & ~3u));  // [2][cap]
+  uint32_t* cnt = reinterpret_cast<uint32_t*>(keys + 2u * a.cap);
   float* thr = reinterpret_cast<float*>(cnt + 1);
-  float* red = thr + 1;                                         // [8]
+  float* red = thr + 1;                                         // [kScanThreads / 32]
   const uint32_t tid = threadIdx.x, g = blockIdx.x, q = blockIdx.y;
-  auto sync = [] { __syncthreads(); };
-  TopKSelect<1> sel;
+  RankTopR sel;
   sel.init(keys, cnt, thr, a.cap, a.R, tid);
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.lut + (size_t)q * a.M * 256);
+    float4* dst = reinterpret_cast<float4*>(lut);
+    for (uint32_t e = tid; e < a.M * 64u; e += kScanThreads) dst[e] = __ldg(src + e);
+  }
   float qpart = 0.f;
   for (uint32_t t = tid; t < a.d; t += kScanThreads) {
     const float v = a.queries[(size_t)q * a.d + t];
     qv[t] = v;
     qpart = __fmaf_rn(v, v, qpart);
   }
-  const float qq = block_sum(qpart, red, tid);  // (its barriers also publish qv and the selector state)
-  // thread j owns codeword j of every sub-space. The table build is pure load latency (M x dsub codebook words per
-  // thread from L2), so sub-spaces are unrolled 4 deep with 16-byte loads to keep ~12 requests per thread in flight.
-  if ((a.dsub & 3u) == 0) {
-    const uint32_t v4 = a.dsub >> 2;
-#pragma unroll 4
-    for (uint32_t m = 0; m < a.M; ++m) {
-      const float4* cw = reinterpret_cast<const float4*>(a.codebooks + ((size_t)m * 256 + tid) * a.dsub);
-      const float* qm = qv + m * a.dsub;
-      float s = 0.f;
-      for (uint32_t t = 0; t < v4; ++t) {
-        const float4 w = __ldg(cw + t);
-        s = __fmaf_rn(qm[4 * t + 0], w.x, s);
-        s = __fmaf_rn(qm[4 * t + 1], w.y, s);
-        s = __fmaf_rn(qm[4 * t + 2], w.z, s);
-        s = __fmaf_rn(qm[4 * t + 3], w.w, s);
-      }
-      lut[m * 256 + tid] = s;
-    }
-  } else {
-#pragma unroll 4
-    for (uint32_t m = 0; m < a.M; ++m) {
-      const float* cw = a.codebooks + ((size_t)m * 256 + tid) * a.dsub;
-      const float* qm = qv + m * a.dsub;
-      float s = 0.f;
-      for (uint32_t t = 0; t < a.dsub; ++t) s = __fmaf_rn(qm[t], __ldg(cw + t), s);
-      lut[m * 256 + tid] = s;
-    }
-  }
-  __syncthreads();
+  const float qq = block_sum(qpart, red, tid);  // (its barriers also publish lut, qv and the selector state)
   const bool vec16 = (a.M & 15u) == 0;
+  constexpr uint32_t U = kScanVecs, TILE = kScanThreads * kScanVecs;
   for (uint32_t p = g; p < a.nprobe; p += a.G) {
     const uint32_t list = a.probes[(size_t)q * a.nprobe + p];
     if (list == 0xFFFFFFFFu) continue;  // nprobe > nlist (uniform over the CTA)
+    const uint32_t begin = a.list_off[list], end = a.list_off[list + 1];
     float cpart = 0.f;
     for (uint32_t t = tid; t < a.d; t += kScanThreads) cpart = __fmaf_rn(qv[t], a.coarse[(size_t)list * a.d + t], cpart);
     const float qc = block_sum(cpart, red, tid);
     const float base_term = __fmaf_rn(-2.f, qc, qq);
-    const uint32_t begin = a.list_off[list], end = a.list_off[list + 1];
-    for (uint32_t base = begin; base < end; base += kScanThreads) {
-      const uint32_t i = base + tid;
-      bool pushed = false;
-      if (i < end) {
-        const uint8_t* code = a.codes + (size_t)i * a.M;
-        float acc = 0.f;
-        if (vec16) {
-          for (uint32_t m0 = 0; m0 < a.M; m0 += 16) {
-            const uint4 w = *reinterpret_cast<const uint4*>(code + m0);
-            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+    // U vectors per thread and barrier interval: their code words are requested together and the next 16 bytes of
+    // every vector are in flight while the current 16 look-ups run, so a tile costs ~one memory round trip instead
+    // of one per vector chunk (a 256-vector tile with dependent loads took 5.8 us: profiles/r1_ivfpq_latency_*.txt)
+    for (uint32_t base = begin; base < end; base += TILE) {
+      uint32_t idx[U], id[U];
+      float rn[U], acc[U];
+      uint4 w[U];
 #pragma unroll
-            for (int u = 0; u < 16; ++u)
-              acc = __fadd_rn(acc, lut[(m0 + u) * 256 + ((ww[u >> 2] >> ((u & 3) * 8)) & 0xFFu)]);
-          }
-        } else {
-          for (uint32_t m = 0; m < a.M; ++m) acc = __fadd_rn(acc, lut[m * 256 + code[m]]);
-        }
-        const float dist = __fmaf_rn(-2.f, acc, __fadd_rn(base_term, a.rnorm[i]));
-        const float score = -dist;
-        if (score >= thr[0]) pushed = sel.offer(0, score, a.ids[i]);
+      for (uint32_t u = 0; u < U; ++u) {
+        idx[u] = base + u * kScanThreads + tid;
+        const bool ok = idx[u] < end;
+        const uint32_t i = ok ? idx[u] : begin;  // clamp: harmless duplicate read, never offered
+        rn[u] = __ldg(a.rnorm + i);
+        id[u] = __ldg(a.ids + i);
+        acc[u] = 0.f;
+        if (vec16) w[u] = __ldg(reinterpret_cast<const uint4*>(a.codes + (size_t)i * a.M));
+        idx[u] = ok ? i : 0xFFFFFFFFu;
       }
-      const uint32_t pushed_threads = (uint32_t)__syncthreads_count(pushed);
-      sel.end_tile(pushed_threads, kScanThreads, tid, kScanThreads, sync);
+      if (vec16) {
+        for (uint32_t m0 = 0; m0 < a.M; m0 += 16) {
+          uint32_t ww[U][4];
+#pragma unroll
+          for (uint32_t u = 0; u < U; ++u) {
+            ww[u][0] = w[u].x;
+            ww[u][1] = w[u].y;
+            ww[u][2] = w[u].z;
+            ww[u][3] = w[u].w;
+            if (m0 + 16 < a.M) {
+              const uint32_t i = idx[u] != 0xFFFFFFFFu ? idx[u] : begin;
+              w[u] = __ldg(reinterpret_cast<const uint4*>(a.codes + (size_t)i * a.M + m0 + 16));
+            }
+          }
+#pragma unroll
+          for (int e = 0; e < 16; ++e)
+#pragma unroll
+            for (uint32_t u = 0; u < U; ++u)
+              acc[u] = __fadd_rn(acc[u], lut[(m0 + e) * 256 + ((ww[u][e >> 2] >> ((e & 3) * 8)) & 0xFFu)]);
+        }
+      } else {
+#pragma unroll
+        for (uint32_t u = 0; u < U; ++u) {
+          const uint8_t* code = a.codes + (size_t)(idx[u] != 0xFFFFFFFFu ? idx[u] : begin) * a.M;
+          for (uint32_t m = 0; m < a.M; ++m) acc[u] = __fadd_rn(acc[u], lut[m * 256 + code[m]]);
+        }
+      }
+      float score[U];
+#pragma unroll
+      for (uint32_t u = 0; u < U; ++u) score[u] = -__fmaf_rn(-2.f, acc[u], __fadd_rn(base_term, rn[u]));
+      if (!sel.have_thr) {  // (uniform) no threshold yet: offer one vector per thread at a time so that the first
+                            // compaction — which installs it — ranks a few hundred keys, not a whole tile
+#pragma unroll
+        for (uint32_t u = 0; u < U; ++u) {
+          if (idx[u] != 0xFFFFFFFFu) sel.offer(score[u], id[u]);
+          sel.after_offers(u + 1 < U ? kScanThreads : TILE, tid, kScanThreads);
+        }
+      } else {
+#pragma unroll
+        for (uint32_t u = 0; u < U; ++u)
+          if (idx[u] != 0xFFFFFFFFu) sel.offer(score[u], id[u]);
+        sel.after_offers(TILE, tid, kScanThreads);
+      }
     }
   }
-  __syncthreads();
-  sel.compact(tid, kScanThreads, sync);
+  sel.compact(tid, kScanThreads);  // survivors sorted best-first in the current half
+  const uint32_t held = *cnt;
+  const uint64_t* fin = keys + sel.cur * a.cap;
   uint64_t* out = a.partial + ((size_t)q * a.G + g) * a.R;
-  for (uint32_t j = tid; j < a.R; j += kScanThreads) out[j] = j < cnt[0] ? keys[j] : 0ull;
+  for (uint32_t j = tid; j < a.R; j += kScanThreads) out[j] = (j < held) ? fin[j] : 0ull;
+}
+
+// G x R candidate keys per query -> the R best as (u32 id, distance), by rank counting (total <= kMergeMax keys)
+constexpr uint32_t kMergeMax = 1024;
+__global__ void __launch_bounds__(kMergeMax / 2)
+ivfpq_merge_kernel(const uint64_t* __restrict__ partial, uint32_t total, uint32_t R, uint32_t* __restrict__ out_ids,
+                   float* __restrict__ out_dist) {
+  __shared__ __align__(16) uint64_t mk[kMergeMax];
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  uint64_t key[2];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const uint32_t j = tid + (uint32_t)u * (kMergeMax / 2);
+    key[u] = j < total ? partial[(size_t)q * total + j] : 0ull;
+    mk[j] = key[u];
+  }
+  const uint32_t valid = (uint32_t)__syncthreads_count(key[0] != 0ull) + (uint32_t)__syncthreads_count(key[1] != 0ull);
+  // two own keys against every held key, two held keys per (broadcast) 16-byte load: rank counting is bound by
+  // shared-memory wavefronts = warps x loads, so few warps with several keys each
+  uint32_t rank[2] = {0, 0};
+  const uint32_t pairs = (total + 1u) >> 1;
+  const ulonglong2* mk2 = reinterpret_cast<const ulonglong2*>(mk);
+#pragma unroll 4
+  for (uint32_t i = 0; i < pairs; ++i) {
+    const ulonglong2 o = mk2[i];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) rank[u] += (o.x > key[u] ? 1u : 0u) + (o.y > key[u] ? 1u : 0u);
+    if (key[0] == 0ull) break;  // (key[1] is then empty too: slots fill from the front) nothing to rank
+  }
+#pragma unroll
+  for (int u = 0; u < 2; ++u)
+    if (key[u] != 0ull && rank[u] < R) {
+      out_ids[(size_t)q * R + rank[u]] = key_row(key[u]);
+      if (out_dist) out_dist[(size_t)q * R + rank[u]] = -key_score(key[u]);
+    }
+  for (uint32_t j = valid + tid; j < R; j += kMergeMax / 2) {  // fewer than R candidates exist
+    out_ids[(size_t)q * R + j] = 0xFFFFFFFFu;
+    if (out_dist) out_dist[(size_t)q * R + j] = 1e30f;
+  }
 }
 
 // sorted_lists[pos] = list that owns grouped position pos (inverse of list_offsets_kernel)
@@ -450,28 +664,40 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   if (nprobe == 0 || R == 0 || R > 2048) return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search: need nprobe >= 1 and 1 <= R <= 2048");
   if (nprobe > h->nlist) nprobe = h->nlist;
   const uint32_t bufn = next_pow2(h->nlist);
-  if ((size_t)bufn * 8 > (size_t)h->max_smem) return ifail(h, NVDB_B200_ERR_UNSUPPORTED, "nlist too large for the probe selector");
+  if (((size_t)bufn + kProbeBuf) * 8 > (size_t)h->max_smem)
+    return ifail(h, NVDB_B200_ERR_UNSUPPORTED, "nlist too large for the probe selector");
   int rc;
   if ((rc = iws(h, IWS_SCORES, (size_t)nq * h->nlist * 4))) return rc;
   if ((rc = iws(h, IWS_PROBES, (size_t)nq * nprobe * 4))) return rc;
   // probe groups per query: enough CTAs to fill the machine for a few queries, one CTA per query for big batches
   uint32_t G = ((uint32_t)h->num_sms * 2u + nq - 1u) / nq;
   if (G > nprobe) G = nprobe;
-  const uint32_t g_merge = 4096u / R > 8u ? 4096u / R : 8u;  // one CTA merges G x R keys per query: keep that a few thousand
+  // the merge ranks G x R keys by counting (cost ~ (G R)^2): a few hundred keys (else >= 8 groups; > kMergeMax keys take
+  // the bitonic merge kernel). Fewer groups = more lists per scan CTA, which costs less than a quadratic merge.
+  const uint32_t g_merge = 640u / R > 8u ? 640u / R : 8u;
   if (G > g_merge) G = g_merge;
   if (G < 1u) G = 1u;
   if ((rc = iws(h, IWS_PARTIAL, (size_t)nq * G * R * 8))) return rc;
+  if ((rc = iws(h, IWS_LUT, (size_t)nq * h->M * 1024))) return rc;
   if ((rc = iws(h, IWS_IDS64, (size_t)nq * R * 8))) return rc;
   if ((rc = iws(h, IWS_SC, (size_t)nq * R * 4))) return rc;
   float* scores = (float*)h->ws[IWS_SCORES];
   uint32_t* probes = (uint32_t*)h->ws[IWS_PROBES];
   ICK(dot_bias_scores_launch(dq, h->d, nq, h->coarse, h->d, h->coarse_hn, h->nlist, h->d, scores, st), "coarse scores");
-  if ((size_t)bufn * 8 > 48u * 1024u)
-    ICK(cudaFuncSetAttribute(select_probes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bufn * 8)), "smem attr");
-  select_probes_kernel<<<nq, kProbeThreads, (size_t)bufn * 8, st>>>(scores, h->nlist, bufn, nprobe, probes);
+  const size_t probe_smem = ((size_t)bufn + kProbeBuf) * 8;
+  if (probe_smem > 48u * 1024u)
+    ICK(cudaFuncSetAttribute(select_probes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)probe_smem), "smem attr");
+  select_probes_kernel<<<nq, kProbeThreads, probe_smem, st>>>(scores, h->nlist, bufn, nprobe, probes);
   count_launch();
+  for (uint32_t q0 = 0; q0 < nq; q0 += 65535u) {
+    const uint32_t nqp = nq - q0 < 65535u ? nq - q0 : 65535u;
+    ivfpq_lut_kernel<<<dim3(h->M, nqp), 256, 0, st>>>(dq + (size_t)q0 * h->d, h->codebooks, h->d, h->M, h->dsub,
+                                                      (float*)h->ws[IWS_LUT] + (size_t)q0 * h->M * 256);
+    count_launch();
+  }
   IvfScanArgs a;
   a.queries = dq;
+  a.lut = (const float*)h->ws[IWS_LUT];
   a.coarse = h->coarse;
   a.codebooks = h->codebooks;
   a.codes = h->codes;
@@ -486,8 +712,8 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   a.dsub = h->dsub;
   a.nprobe = nprobe;
   a.R = R;
-  a.cap = next_pow2(R + kScanThreads);
-  const size_t smem = (size_t)h->M * 1024 + (size_t)((h->d + 3u) & ~3u) * 4 + (size_t)a.cap * 8 + 8 + 32 + 8;
+  a.cap = (R + 2 * kScanThreads * kScanVecs + 1u) & ~1u;  // even: both halves of the double buffer 16-byte aligned
+  const size_t smem = (size_t)h->M * 1024 + (size_t)((h->d + 3u) & ~3u) * 4 + (size_t)a.cap * 16 + 8 + 4 * (kScanThreads / 32) + 8;
   if (smem > (size_t)h->max_smem) return ifail(h, NVDB_B200_ERR_UNSUPPORTED, "PQ look-up table does not fit shared memory");
   ICK(cudaFuncSetAttribute(ivfpq_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr");
   for (uint32_t q0 = 0; q0 < nq; q0 += 65535u) {  // grid.y limit
@@ -496,8 +722,15 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
     b.queries = dq + (size_t)q0 * h->d;
     b.probes = probes + (size_t)q0 * nprobe;
     b.partial = a.partial + (size_t)q0 * G * R;
+    b.lut = a.lut + (size_t)q0 * h->M * 256;
     ivfpq_scan_kernel<<<dim3(G, nqp), kScanThreads, smem, st>>>(b);
     count_launch();
+  }
+  if (G * R <= kMergeMax) {
+    ivfpq_merge_kernel<<<nq, kMergeMax / 2, 0, st>>>(a.partial, G * R, R, cand_ids, cand_dist);
+    count_launch();
+    ICK(cudaGetLastError(), "ivfpq search kernels");
+    return NVDB_B200_OK;
   }
   ICK(merge_partials_launch(a.partial, G, nq, R, 0, (uint64_t*)h->ws[IWS_IDS64], (float*)h->ws[IWS_SC], st),
       "candidate merge");

@@ -153,12 +153,22 @@ dot_bias_small_kernel(const float* __restrict__ x, size_t ldx, uint32_t n, const
   const uint32_t tid = threadIdx.x, cj = tid & 31u, qi = tid >> 5, j0 = blockIdx.x * 32u;
   for (uint32_t e = tid; e < n * d; e += 256) xs[e] = x[(size_t)(e / d) * ldx + (e % d)];
   float acc = 0.f;
+  float nxt[4];  // the next 32-column slab of the 32 centroid rows is fetched while the current one is consumed
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const uint32_t r = qi + 8u * u;
+    nxt[u] = (j0 + r < k && cj < d) ? c[(size_t)(j0 + r) * ldc + cj] : 0.f;
+  }
   for (uint32_t k0 = 0; k0 < d; k0 += 32) {
     __syncthreads();
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const uint32_t r = qi + 8u * u, col = k0 + cj;
-      cs[r][cj] = (j0 + r < k && col < d) ? c[(size_t)(j0 + r) * ldc + col] : 0.f;
+    for (int u = 0; u < 4; ++u) cs[qi + 8u * u][cj] = nxt[u];
+    if (k0 + 32 < d) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t r = qi + 8u * u, col = k0 + 32 + cj;
+        nxt[u] = (j0 + r < k && col < d) ? c[(size_t)(j0 + r) * ldc + col] : 0.f;
+      }
     }
     __syncthreads();
     if (qi < n) {

@@ -18,3 +18,21 @@ for nprobe, R in ((64, 0), (64, 50)):
     for i in range(50):
         ivf.search(q[i:i + 1], nprobe, 10) if R == 0 else ivf.search_refine(q[i:i + 1], nprobe, R, 10)
     print(nprobe, R, "avg ms", (time.perf_counter() - t0) * 1e3 / 50, flush=True)
+
+# device-side only: queries and candidates stay on the device, CUDA events around 200 back-to-back calls
+import torch
+dev = torch.device("cuda", 0)
+qd = torch.from_numpy(q).to(dev)
+cand = torch.empty((64, 256), dtype=torch.int32, device=dev)
+st = torch.cuda.Stream(device=dev)
+for nprobe, R, nq in ((8, 10, 1), (64, 10, 1), (64, 50, 1), (64, 256, 1), (64, 50, 64)):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(st):
+        for _ in range(5):
+            ivf.search_device(qd.data_ptr(), nq, nprobe, R, cand.data_ptr(), None, st.cuda_stream)
+        e0.record(st)
+        for _ in range(200):
+            ivf.search_device(qd.data_ptr(), nq, nprobe, R, cand.data_ptr(), None, st.cuda_stream)
+        e1.record(st)
+        st.synchronize()
+    print("device-only nq", nq, "nprobe", nprobe, "R", R, "us per call", e0.elapsed_time(e1) * 1e3 / 200, flush=True)
