@@ -26,7 +26,8 @@ $(LIBDIR)/libnvdb_b200.so: $(CU_OBJS)
 	$(NVCC) $(ARCH) -shared -ccbin $(CXX) -o $@ $^
 
 HOST_HDRS := $(wildcard $(PKG)/host/*.h) include/nvdb_b200.h
-HOST_BINS := $(BINDIR)/nvdb_bench $(BINDIR)/nvdb_gt_build $(BINDIR)/nvdb_convert_f16 $(BINDIR)/nvdb_quantize_i8
+HOST_BINS := $(BINDIR)/nvdb_bench $(BINDIR)/nvdb_gt_build $(BINDIR)/nvdb_convert_f16 $(BINDIR)/nvdb_quantize_i8 \
+             $(BINDIR)/nvdb_ivfpq_build $(BINDIR)/nvdb_ivf_eval
 HOST_CXX  := $(CXX) -std=c++17 -O2 -fopenmp -Iinclude -I$(PKG)/host
 HOST_LD   := -L$(LIBDIR) -lnvdb_b200 -Wl,-rpath,'$$ORIGIN/../lib' -lpthread
 host: lib $(HOST_BINS)
@@ -36,6 +37,14 @@ $(BINDIR)/nvdb_bench: $(PKG)/host/nvdb_bench.cpp $(HOST_HDRS)
 	$(HOST_CXX) -o $@ $< $(HOST_LD)
 
 $(BINDIR)/nvdb_gt_build: $(PKG)/host/nvdb_gt_build.cpp $(HOST_HDRS)
+	@mkdir -p $(BINDIR)
+	$(HOST_CXX) -o $@ $< $(HOST_LD)
+
+$(BINDIR)/nvdb_ivfpq_build: $(PKG)/host/nvdb_ivfpq_build.cpp $(HOST_HDRS)
+	@mkdir -p $(BINDIR)
+	$(HOST_CXX) -o $@ $< $(HOST_LD)
+
+$(BINDIR)/nvdb_ivf_eval: $(PKG)/host/nvdb_ivf_eval.cpp $(HOST_HDRS)
 	@mkdir -p $(BINDIR)
 	$(HOST_CXX) -o $@ $< $(HOST_LD)
 

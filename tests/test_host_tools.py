@@ -86,3 +86,68 @@ def test_gt_build_matches_reference_gtbin(tools, oracle, tmp_path, dt):
     assert our_h == ref_h
     assert (tmp_path / "our.gtbin").stat().st_size == (tmp_path / "ref.gtbin").stat().st_size
     assert np.array_equal(our_ids, ref_ids)      # continuous random data: no exact ties
+
+
+def test_ivf_tools_usage_and_input_checks_without_gpu(tools, oracle, tmp_path):
+    """argv / exit codes of the reference tools (apps/nvdb_ivfpq_build.cpp:24-58, apps/nvdb_ivf_eval.cpp:309-345)"""
+    assert run(tools / "nvdb_ivfpq_build").returncode == 1
+    assert run(tools / "nvdb_ivf_eval").returncode == 1
+    f = oracle.synth_f32(1, 0, 300, 16)
+    write_vecbin(tmp_path / "b.vecbin", F32, f)
+    r = run(tools / "nvdb_ivfpq_build", tmp_path / "b.vecbin", tmp_path / "o.ivf", env={"PQ_M": "5"})
+    assert r.returncode == 2 and "PQ_M must divide dim. dim=16 PQ_M=5" in r.stderr
+    r = run(tools / "nvdb_ivfpq_build", tmp_path / "b.vecbin", tmp_path / "o.ivf", env={"PQ_M": "4", "USE_OPQ": "1"})
+    assert r.returncode == 3
+    write_raw12(tmp_path / "q8.raw12", f[:3, :8])
+    r = run(tools / "nvdb_ivf_eval", tmp_path / "b.vecbin", tmp_path / "missing.ivf", tmp_path / "q8.raw12", 5)
+    assert r.returncode == 3 and "Dim mismatch: base.dim=16 query.dim=8" in r.stderr
+    write_vecbin(tmp_path / "q16.vecbin", 2, oracle.to_f16(f[:3]))
+    r = run(tools / "nvdb_ivf_eval", tmp_path / "b.vecbin", tmp_path / "missing.ivf", tmp_path / "q16.vecbin", 5)
+    assert r.returncode == 2 and "Query must be float32 vecbin" in r.stderr
+
+
+@pytest.mark.gpu
+def test_ivfpq_build_then_eval_reports_recall_and_latencies(tools, oracle, tmp_path):
+    """nvdb_ivfpq_build -> index file -> nvdb_ivf_eval with a gtbin from nvdb_gt_build: the reference's three-tool
+    workflow (build, ground truth, evaluate) end to end on the GPU, report in the reference's format."""
+    rng = np.random.default_rng(5)
+    n, d, k = 20_000, 64, 10
+    z = rng.standard_normal((n, 12)).astype(np.float32) @ rng.standard_normal((12, d)).astype(np.float32)
+    x = z + 0.2 * rng.standard_normal((n, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    q = x[rng.integers(0, n, 200)] + 0.02 * rng.standard_normal((200, d)).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    write_vecbin(tmp_path / "base.vecbin", 2, oracle.to_f16(np.ascontiguousarray(x, np.float32)))
+    write_raw12(tmp_path / "q.raw12", np.ascontiguousarray(q, np.float32))
+    env = {"IVF_NLIST": "64", "IVF_TRAIN": "10000", "PQ_M": "16", "IVF_NITER": "8"}
+    r = run(tools / "nvdb_ivfpq_build", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", env=env)
+    assert r.returncode == 0, r.stderr
+    assert "nlist=64 ntrain=10000 PQ_M=16 PQ_BITS=8 USE_OPQ=0" in r.stdout and "Saved IVF-PQ index" in r.stdout
+    assert (tmp_path / "idx.nvdbivf").stat().st_size == 64 + 64 * d * 4 + 16 * 256 * 4 * 4 + 65 * 4 + n * 4 + n * 16
+    r = run(tools / "nvdb_gt_build", tmp_path / "base.vecbin", tmp_path / "q.raw12", k, tmp_path / "q.gtbin")
+    assert r.returncode == 0, r.stderr
+
+    def evaluate(**e):
+        env = {"GT_PATH": str(tmp_path / "q.gtbin")}
+        env.update({a: str(b) for a, b in e.items()})
+        r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k, env=env)
+        assert r.returncode == 0, r.stderr
+        res = dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:])
+        assert f"Recall@{k}: " in r.stdout and "ANN p99:" in r.stdout and "TOTAL p99:" in r.stdout
+        return r.stdout, res
+
+    out, raw = evaluate(IVF_NPROBE=4)
+    assert "REFINE_K=0 (k_search=10)" in out and "IVF nlist=64 nprobe=4" in out and raw["refine_backend"] == "none"
+    out, ref50 = evaluate(IVF_NPROBE=16, REFINE_K=50)
+    assert "REFINE_K=50 (k_search=50)" in out and "CUDA_REFINE=1 refine_ms_total=" in out and ref50["refine_backend"] == "cuda"
+    _, all_lists = evaluate(IVF_NPROBE=64, REFINE_K=500)
+    assert float(ref50["recall"]) > float(raw["recall"]) and float(all_lists["recall"]) > 0.99
+    assert float(ref50["total_avg_ms"]) >= float(ref50["ann_avg_ms"]) > 0
+    # without GT_PATH the neighbours come from the exact flat scan: same recall on normalised data
+    r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
+            env={"IVF_NPROBE": "16", "REFINE_K": "50"})
+    res = dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:])
+    assert abs(float(res["recall"]) - float(ref50["recall"])) < 1e-9
+    r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
+            env={"EVAL_MODE": "ann_only"})
+    assert r.returncode == 0 and f"Recall@{k}: N/A (EVAL_MODE=ann_only)" in r.stdout
