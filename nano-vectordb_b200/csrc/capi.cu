@@ -958,37 +958,37 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   const size_t qbytes = (size_t)nq * idx->dim * 4, ibytes = (size_t)nq * k * 8, sbytes = (size_t)nq * k * 4;
   int rc;
   if ((rc = ensure_ws(idx, WS_QUERIES, qbytes))) return rc;
-  if ((rc = ensure_ws(idx, WS_OUT_IDS, ibytes))) return rc;
-  if ((rc = ensure_ws(idx, WS_OUT_SCORES, sbytes))) return rc;
+  // ids and scores share one device buffer and one pinned buffer: a single D2H copy per call; the four timing events
+  // are recorded only when the caller asked for timings (each costs a few microseconds of a 0.7 ms batch-1 call)
+  if ((rc = ensure_ws(idx, WS_OUT_IDS, ibytes + sbytes))) return rc;
   if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
   if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
   cudaStream_t s = idx->stream;
+  uint64_t* d_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
+  float* d_scores = (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
   std::memcpy(idx->h_pin[0], queries_host, qbytes);
-  CK(cudaEventRecord(idx->ev[0], s), "event");
+  if (timing) CK(cudaEventRecord(idx->ev[0], s), "event");
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
-  CK(cudaEventRecord(idx->ev[1], s), "event");
+  if (timing) CK(cudaEventRecord(idx->ev[1], s), "event");
   uint32_t launches = 0, path_used = 0;
   bool deferred = false;
-  rc = search_device_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, (uint64_t*)idx->d_ws[WS_OUT_IDS],
-                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches, &path_used, &deferred);
+  rc = search_device_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s, &launches, &path_used,
+                          &deferred);
   if (rc) return rc;
-  CK(cudaEventRecord(idx->ev[2], s), "event");
+  if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
   char* hp = (char*)idx->h_pin[1];
-  CK(cudaMemcpyAsync(hp, idx->d_ws[WS_OUT_IDS], ibytes, cudaMemcpyDeviceToHost, s), "D2H ids");
-  CK(cudaMemcpyAsync(hp + ibytes, idx->d_ws[WS_OUT_SCORES], sbytes, cudaMemcpyDeviceToHost, s), "D2H scores");
-  CK(cudaEventRecord(idx->ev[3], s), "event");
-  CK(cudaEventSynchronize(idx->ev[3]), "search sync");
+  CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
+  if (timing) CK(cudaEventRecord(idx->ev[3], s), "event");
+  CK(cudaStreamSynchronize(s), "search sync");
   if (deferred) {  // exact tensor-core path: the certificate verdict arrived with the results
     uint32_t nfall = 0;
-    rc = mma_exact_finish(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, (uint64_t*)idx->d_ws[WS_OUT_IDS],
-                          (float*)idx->d_ws[WS_OUT_SCORES], s, &launches, &nfall);
+    rc = mma_exact_finish(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s, &launches, &nfall);
     if (rc) return rc;
     if (nfall) {  // flagged queries were re-run on the streaming scan: fetch the corrected results
-      CK(cudaEventRecord(idx->ev[2], s), "event");
-      CK(cudaMemcpyAsync(hp, idx->d_ws[WS_OUT_IDS], ibytes, cudaMemcpyDeviceToHost, s), "D2H ids");
-      CK(cudaMemcpyAsync(hp + ibytes, idx->d_ws[WS_OUT_SCORES], sbytes, cudaMemcpyDeviceToHost, s), "D2H scores");
-      CK(cudaEventRecord(idx->ev[3], s), "event");
-      CK(cudaEventSynchronize(idx->ev[3]), "search sync");
+      if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
+      CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
+      if (timing) CK(cudaEventRecord(idx->ev[3], s), "event");
+      CK(cudaStreamSynchronize(s), "search sync");
     }
   }
   std::memcpy(out_ids, hp, ibytes);
