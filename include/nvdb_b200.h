@@ -163,13 +163,23 @@ int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, c
  * apps/nvdb_ivfpq_build.cpp:78-135 (IndexIVFPQ(IndexFlatL2, d, nlist, PQ_M, PQ_BITS, METRIC_L2), train on the first
  * IVF_TRAIN rows, add all rows); search: apps/nvdb_ivf_eval.cpp:398-408,482 (ivf->nprobe, idx->search(1, q, k_search)).
  * FAISS is not vendored by the reference and not present here: parity is UNPINNED; the algorithm is the
- * published IVFADC with residual encoding, checked against oracle/ivfpq_ref.py. OPQ (USE_OPQ=1) is not implemented.
+ * published IVFADC with residual encoding (+ optional OPQ rotation), checked against oracle/ivfpq_ref.py.
  * All kernels run on `base`'s device; base rows are read from its device-resident payload (f32 / f16 / i8+scale). */
 typedef struct nvdb_b200_ivfpq nvdb_b200_ivfpq;
 /* pq_bits must be 8; pq_m must divide dim (exit code 2 of nvdb_ivfpq_build); ntrain = 0 -> all rows (the tool's
  * IVF_TRAIN=200000 default is the caller's); niter <= 0 -> 25 Lloyd iterations. Deterministic for a given seed. */
 int nvdb_b200_ivfpq_build(nvdb_b200_index* base, uint32_t nlist, uint32_t pq_m, uint32_t pq_bits, uint64_t ntrain,
                           int niter, uint64_t seed, nvdb_b200_ivfpq** out);
+/* Same with an OPQ rotation in front (the reference's USE_OPQ=1: faiss::OPQMatrix + IndexPreTransform,
+ * apps/nvdb_ivfpq_build.cpp:78-91, OPQ_NITER default 25): opq_niter rounds of {PQ of the rotated training rows,
+ * orthogonal Procrustes update of the rotation}; 0 = no rotation. Queries are rotated inside search; the refine stage
+ * works on the original rows. */
+int nvdb_b200_ivfpq_build_opq(nvdb_b200_index* base, uint32_t nlist, uint32_t pq_m, uint32_t pq_bits, uint64_t ntrain,
+                              int niter, int opq_niter, uint64_t seed, nvdb_b200_ivfpq** out);
+/* The rotation R (dim x dim, row-major, x' = x R): *has_rotation = 0/1; rotation may be NULL. set_rotation installs one on
+ * an imported index (NULL removes it). */
+int nvdb_b200_ivfpq_rotation(const nvdb_b200_ivfpq* ivf, float* rotation, int* has_rotation);
+int nvdb_b200_ivfpq_set_rotation(nvdb_b200_ivfpq* ivf, const float* rotation);
 int nvdb_b200_ivfpq_destroy(nvdb_b200_ivfpq* ivf);
 const char* nvdb_b200_ivfpq_last_error(const nvdb_b200_ivfpq* ivf);
 int nvdb_b200_ivfpq_info(const nvdb_b200_ivfpq* ivf, uint64_t* n, uint32_t* dim, uint32_t* nlist, uint32_t* pq_m,

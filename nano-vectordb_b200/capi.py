@@ -65,6 +65,9 @@ _sig = {
     "nvdb_b200_convert": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp]),
     "nvdb_b200_convert_device": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp, _vp]),
     "nvdb_b200_ivfpq_build": (_i, [_vp, _u32, _u32, _u32, _u64, _i, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_ivfpq_build_opq": (_i, [_vp, _u32, _u32, _u32, _u64, _i, _i, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_ivfpq_rotation": (_i, [_vp, _vp, C.POINTER(_i)]),
+    "nvdb_b200_ivfpq_set_rotation": (_i, [_vp, _vp]),
     "nvdb_b200_ivfpq_destroy": (_i, [_vp]),
     "nvdb_b200_ivfpq_last_error": (C.c_char_p, [_vp]),
     "nvdb_b200_ivfpq_info": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u64)]),
@@ -262,11 +265,12 @@ class IvfPqIndex:
     """IVF-PQ candidate generator over a device-resident base (reference: FAISS IndexIVFPQ as used by
     apps/nvdb_ivfpq_build.cpp:78-135 and apps/nvdb_ivf_eval.cpp:398-408,482). Parity unpinned (no FAISS here)."""
 
-    def __init__(self, base: "FlatIndexCuda", nlist=4096, pq_m=48, pq_bits=8, ntrain=200_000, niter=25, seed=1234, _handle=None):
+    def __init__(self, base: "FlatIndexCuda", nlist=4096, pq_m=48, pq_bits=8, ntrain=200_000, niter=25, seed=1234,
+                 opq_niter=0, _handle=None):
         h = _handle
         if h is None:
             h = _vp()
-            st = lib.nvdb_b200_ivfpq_build(base._h, nlist, pq_m, pq_bits, ntrain, niter, seed, C.byref(h))
+            st = lib.nvdb_b200_ivfpq_build_opq(base._h, nlist, pq_m, pq_bits, ntrain, niter, opq_niter, seed, C.byref(h))
             if st != 0:
                 raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(None) or b"").decode())
         self._h = h
@@ -274,7 +278,7 @@ class IvfPqIndex:
         self._fill_info()
 
     @classmethod
-    def from_arrays(cls, base, coarse, codebooks, list_off, ids, codes, device=0):
+    def from_arrays(cls, base, coarse, codebooks, list_off, ids, codes, device=0, rotation=None):
         """index from exported / externally trained parameters (nvdb_b200_ivfpq_import); `base` is only used by search_refine"""
         coarse = np.ascontiguousarray(coarse, np.float32)
         codebooks = np.ascontiguousarray(codebooks, np.float32)
@@ -287,7 +291,24 @@ class IvfPqIndex:
                                         _ptr(list_off), _ptr(ids), _ptr(codes), C.byref(h))
         if st != 0:
             raise NvdbError(st, (lib.nvdb_b200_ivfpq_last_error(None) or b"").decode())
-        return cls(base, _handle=h)
+        self = cls(base, _handle=h)
+        if rotation is not None:
+            self.set_rotation(rotation)
+        return self
+
+    def rotation(self):
+        """the OPQ rotation R [d,d] (x' = x @ R) or None"""
+        has = _i()
+        self._ck(lib.nvdb_b200_ivfpq_rotation(self._h, None, C.byref(has)))
+        if not has.value:
+            return None
+        R = np.empty((self.dim, self.dim), np.float32)
+        self._ck(lib.nvdb_b200_ivfpq_rotation(self._h, _ptr(R), C.byref(has)))
+        return R
+
+    def set_rotation(self, R):
+        R = None if R is None else np.ascontiguousarray(R, np.float32)
+        self._ck(lib.nvdb_b200_ivfpq_set_rotation(self._h, _ptr(R)))
 
     def _fill_info(self):
         h = self._h

@@ -23,6 +23,11 @@ cudaError_t nearest_centroid_launch(const float* x, size_t ldx, uint32_t n, cons
 // nearest_centroid, centroid update in ascending point order, empty clusters re-seeded from the largest cluster.
 // centroids: [k x d] dense. Allocates and frees its own scratch (build-time path).
 cudaError_t kmeans_train(const float* x, size_t ldx, uint32_t n, uint32_t d, uint32_t k, int niter, uint64_t seed,
-                         float* centroids, int num_sms, cudaStream_t stream);
+                         float* centroids, int num_sms, cudaStream_t stream, bool warm_start = false);
+
+// out[c][r] = in[r][c]
+cudaError_t transpose_launch(const float* in, uint32_t rows, uint32_t cols, float* out, cudaStream_t stream);
+// M <- orthogonal polar factor of M (d x d) by `iters` Newton-Schulz steps; ws: 3*d*d + 1 floats; zeros_d: d zeros
+cudaError_t polar_factor_launch(float* M, uint32_t d, int iters, float* ws, const float* zeros_d, cudaStream_t stream);
 
 }  // namespace nvdb_b200

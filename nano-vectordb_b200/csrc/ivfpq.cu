@@ -43,10 +43,12 @@ struct nvdb_b200_ivfpq {
   uint32_t* ids = nullptr;     // [n] row id of every grouped position
   float* rnorm = nullptr;      // [n] |c + reconstruction|^2 of every grouped position
   uint32_t* list_off = nullptr;  // [nlist + 1]
+  float* rot_t = nullptr;      // OPQ: [d x d] R^T (row j = column j of the rotation R; x' = x R), NULL without OPQ
+  float* zeros = nullptr;      // [max(d, 256)] zeros (GEMM bias of plain products)
   cudaStream_t stream = nullptr;
   // grow-only search workspaces
-  void* ws[9] = {};
-  size_t ws_bytes[9] = {};
+  void* ws[10] = {};
+  size_t ws_bytes[10] = {};
   void* h_pin = nullptr;
   size_t h_pin_bytes = 0;
   std::mutex mu;
@@ -56,7 +58,8 @@ struct nvdb_b200_ivfpq {
 namespace {
 
 thread_local std::string t_ivf_err;
-enum { IWS_Q = 0, IWS_SCORES = 1, IWS_PROBES = 2, IWS_PARTIAL = 3, IWS_IDS64 = 4, IWS_SC = 5, IWS_CAND = 6, IWS_OUT = 7, IWS_LUT = 8 };
+enum { IWS_Q = 0, IWS_SCORES = 1, IWS_PROBES = 2, IWS_PARTIAL = 3, IWS_IDS64 = 4, IWS_SC = 5, IWS_CAND = 6, IWS_OUT = 7, IWS_LUT = 8,
+       IWS_QROT = 9 };
 
 int ifail(const nvdb_b200_ivfpq* h, int code, const std::string& msg) {
   t_ivf_err = msg;
@@ -110,6 +113,21 @@ __global__ void write_code_kernel(const uint32_t* __restrict__ assign, uint32_t 
                                   uint8_t* __restrict__ codes /* already offset to the chunk's first row */) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < nrows) codes[(size_t)i * M + m] = (uint8_t)assign[i];
+}
+
+// y[i][m*dsub .. +dsub) = codeword_m[assign[i]]   (OPQ training: reconstruction of the rotated training rows)
+__global__ void gather_codewords_kernel(const uint32_t* __restrict__ assign, uint32_t nrows, const float* __restrict__ cb_m,
+                                        uint32_t dsub, float* __restrict__ y_m, uint32_t ldy) {
+  const size_t total = (size_t)nrows * dsub;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = e / dsub, t = e - r * dsub;
+    y_m[r * ldy + t] = cb_m[(size_t)assign[r] * dsub + t];
+  }
+}
+__global__ void identity_kernel(float* __restrict__ a, uint32_t d) {
+  const size_t total = (size_t)d * d;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x)
+    a[e] = (e / d == e % d) ? 1.f : 0.f;
 }
 
 __global__ void iota_kernel(uint32_t* __restrict__ v, uint32_t n) {
@@ -555,6 +573,8 @@ void ivf_free(nvdb_b200_ivfpq* h) {
   cudaFree(h->ids);
   cudaFree(h->rnorm);
   cudaFree(h->list_off);
+  cudaFree(h->rot_t);
+  cudaFree(h->zeros);
   for (void* w : h->ws) cudaFree(w);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -569,8 +589,63 @@ struct DevBuf {  // build-time scratch, freed on scope exit
   T* as() { return reinterpret_cast<T*>(p); }
 };
 
+// out[n x d] = x[n x d] R  (rot_t = R^T, so this is the "row . row" product of the tile GEMM)
+cudaError_t rotate_rows(const nvdb_b200_ivfpq* h, const float* x, uint32_t n, float* out, cudaStream_t st) {
+  return dot_bias_scores_launch(x, h->d, n, h->rot_t, h->d, h->zeros, h->d, h->d, out, st);
+}
+
+// OPQ (Ge, He, Ke, Sun: "Optimized Product Quantization", non-parametric solution), what the reference enables with
+// USE_OPQ=1 (faiss::OPQMatrix, apps/nvdb_ivfpq_build.cpp:78-91): alternate (a) PQ of the rotated training rows X R,
+// (b) R = argmin |X R - Y|_F over orthogonal R with Y the PQ reconstruction = polar factor of X^T Y. All on the device:
+// rotation and X^T Y by the tile GEMM, the polar factor by Newton-Schulz (kmeans.cu), PQ by the k-means above, warm
+// started after the first round. x: [nt x d] training rows (unchanged). Leaves h->rot_t = R^T.
+int opq_train(nvdb_b200_ivfpq* h, const float* x, uint32_t nt, int opq_niter, uint64_t seed, void* assign_ws, uint32_t* assign) {
+  const uint32_t d = h->d, M = h->M, dsub = h->dsub;
+  cudaStream_t st = h->stream;
+  const size_t nd = (size_t)nt * d, dd = (size_t)d * d;
+  DevBuf xr, y, xt, yt, R, cb, cbhn, pws;
+  ICK(xr.alloc(nd * 4), "cudaMalloc OPQ rotated rows");
+  ICK(y.alloc(nd * 4), "cudaMalloc OPQ reconstruction");
+  ICK(xt.alloc(nd * 4), "cudaMalloc OPQ X^T");
+  ICK(yt.alloc(nd * 4), "cudaMalloc OPQ Y^T");
+  ICK(R.alloc(dd * 4), "cudaMalloc OPQ rotation");
+  ICK(cb.alloc((size_t)M * 256 * dsub * 4), "cudaMalloc OPQ codebooks");
+  ICK(cbhn.alloc((size_t)M * 256 * 4), "cudaMalloc OPQ codebook norms");
+  ICK(pws.alloc((3 * dd + 1) * 4), "cudaMalloc polar workspace");
+  ICK(cudaMalloc(&h->rot_t, dd * 4), "cudaMalloc rotation");
+  identity_kernel<<<256, 256, 0, st>>>(h->rot_t, d);
+  count_launch();
+  ICK(transpose_launch(x, nt, d, xt.as<float>(), st), "transpose X");
+  const int grid = h->num_sms * 8;
+  for (int it = 0; it < opq_niter; ++it) {
+    ICK(rotate_rows(h, x, nt, xr.as<float>(), st), "OPQ rotate");
+    for (uint32_t m = 0; m < M; ++m) {
+      float* cbm = cb.as<float>() + (size_t)m * 256 * dsub;
+      ICK(kmeans_train(xr.as<float>() + (size_t)m * dsub, d, nt, dsub, 256, it == 0 ? 6 : 1, seed + 1000 + m, cbm, h->num_sms, st,
+                       it > 0),
+          "OPQ PQ k-means");
+    }
+    ICK(half_norms_launch(cb.as<float>(), dsub, M * 256, dsub, cbhn.as<float>(), st), "OPQ codebook norms");
+    for (uint32_t m = 0; m < M; ++m) {
+      const float* cbm = cb.as<float>() + (size_t)m * 256 * dsub;
+      ICK(nearest_centroid_launch(xr.as<float>() + (size_t)m * dsub, d, nt, cbm, dsub, cbhn.as<float>() + (size_t)m * 256, 256,
+                                  dsub, assign, assign_ws, h->num_sms, st),
+          "OPQ PQ assignment");
+      gather_codewords_kernel<<<grid, 256, 0, st>>>(assign, nt, cbm, dsub, y.as<float>() + (size_t)m * dsub, d);
+      count_launch();
+    }
+    ICK(transpose_launch(y.as<float>(), nt, d, yt.as<float>(), st), "transpose Y");
+    // X^T Y  (d x d, inner dimension nt)
+    ICK(dot_bias_scores_launch(xt.as<float>(), nt, d, yt.as<float>(), nt, h->zeros, d, nt, R.as<float>(), st), "X^T Y");
+    ICK(polar_factor_launch(R.as<float>(), d, 40, pws.as<float>(), h->zeros, st), "polar factor");
+    ICK(transpose_launch(R.as<float>(), d, d, h->rot_t, st), "transpose R");
+  }
+  ICK(cudaStreamSynchronize(st), "OPQ training");
+  return NVDB_B200_OK;
+}
+
 int build_impl(nvdb_b200_ivfpq* h, const void* payload, const float* scales, uint32_t dtype, uint64_t ntrain, int niter,
-               uint64_t seed) {
+               int opq_niter, uint64_t seed) {
   const uint32_t d = h->d, M = h->M, dsub = h->dsub, nlist = h->nlist;
   const uint32_t n = (uint32_t)h->n;
   cudaStream_t st = h->stream;
@@ -583,6 +658,8 @@ int build_impl(nvdb_b200_ivfpq* h, const void* payload, const float* scales, uin
   ICK(cudaMalloc(&h->ids, (size_t)n * 4), "cudaMalloc ids");
   ICK(cudaMalloc(&h->rnorm, (size_t)n * 4), "cudaMalloc reconstruction norms");
   ICK(cudaMalloc(&h->list_off, (size_t)(nlist + 1) * 4), "cudaMalloc list offsets");
+  ICK(cudaMalloc(&h->zeros, (size_t)(d > 256 ? d : 256) * 4), "cudaMalloc zeros");
+  ICK(cudaMemsetAsync(h->zeros, 0, (size_t)(d > 256 ? d : 256) * 4, st), "memset zeros");
 
   const uint32_t chunk = 131072;
   const uint32_t xrows = nt > chunk ? nt : chunk;
@@ -597,9 +674,17 @@ int build_impl(nvdb_b200_ivfpq* h, const void* payload, const float* scales, uin
   ICK(codes_tmp.alloc((size_t)n * M), "cudaMalloc codes (row order)");
   const int fill_grid = h->num_sms * 8;
 
-  // ---- train: coarse centroids on the first nt rows, PQ codebooks on their residuals
+  // ---- train: (OPQ rotation,) coarse centroids on the first nt rows, PQ codebooks on their residuals
   rows_to_f32_kernel<<<fill_grid, 256, 0, st>>>(dtype, payload, scales, 0, nt, d, x.as<float>());
   count_launch();
+  DevBuf xrot;  // rotated rows of the current chunk (OPQ only)
+  if (opq_niter > 0) {
+    const int rc = opq_train(h, x.as<float>(), nt, opq_niter, seed, ws.p, assign.as<uint32_t>());
+    if (rc) return rc;
+    ICK(xrot.alloc((size_t)xrows * d * 4), "cudaMalloc rotated rows");
+    ICK(rotate_rows(h, x.as<float>(), nt, xrot.as<float>(), st), "rotate training rows");
+    ICK(cudaMemcpyAsync(x.p, xrot.p, (size_t)nt * d * 4, cudaMemcpyDeviceToDevice, st), "copy rotated rows");
+  }
   ICK(kmeans_train(x.as<float>(), d, nt, d, nlist, niter, seed, h->coarse, h->num_sms, st), "coarse k-means");
   ICK(half_norms_launch(h->coarse, d, nlist, d, h->coarse_hn, st), "coarse norms");
   ICK(nearest_centroid_launch(x.as<float>(), d, nt, h->coarse, d, h->coarse_hn, nlist, d, assign.as<uint32_t>(), ws.p,
@@ -618,6 +703,10 @@ int build_impl(nvdb_b200_ivfpq* h, const void* payload, const float* scales, uin
     const uint32_t nr = (uint32_t)((n - r0) < chunk ? (n - r0) : chunk);
     rows_to_f32_kernel<<<fill_grid, 256, 0, st>>>(dtype, payload, scales, r0, nr, d, x.as<float>());
     count_launch();
+    if (h->rot_t) {
+      ICK(rotate_rows(h, x.as<float>(), nr, xrot.as<float>(), st), "rotate rows");
+      ICK(cudaMemcpyAsync(x.p, xrot.p, (size_t)nr * d * 4, cudaMemcpyDeviceToDevice, st), "copy rotated rows");
+    }
     ICK(nearest_centroid_launch(x.as<float>(), d, nr, h->coarse, d, h->coarse_hn, nlist, d, lists.as<uint32_t>() + r0, ws.p,
                                 h->num_sms, st),
         "coarse assignment");
@@ -683,6 +772,11 @@ int search_device_impl(nvdb_b200_ivfpq* h, const float* dq, uint32_t nq, uint32_
   if ((rc = iws(h, IWS_SC, (size_t)nq * R * 4))) return rc;
   float* scores = (float*)h->ws[IWS_SCORES];
   uint32_t* probes = (uint32_t*)h->ws[IWS_PROBES];
+  if (h->rot_t) {  // OPQ: the index lives in the rotated space (distances are rotation invariant)
+    if ((rc = iws(h, IWS_QROT, (size_t)nq * h->d * 4))) return rc;
+    ICK(rotate_rows(h, dq, nq, (float*)h->ws[IWS_QROT], st), "rotate queries");
+    dq = (const float*)h->ws[IWS_QROT];
+  }
   ICK(dot_bias_scores_launch(dq, h->d, nq, h->coarse, h->d, h->coarse_hn, h->nlist, h->d, scores, st), "coarse scores");
   const size_t probe_smem = ((size_t)bufn + kProbeBuf) * 8;
   if (probe_smem > 48u * 1024u)
@@ -761,6 +855,41 @@ const char* nvdb_b200_ivfpq_last_error(const nvdb_b200_ivfpq* h) { return h ? h-
 
 int nvdb_b200_ivfpq_build(nvdb_b200_index* base, uint32_t nlist, uint32_t pq_m, uint32_t pq_bits, uint64_t ntrain,
                           int niter, uint64_t seed, nvdb_b200_ivfpq** out) {
+  return nvdb_b200_ivfpq_build_opq(base, nlist, pq_m, pq_bits, ntrain, niter, 0, seed, out);
+}
+
+int nvdb_b200_ivfpq_rotation(const nvdb_b200_ivfpq* h, float* rotation, int* has_rotation) {
+  if (!h) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq handle is NULL");
+  if (has_rotation) *has_rotation = h->rot_t ? 1 : 0;
+  if (rotation && h->rot_t) {
+    ICK(cudaSetDevice(h->device), "cudaSetDevice");
+    std::vector<float> rt((size_t)h->d * h->d);
+    ICK(cudaMemcpy(rt.data(), h->rot_t, rt.size() * 4, cudaMemcpyDeviceToHost), "export rotation");
+    for (uint32_t i = 0; i < h->d; ++i)
+      for (uint32_t j = 0; j < h->d; ++j) rotation[(size_t)i * h->d + j] = rt[(size_t)j * h->d + i];
+  }
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_ivfpq_set_rotation(nvdb_b200_ivfpq* h, const float* rotation) {
+  if (!h) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq handle is NULL");
+  std::lock_guard<std::mutex> lock(h->mu);
+  ICK(cudaSetDevice(h->device), "cudaSetDevice");
+  if (!rotation) {
+    cudaFree(h->rot_t);
+    h->rot_t = nullptr;
+    return NVDB_B200_OK;
+  }
+  std::vector<float> rt((size_t)h->d * h->d);
+  for (uint32_t i = 0; i < h->d; ++i)
+    for (uint32_t j = 0; j < h->d; ++j) rt[(size_t)j * h->d + i] = rotation[(size_t)i * h->d + j];
+  if (!h->rot_t) ICK(cudaMalloc(&h->rot_t, rt.size() * 4), "cudaMalloc rotation");
+  ICK(cudaMemcpy(h->rot_t, rt.data(), rt.size() * 4, cudaMemcpyHostToDevice), "H2D rotation");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_ivfpq_build_opq(nvdb_b200_index* base, uint32_t nlist, uint32_t pq_m, uint32_t pq_bits, uint64_t ntrain,
+                              int niter, int opq_niter, uint64_t seed, nvdb_b200_ivfpq** out) {
   nvdb_b200_ivfpq* h = nullptr;
   if (!out) return ifail(nullptr, NVDB_B200_ERR_ARG, "out is NULL");
   *out = nullptr;
@@ -797,7 +926,7 @@ int nvdb_b200_ivfpq_build(nvdb_b200_index* base, uint32_t nlist, uint32_t pq_m, 
   }
   h->num_sms = prop.multiProcessorCount;
   h->max_smem = (int)prop.sharedMemPerBlockOptin;
-  const int rc = build_impl(h, payload, scales, dtype, nt, niter, seed);
+  const int rc = build_impl(h, payload, scales, dtype, nt, niter, opq_niter < 0 ? 0 : opq_niter, seed);
   if (rc != NVDB_B200_OK) {
     t_ivf_err = h->err;
     ivf_free(h);
@@ -865,6 +994,8 @@ int nvdb_b200_ivfpq_import(int device, uint32_t dim, uint32_t nlist, uint32_t pq
     ICK(cudaMalloc(&h->ids, (size_t)n * 4), "cudaMalloc ids");
     ICK(cudaMalloc(&h->rnorm, (size_t)n * 4), "cudaMalloc reconstruction norms");
     ICK(cudaMalloc(&h->list_off, (size_t)(nlist + 1) * 4), "cudaMalloc list offsets");
+    ICK(cudaMalloc(&h->zeros, (size_t)(dim > 256 ? dim : 256) * 4), "cudaMalloc zeros");
+    ICK(cudaMemset(h->zeros, 0, (size_t)(dim > 256 ? dim : 256) * 4), "memset zeros");
     ICK(cudaMemcpy(h->coarse, coarse, cb, cudaMemcpyHostToDevice), "H2D coarse");
     ICK(cudaMemcpy(h->codebooks, codebooks, pb, cudaMemcpyHostToDevice), "H2D codebooks");
     ICK(cudaMemcpy(h->codes, codes, (size_t)n * pq_m, cudaMemcpyHostToDevice), "H2D codes");

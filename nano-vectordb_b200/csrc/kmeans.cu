@@ -361,7 +361,7 @@ cudaError_t nearest_centroid_launch(const float* x, size_t ldx, uint32_t n, cons
 }
 
 cudaError_t kmeans_train(const float* x, size_t ldx, uint32_t n, uint32_t d, uint32_t k, int niter, uint64_t seed,
-                         float* centroids, int num_sms, cudaStream_t stream) {
+                         float* centroids, int num_sms, cudaStream_t stream, bool warm_start) {
   if (n == 0 || k == 0 || d == 0 || d > (uint32_t)(kUpdThreads * kUpdRegs) || n < k) return cudaErrorInvalidValue;
   uint32_t *assign = nullptr, *counts = nullptr;
   float* hn = nullptr;
@@ -379,8 +379,10 @@ cudaError_t kmeans_train(const float* x, size_t ldx, uint32_t n, uint32_t d, uin
   if ((e = cudaMalloc(&counts, (size_t)k * 4)) != cudaSuccess) return done(e);
   if ((e = cudaMalloc(&hn, (size_t)k * 4)) != cudaSuccess) return done(e);
   if ((e = cudaMalloc(&ws, nearest_centroid_ws_bytes(n, k, num_sms))) != cudaSuccess) return done(e);
-  init_centroids_kernel<<<k, 128, 0, stream>>>(x, ldx, n, d, k, seed, centroids);
-  count_launch();
+  if (!warm_start) {
+    init_centroids_kernel<<<k, 128, 0, stream>>>(x, ldx, n, d, k, seed, centroids);
+    count_launch();
+  }
   for (int it = 0; it < niter; ++it) {
     if ((e = half_norms_launch(centroids, d, k, d, hn, stream)) != cudaSuccess) return done(e);
     if ((e = nearest_centroid_launch(x, ldx, n, centroids, d, hn, k, d, assign, ws, num_sms, stream)) != cudaSuccess)
@@ -391,6 +393,73 @@ cudaError_t kmeans_train(const float* x, size_t ldx, uint32_t n, uint32_t d, uin
     if ((e = cudaGetLastError()) != cudaSuccess) return done(e);
   }
   return done(cudaStreamSynchronize(stream));
+}
+
+// ---- small dense helpers for the OPQ rotation (ivfpq.cu): transposes, A <- a*A + b*B, Frobenius norm ---------------
+namespace {
+__global__ void transpose_kernel(const float* __restrict__ in, uint32_t rows, uint32_t cols, float* __restrict__ out) {
+  __shared__ float tile[32][33];
+  const uint32_t bx = blockIdx.x * 32, by = blockIdx.y * 32;
+  for (uint32_t r = threadIdx.y; r < 32; r += 8) {
+    const uint32_t gr = by + r, gc = bx + threadIdx.x;
+    tile[r][threadIdx.x] = (gr < rows && gc < cols) ? in[(size_t)gr * cols + gc] : 0.f;
+  }
+  __syncthreads();
+  for (uint32_t r = threadIdx.y; r < 32; r += 8) {
+    const uint32_t gr = bx + r, gc = by + threadIdx.x;  // out is [cols][rows]
+    if (gr < cols && gc < rows) out[(size_t)gr * rows + gc] = tile[threadIdx.x][r];
+  }
+}
+__global__ void axpby_kernel(float a, const float* __restrict__ A, float b, const float* __restrict__ B, size_t n,
+                             float* __restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = __fmaf_rn(a, A[i], __fmul_rn(b, B[i]));
+}
+// deterministic: one CTA, fixed strides and a fixed tree
+__global__ void __launch_bounds__(1024) sumsq_kernel(const float* __restrict__ A, size_t n, float* __restrict__ out) {
+  __shared__ float red[32];
+  float s = 0.f;
+  for (size_t i = threadIdx.x; i < n; i += 1024) s = __fmaf_rn(A[i], A[i], s);
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) s = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 32; ++w) t = __fadd_rn(t, red[w]);
+    *out = t;
+  }
+}
+__global__ void scale_by_rsqrt_kernel(float* __restrict__ A, size_t n, const float* __restrict__ sumsq) {
+  const float inv = rsqrtf(fmaxf(*sumsq, 1e-30f));
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) A[i] *= inv;
+}
+}  // namespace
+
+cudaError_t transpose_launch(const float* in, uint32_t rows, uint32_t cols, float* out, cudaStream_t stream) {
+  transpose_kernel<<<dim3((cols + 31) / 32, (rows + 31) / 32), dim3(32, 8), 0, stream>>>(in, rows, cols, out);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// Orthogonal polar factor of the square matrix M (d x d, row-major, overwritten): the solution U V^T of the orthogonal
+// Procrustes problem for M = U S V^T, by Newton-Schulz iterations A <- 1.5 A - 0.5 (A A^T) A on A = M / |M|_F — matrix
+// products only (the tile GEMM above), no SVD library. ws: 3 * d * d floats + 1.
+cudaError_t polar_factor_launch(float* M, uint32_t d, int iters, float* ws, const float* zeros_d, cudaStream_t stream) {
+  const size_t nn = (size_t)d * d;
+  float *G = ws, *AT = ws + nn, *T = ws + 2 * nn, *ss = ws + 3 * nn;
+  sumsq_kernel<<<1, 1024, 0, stream>>>(M, nn, ss);
+  scale_by_rsqrt_kernel<<<256, 256, 0, stream>>>(M, nn, ss);
+  count_launch(2);
+  for (int it = 0; it < iters; ++it) {
+    cudaError_t e = dot_bias_scores_launch(M, d, d, M, d, zeros_d, d, d, G, stream);        // G = A A^T
+    if (e != cudaSuccess) return e;
+    if ((e = transpose_launch(M, d, d, AT, stream)) != cudaSuccess) return e;               // AT = A^T
+    if ((e = dot_bias_scores_launch(G, d, d, AT, d, zeros_d, d, d, T, stream)) != cudaSuccess) return e;  // T = G A
+    axpby_kernel<<<256, 256, 0, stream>>>(1.5f, M, -0.5f, T, nn, M);
+    count_launch();
+  }
+  return cudaGetLastError();
 }
 
 }  // namespace nvdb_b200

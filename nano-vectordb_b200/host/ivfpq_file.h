@@ -5,8 +5,9 @@
 // nvdb_b200_ivfpq_export behind a 64-byte little-endian header, in the style of the reference's own vecbin / gtbin headers
 // (include/nvdb/vecbin_format.h:17-29):
 //
-//   u64 magic "NVDBIVF1" | u32 version=1 | u32 dim | u32 nlist | u32 pq_m | u32 pq_bits=8 | u32 reserved | u64 n | pad to 64
+//   u64 magic "NVDBIVF1" | u32 version=1 | u32 dim | u32 nlist | u32 pq_m | u32 pq_bits=8 | u32 has_opq | u64 n | pad to 64
 //   f32 coarse[nlist*dim] | f32 codebooks[pq_m*256*(dim/pq_m)] | u32 list_off[nlist+1] | u32 ids[n] | u8 codes[n*pq_m]
+//   | f32 rotation[dim*dim] (only when has_opq = 1: the OPQ rotation R, x' = x R)
 #pragma once
 #include <cstdint>
 #include <cstring>
@@ -22,7 +23,7 @@ namespace nvdb {
 #pragma pack(push, 1)
 struct IvfPqFileHeader {
   uint64_t magic;
-  uint32_t version, dim, nlist, pq_m, pq_bits, reserved0;
+  uint32_t version, dim, nlist, pq_m, pq_bits, has_opq;
   uint64_t n;
   uint8_t reserved[64 - 40];
 };
@@ -36,6 +37,7 @@ struct IvfPqArrays {
   std::vector<float> coarse, codebooks;
   std::vector<uint32_t> list_off, ids;
   std::vector<uint8_t> codes;
+  std::vector<float> rotation;  // empty without OPQ
   void resize() {
     coarse.resize((size_t)nlist * dim);
     codebooks.resize((size_t)pq_m * 256 * (dim / pq_m));
@@ -54,6 +56,13 @@ inline void ivfpq_save(const nvdb_b200_ivfpq* ivf, const std::string& path) {
   if (nvdb_b200_ivfpq_export(ivf, a.coarse.data(), a.codebooks.data(), a.list_off.data(), a.ids.data(), a.codes.data()) !=
       NVDB_B200_OK)
     throw std::runtime_error(nvdb_b200_ivfpq_last_error(ivf));
+  int has_rot = 0;
+  if (nvdb_b200_ivfpq_rotation(ivf, nullptr, &has_rot) != NVDB_B200_OK) throw std::runtime_error(nvdb_b200_ivfpq_last_error(ivf));
+  if (has_rot) {
+    a.rotation.resize((size_t)a.dim * a.dim);
+    if (nvdb_b200_ivfpq_rotation(ivf, a.rotation.data(), &has_rot) != NVDB_B200_OK)
+      throw std::runtime_error(nvdb_b200_ivfpq_last_error(ivf));
+  }
   std::ofstream out(path, std::ios::binary);
   if (!out) throw std::runtime_error("Failed to open output: " + path);
   IvfPqFileHeader h{};
@@ -63,6 +72,7 @@ inline void ivfpq_save(const nvdb_b200_ivfpq* ivf, const std::string& path) {
   h.nlist = a.nlist;
   h.pq_m = a.pq_m;
   h.pq_bits = 8;
+  h.has_opq = has_rot ? 1u : 0u;
   h.n = a.n;
   auto put = [&](const void* p, size_t nbytes) { out.write(reinterpret_cast<const char*>(p), (std::streamsize)nbytes); };
   put(&h, sizeof(h));
@@ -71,6 +81,7 @@ inline void ivfpq_save(const nvdb_b200_ivfpq* ivf, const std::string& path) {
   put(a.list_off.data(), a.list_off.size() * 4);
   put(a.ids.data(), a.ids.size() * 4);
   put(a.codes.data(), a.codes.size());
+  if (has_rot) put(a.rotation.data(), a.rotation.size() * 4);
   if (!out) throw std::runtime_error("Write failed: " + path);
 }
 
@@ -93,11 +104,20 @@ inline nvdb_b200_ivfpq* ivfpq_load(const std::string& path, int device) {
   get(a.list_off.data(), a.list_off.size() * 4);
   get(a.ids.data(), a.ids.size() * 4);
   get(a.codes.data(), a.codes.size());
+  if (h.has_opq) {
+    a.rotation.resize((size_t)a.dim * a.dim);
+    get(a.rotation.data(), a.rotation.size() * 4);
+  }
   if (!in) throw std::runtime_error("IVF-PQ index file truncated: " + path);
   nvdb_b200_ivfpq* ivf = nullptr;
   if (nvdb_b200_ivfpq_import(device, a.dim, a.nlist, a.pq_m, a.n, a.coarse.data(), a.codebooks.data(), a.list_off.data(),
                              a.ids.data(), a.codes.data(), &ivf) != NVDB_B200_OK)
     throw std::runtime_error(nvdb_b200_ivfpq_last_error(nullptr));
+  if (h.has_opq && nvdb_b200_ivfpq_set_rotation(ivf, a.rotation.data()) != NVDB_B200_OK) {
+    const std::string msg = nvdb_b200_ivfpq_last_error(ivf);
+    nvdb_b200_ivfpq_destroy(ivf);
+    throw std::runtime_error(msg);
+  }
   return ivf;
 }
 

@@ -139,8 +139,10 @@ int main(int argc, char** argv) {
       std::cerr << "Index does not belong to this base (n/d)\n";
       return 5;
     }
+    int has_opq = 0;
+    nvdb_b200_ivfpq_rotation(ivf, nullptr, &has_opq);
     std::cout << "IVF nlist=" << nlist << " nprobe=" << nprobe << " | d=" << d << " k=" << k << " Q=" << Q << " | pq_m=" << pq_m
-              << "\n";
+              << (has_opq ? " | pretransform=OPQ" : "") << "\n";
 
     if (gt.empty() && !ann_only) {  // exact neighbours from the flat scan (see the header comment)
       gt.resize((size_t)Q * k);

@@ -1,12 +1,13 @@
 // nvdb_ivfpq_build (B200) — IVF-PQ index construction on the GPU with the reference tool's command line.
 //
 //   nvdb_ivfpq_build <base.vecbin> <out.nvdbivf>
-//   Env: IVF_NLIST=4096  IVF_TRAIN=200000  PQ_M=48  PQ_BITS=8  USE_OPQ=0  (+ IVF_NITER=25, IVF_SEED=1234, IVF_GPU=0)
+//   Env: IVF_NLIST=4096  IVF_TRAIN=200000  PQ_M=48  PQ_BITS=8  USE_OPQ=0  OPQ_NITER=25  (+ IVF_NITER=25, IVF_SEED=1234, IVF_GPU=0)
 //
 // Same argv, environment variables, messages and exit codes as apps/nvdb_ivfpq_build.cpp:24-64 (1 usage, 2 "PQ_M must
 // divide dim"). The reference builds faiss::IndexIVFPQ on the host cores and writes FAISS' own file format; here the
 // base goes to the device once and nvdb_b200_ivfpq_build trains + encodes there (kmeans.cu / ivfpq.cu); the index is
-// written in this repo's own container (ivfpq_file.h). USE_OPQ=1 is refused (exit 3): the OPQ rotation is not built.
+// written in this repo's own container (ivfpq_file.h). USE_OPQ=1 trains the OPQ rotation on the device as well
+// (OPQ_NITER rounds, the reference's default 25: apps/nvdb_ivfpq_build.cpp:84).
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
@@ -29,7 +30,8 @@ int main(int argc, char** argv) {
               << "  IVF_TRAIN=200000\n"
               << "  PQ_M=48            (must divide dim)\n"
               << "  PQ_BITS=8          (8 only)\n"
-              << "  USE_OPQ=0          (1 is not supported by the GPU builder)\n"
+              << "  USE_OPQ=0          (0/1; optional)\n"
+              << "  OPQ_NITER=25\n"
               << "  IVF_NITER=25  IVF_SEED=1234  IVF_GPU=0\n";
     return 1;
   }
@@ -49,17 +51,14 @@ int main(int argc, char** argv) {
       std::cerr << "PQ_M must divide dim. dim=" << d << " PQ_M=" << pq_m << "\n";
       return 2;
     }
-    if (use_opq) {
-      std::cerr << "USE_OPQ=1 is not supported by the GPU builder (no OPQ rotation)\n";
-      return 3;
-    }
     std::cout << "Base: N=" << N << " d=" << d << " dtype=" << base.dtype() << " nlist=" << nlist << " ntrain=" << train_n
               << " PQ_M=" << pq_m << " PQ_BITS=" << pq_bits << " USE_OPQ=" << use_opq << "\n";
     nvdb::FlatIndexCuda flat(&base, getenv_int("IVF_GPU", 0));
     nvdb_b200_ivfpq* ivf = nullptr;
     const auto t0 = std::chrono::steady_clock::now();
-    const int rc = nvdb_b200_ivfpq_build(flat.handle(), (uint32_t)nlist, (uint32_t)pq_m, (uint32_t)pq_bits, train_n,
-                                         getenv_int("IVF_NITER", 25), (uint64_t)getenv_int("IVF_SEED", 1234), &ivf);
+    const int rc = nvdb_b200_ivfpq_build_opq(flat.handle(), (uint32_t)nlist, (uint32_t)pq_m, (uint32_t)pq_bits, train_n,
+                                             getenv_int("IVF_NITER", 25), use_opq ? getenv_int("OPQ_NITER", 25) : 0,
+                                             (uint64_t)getenv_int("IVF_SEED", 1234), &ivf);
     if (rc != NVDB_B200_OK) {
       std::cerr << "Error: " << nvdb_b200_ivfpq_last_error(nullptr) << "\n";
       return 10;
@@ -68,7 +67,7 @@ int main(int argc, char** argv) {
     std::cout << "Train+Add: " << std::chrono::duration<double>(t1 - t0).count() << " s\n";
     nvdb::ivfpq_save(ivf, out_path);
     nvdb_b200_ivfpq_destroy(ivf);
-    std::cout << "Saved IVF-PQ index: " << out_path << "\n";
+    std::cout << "Saved IVF-" << (use_opq ? "OPQ-PQ" : "PQ") << " index: " << out_path << "\n";
     return 0;
   } catch (const std::exception& e) {
     std::cerr << "Error: " << e.what() << "\n";

@@ -156,3 +156,48 @@ def recall_at_k(found: np.ndarray, truth: np.ndarray) -> float:
     """fraction of the true top-k present anywhere in `found` (candidate recall when found has R > k columns)"""
     k = truth.shape[1]
     return float(np.mean([len(set(f.tolist()) & set(t.tolist())) / k for f, t in zip(found, truth)]))
+
+
+def opq_train(x: np.ndarray, pq_m: int, opq_niter: int, seed: int, pq_iters_first=6, pq_iters_next=1):
+    """Non-parametric OPQ (Ge, He, Ke, Sun, CVPR 2013; what faiss::OPQMatrix implements and the reference switches on with
+    USE_OPQ=1, apps/nvdb_ivfpq_build.cpp:78-91): alternate PQ of X R (warm-started Lloyd steps, the build's seeds
+    seed+1000+m) with the orthogonal Procrustes solution R = U V^T of X^T Y = U S V^T. Returns (R, quantisation error
+    per round). float64; the device version uses Newton-Schulz instead of an SVD for the polar factor."""
+    x = np.asarray(x, np.float64)
+    n, d = x.shape
+    dsub = d // pq_m
+    R = np.eye(d)
+    cbs = [None] * pq_m
+    errs = []
+    for it in range(opq_niter):
+        xr = x @ R
+        y = np.empty_like(xr)
+        for m in range(pq_m):
+            sub = xr[:, m * dsub:(m + 1) * dsub]
+            if it == 0:
+                cbs[m] = kmeans(sub, 256, pq_iters_first, seed + 1000 + m)
+            else:
+                for _ in range(pq_iters_next):
+                    a = nearest(sub, cbs[m])
+                    counts = np.bincount(a, minlength=256)
+                    sums = np.zeros_like(cbs[m])
+                    np.add.at(sums, a, sub)
+                    nz = counts > 0
+                    cbs[m][nz] = sums[nz] / counts[nz, None]
+            y[:, m * dsub:(m + 1) * dsub] = cbs[m][nearest(sub, cbs[m])]
+        errs.append(float(((xr - y) ** 2).sum() / n))
+        u, _, vt = np.linalg.svd(x.T @ y)
+        R = u @ vt
+    return R, errs
+
+
+def pq_error(x: np.ndarray, pq_m: int, niter: int, seed: int) -> float:
+    """mean squared PQ reconstruction error of rows x with freshly trained codebooks"""
+    x = np.asarray(x, np.float64)
+    dsub = x.shape[1] // pq_m
+    err = 0.0
+    for m in range(pq_m):
+        sub = x[:, m * dsub:(m + 1) * dsub]
+        cb = kmeans(sub, 256, niter, seed + m)
+        err += float(((sub - cb[nearest(sub, cb)]) ** 2).sum())
+    return err / len(x)

@@ -11,7 +11,7 @@ numbers therefore describe THIS data, only their shape (monotone in nprobe, thre
 comparable with the reference's table.
 
   NVDB_IVF_ROWS (1,000,000)  NVDB_IVF_DIM (768)  NVDB_IVF_NLIST (4096)  NVDB_IVF_M (64)  NVDB_IVF_TRAIN (200000)
-  NVDB_IVF_NITER (25)  NVDB_IVF_Q (1000)  NVDB_IVF_LATENT (24)
+  NVDB_IVF_NITER (25)  NVDB_IVF_Q (1000)  NVDB_IVF_LATENT (24)  NVDB_IVF_OPQ (0)
 """
 import importlib
 import json
@@ -35,6 +35,7 @@ M = int(os.environ.get("NVDB_IVF_M", 64))
 NTRAIN = int(os.environ.get("NVDB_IVF_TRAIN", 200_000))
 NITER = int(os.environ.get("NVDB_IVF_NITER", 25))
 Q = int(os.environ.get("NVDB_IVF_Q", 1000))
+OPQ = int(os.environ.get("NVDB_IVF_OPQ", 0))  # OPQ rounds (the reference's USE_OPQ=1 / OPQ_NITER=25), 0 = plain IVF-PQ
 K = 10
 dev = torch.device("cuda", 0)
 g = torch.Generator(device=dev)
@@ -69,9 +70,9 @@ torch.cuda.synchronize()
 
 idx = nv.FlatIndexCuda.from_device(base.data_ptr(), None, nv.F16, N, D, keepalive=base)
 t0 = time.perf_counter()
-ivf = nv.IvfPqIndex(idx, nlist=NLIST, pq_m=M, ntrain=NTRAIN, niter=NITER, seed=1234)
+ivf = nv.IvfPqIndex(idx, nlist=NLIST, pq_m=M, ntrain=NTRAIN, niter=NITER, seed=1234, opq_niter=OPQ)
 build_s = time.perf_counter() - t0
-print(json.dumps({"what": "build", "rows": N, "dim": D, "nlist": NLIST, "pq_m": M, "ntrain": NTRAIN, "niter": NITER,
+print(json.dumps({"what": "build", "rows": N, "dim": D, "nlist": NLIST, "pq_m": M, "ntrain": NTRAIN, "niter": NITER, "opq_niter": OPQ,
                   "build_s": round(build_s, 2), "index_MB": round(ivf.index_bytes / 1e6, 1),
                   "base_MB": round(N * D * 2 / 1e6, 1)}), flush=True)
 

@@ -96,8 +96,6 @@ def test_ivf_tools_usage_and_input_checks_without_gpu(tools, oracle, tmp_path):
     write_vecbin(tmp_path / "b.vecbin", F32, f)
     r = run(tools / "nvdb_ivfpq_build", tmp_path / "b.vecbin", tmp_path / "o.ivf", env={"PQ_M": "5"})
     assert r.returncode == 2 and "PQ_M must divide dim. dim=16 PQ_M=5" in r.stderr
-    r = run(tools / "nvdb_ivfpq_build", tmp_path / "b.vecbin", tmp_path / "o.ivf", env={"PQ_M": "4", "USE_OPQ": "1"})
-    assert r.returncode == 3
     write_raw12(tmp_path / "q8.raw12", f[:3, :8])
     r = run(tools / "nvdb_ivf_eval", tmp_path / "b.vecbin", tmp_path / "missing.ivf", tmp_path / "q8.raw12", 5)
     assert r.returncode == 3 and "Dim mismatch: base.dim=16 query.dim=8" in r.stderr
@@ -151,3 +149,13 @@ def test_ivfpq_build_then_eval_reports_recall_and_latencies(tools, oracle, tmp_p
     r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
             env={"EVAL_MODE": "ann_only"})
     assert r.returncode == 0 and f"Recall@{k}: N/A (EVAL_MODE=ann_only)" in r.stdout
+    # USE_OPQ=1: rotation trained on the device, stored in the index file, announced by the evaluator like the reference
+    r = run(tools / "nvdb_ivfpq_build", tmp_path / "base.vecbin", tmp_path / "opq.nvdbivf",
+            env={"IVF_NLIST": "64", "IVF_TRAIN": "10000", "PQ_M": "16", "IVF_NITER": "8", "USE_OPQ": "1", "OPQ_NITER": "6"})
+    assert r.returncode == 0 and "USE_OPQ=1" in r.stdout and "Saved IVF-OPQ-PQ index" in r.stdout, r.stderr
+    assert (tmp_path / "opq.nvdbivf").stat().st_size == (tmp_path / "idx.nvdbivf").stat().st_size + d * d * 4
+    r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "opq.nvdbivf", tmp_path / "q.raw12", k,
+            env={"GT_PATH": str(tmp_path / "q.gtbin"), "IVF_NPROBE": "16", "REFINE_K": "50"})
+    assert r.returncode == 0 and "| pretransform=OPQ" in r.stdout, r.stderr
+    res = dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:])
+    assert float(res["recall"]) > 0.8

@@ -66,3 +66,19 @@ def test_encode_group_search_invariants():
     rec_np = [ref.recall_at_k(ref.search(q, coarse, cb, off, ids, gcodes, p, 400)[0][:, :400], truth) for p in (1, 4, 16)]
     assert rec_np[0] <= rec_np[1] + 1e-9 <= rec_np[2] + 2e-9
     assert rec_np[-1] > 0.9
+
+
+def correlated(n, d, seed):
+    """rows whose energy is concentrated in a few correlated directions: plain PQ wastes codes, OPQ re-balances them"""
+    rng = np.random.default_rng(seed)
+    mix = np.linalg.qr(rng.standard_normal((d, d)))[0]
+    scales = np.geomspace(4.0, 0.05, d)
+    return ((rng.standard_normal((n, d)) * scales) @ mix).astype(np.float32)
+
+
+def test_opq_rotation_is_orthogonal_and_reduces_quantisation_error():
+    x = correlated(4000, 16, 3)
+    R, errs = ref.opq_train(x, 4, 8, 5)
+    assert np.allclose(R.T @ R, np.eye(16), atol=1e-9)
+    assert errs[-1] < 0.8 * errs[0], errs          # PQ error of X R falls over the rounds
+    assert ref.pq_error(x @ R, 4, 6, 9) < 0.85 * ref.pq_error(x, 4, 6, 9)
