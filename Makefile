@@ -31,6 +31,7 @@ HOST_BINS := $(BINDIR)/nvdb_bench $(BINDIR)/nvdb_gt_build $(BINDIR)/nvdb_convert
 HOST_CXX  := $(CXX) -std=c++17 -O2 -fopenmp -Iinclude -I$(PKG)/host
 HOST_LD   := -L$(LIBDIR) -lnvdb_b200 -Wl,-rpath,'$$ORIGIN/../lib' -lpthread
 host: lib $(HOST_BINS)
+$(filter-out $(BINDIR)/nvdb_quantize_i8,$(HOST_BINS)): | $(LIBDIR)/libnvdb_b200.so
 
 $(BINDIR)/nvdb_bench: $(PKG)/host/nvdb_bench.cpp $(HOST_HDRS)
 	@mkdir -p $(BINDIR)
