@@ -253,7 +253,8 @@ def run_ours(args):
     q_host = q_dev.cpu().numpy()
     out_ids = torch.empty((1, TOPK), dtype=torch.int64, device=dev)
     out_sc = torch.empty((1, TOPK), dtype=torch.float32, device=dev)
-    sharded = nv.ShardedFlatIndex(idx, dev) if world > 1 else None   # local scan -> ONE packed all-gather -> merge
+    # local scan -> exchange + merge: ONE kernel over NVLink peer memory ("peer"), or all-gather + merge ("nccl")
+    sharded = nv.ShardedFlatIndex(idx, dev, exchange=os.environ.get("NVDB_B200_EXCHANGE", "auto")) if world > 1 else None
 
     def step_device(i):
         if world > 1:
@@ -331,6 +332,13 @@ def run_ours(args):
     ids0, sc0 = (idx.search_topk_dot(q_host[0], TOPK) if world == 1 else (None, None))
     if world == 1:
         assert int(ids0[0]) == qrows[0], f"self-query check failed: {ids0[0]} vs {qrows[0]}"
+    else:   # the row lives on ONE shard: every rank must find it through the exchange
+        for i in (0, 1, NQ_POOL - 1):
+            with torch.cuda.stream(stream):
+                g_ids, _ = sharded.search(q_dev[i:i + 1], TOPK)
+            stream.synchronize()
+            assert int(g_ids[0, 0]) == qrows[i], f"rank {rank}: sharded self-query check failed: {int(g_ids[0, 0])} vs {qrows[i]}"
+        assert sharded.exchange_status() == 0, "peer exchange timed out"
 
     peak, peak_src = measured_peaks()
     kern_ms = scan_ms / max(calls, 1)
@@ -342,11 +350,13 @@ def run_ours(args):
         "config": {"workload": f"FP16 exact flat-scan top-{TOPK}, {n_rows}x{DIM} per GPU, batch 1 (BASELINE.json configs[1])",
                    "rows_per_gpu": n_rows, "dim": DIM, "k": TOPK, "batch": 1, "base_dtype": "f16",
                    "l2": f"base ({nbytes / 1e9:.2f} GB) is larger than L2 (126 MB); queries cycle through {NQ_POOL} rows",
-                   "parallelism": f"row-shard x{world}, all-gather + merge" if world > 1 else "single GPU"},
+                   "parallelism": (f"row-shard x{world}, " + ("fused peer-memory exchange + merge kernel (NVLink stores, no NCCL)"
+                                                                if sharded.exchange == "peer" else "NCCL all-gather + merge kernel"))
+                   if world > 1 else "single GPU"},
         "qps": qps,
         "e2e": {"value": e2e_value, "unit": "GB/s", "qps": K / e2e_s, "ms_per_step": e2e_s / K * 1e3,
                 "h2d_bytes_per_step": DIM * 4, "d2h_bytes_per_step": TOPK * 12,
-                "api": "nvdb_b200_search (host buffers)" if world == 1 else "ShardedFlatIndex.search: host query -> H2D -> local scan -> packed all_gather -> merge -> D2H"},
+                "api": "nvdb_b200_search (host buffers)" if world == 1 else f"ShardedFlatIndex.search: host query -> H2D -> local scan -> {sharded.exchange} exchange + merge -> D2H"},
         "gpu_launches": int(l1 - l0),
         "roofline": {"bound": "hbm", "kernel": "scan_gemv_tma_kernel<f16,1>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,

@@ -118,6 +118,37 @@ int nvdb_b200_merge_topk_device(int device, const uint64_t* ids_dev, const float
 int nvdb_b200_merge_topk_packed_device(int device, const void* packed_dev, uint32_t nlists, uint32_t nq, uint32_t k,
                                        uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
 
+/* ---- exchange over NVLink peer memory (row-sharded index, one process or one handle per GPU) ----------------------
+ * The step after the local scans of a row-sharded index (the reference's serial merge of its row
+ * blocks, src/flat_index_pool.cpp:212-214) as ONE kernel per rank: push the packed local result (layout of
+ * nvdb_b200_merge_topk_packed_device) into every peer's window with NVLink stores, publish a flag, wait for the peers'
+ * flags, merge world*k candidates per query under (score desc, id asc). No NCCL call and no second launch.
+ *   create   allocates this rank's window (slot_bytes >= 8 * (nq*k + (nq*k+1)/2) of the largest call);
+ *   connect  maps the peers: `handles` = world * NVDB_B200_IPC_HANDLE_BYTES bytes gathered from every rank's
+ *            _ipc_handle (ranks in other processes), or `windows` = world device pointers from _window (same process);
+ *   merge    phases 3 = push + wait + merge in one launch (every rank must call it, all calls of one exchange on one
+ *            stream, same order on every rank); phases 1 / 2 split it into two launches (logical shards sharing one
+ *            GPU: push all ranks first, then merge all ranks);
+ *   status   0 = fine, 1 = a wait timed out (NVDB_B200_XCHG_TIMEOUT_MS, default 30000): the outputs of that call were
+ *            filled with the padding values (UINT64_MAX / -inf) and later calls fail the same way. Synchronises. */
+#define NVDB_B200_IPC_HANDLE_BYTES 64
+typedef struct nvdb_b200_exchange nvdb_b200_exchange;
+int nvdb_b200_exchange_create(int device, uint32_t world, uint32_t rank, uint64_t slot_bytes, nvdb_b200_exchange** out);
+int nvdb_b200_exchange_ipc_handle(nvdb_b200_exchange* x, unsigned char* handle64);
+int nvdb_b200_exchange_window(nvdb_b200_exchange* x, void** window_dev, uint64_t* window_bytes);
+int nvdb_b200_exchange_connect(nvdb_b200_exchange* x, const unsigned char* handles, void* const* windows);
+int nvdb_b200_exchange_merge(nvdb_b200_exchange* x, const void* local_packed_dev, uint32_t nq, uint32_t k,
+                             uint64_t* out_ids_dev, float* out_scores_dev, int phases, void* stream);
+int nvdb_b200_exchange_status(nvdb_b200_exchange* x, uint32_t* status);
+const char* nvdb_b200_exchange_last_error(const nvdb_b200_exchange* x);
+int nvdb_b200_exchange_destroy(nvdb_b200_exchange* x);
+/* The whole step of one rank of a row-sharded index: local scan of `idx` (NULL = this rank's shard is empty) + exchange
+ * + merge; out_* receive the top-k over ALL shards on every rank. Single-query / single-pass streaming scans do it in
+ * ONE launch (the scan's last CTA pushes its list to the peers, waits for theirs and merges); other shapes run the
+ * scan into the exchange's staging buffer and then the exchange kernel. Same calling rules as nvdb_b200_exchange_merge. */
+int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_dev, uint32_t nq,
+                                     uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+
 /* Kernel-selection knobs for A/B measurements and tests; results never depend on them. Defaults can also be set with
  * the environment variables NVDB_B200_MMA_SEED / NVDB_B200_GEMV_CTAS / NVDB_B200_MMA_2CTA at index creation. */
 enum {

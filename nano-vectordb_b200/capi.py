@@ -76,6 +76,15 @@ _sig = {
     "nvdb_b200_ivfpq_search": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp]),
     "nvdb_b200_ivfpq_search_device": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_ivfpq_search_refine": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
+    "nvdb_b200_exchange_create": (_i, [_i, _u32, _u32, _u64, C.POINTER(_vp)]),
+    "nvdb_b200_exchange_ipc_handle": (_i, [_vp, _vp]),
+    "nvdb_b200_exchange_window": (_i, [_vp, C.POINTER(_vp), C.POINTER(_u64)]),
+    "nvdb_b200_exchange_connect": (_i, [_vp, _vp, _vp]),
+    "nvdb_b200_exchange_merge": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _i, _vp]),
+    "nvdb_b200_exchange_status": (_i, [_vp, C.POINTER(_u32)]),
+    "nvdb_b200_exchange_last_error": (C.c_char_p, [_vp]),
+    "nvdb_b200_exchange_destroy": (_i, [_vp]),
+    "nvdb_b200_search_exchange_device": (_i, [_vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_launch_count": (_u64, []),
     "nvdb_b200_index_profile": (_i, [_vp, _i]),
     "nvdb_b200_index_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_u32)]),
@@ -112,6 +121,78 @@ def merge_topk_device(device, ids_ptr, scores_ptr, nlists, nq, k, out_ids_ptr, o
 
 def merge_topk_packed_device(device, packed_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
     _check(lib.nvdb_b200_merge_topk_packed_device(device, packed_ptr, nlists, nq, k, out_ids_ptr, out_scores_ptr, stream))
+
+
+IPC_HANDLE_BYTES = 64
+XCHG_PUSH, XCHG_MERGE, XCHG_FUSED = 1, 2, 3
+
+
+class PeerExchange:
+    """One rank's end of the NVLink peer-memory exchange (include/nvdb_b200.h, csrc/exchange.cu): the window its
+    peers store their local top-k lists into, and the fused push + wait + merge kernel. `slot_bytes` bounds the packed
+    result of one call: 8 * (nq*k + (nq*k+1)//2)."""
+
+    def __init__(self, device: int, world: int, rank: int, slot_bytes: int):
+        h = _vp()
+        st = lib.nvdb_b200_exchange_create(device, world, rank, slot_bytes, C.byref(h))
+        if st != 0:
+            raise NvdbError(st, (lib.nvdb_b200_exchange_last_error(None) or b"").decode())
+        self._h = h
+        self.device, self.world, self.rank, self.slot_bytes = device, world, rank, slot_bytes
+
+    def _ck(self, st):
+        if st != 0:
+            raise NvdbError(st, (lib.nvdb_b200_exchange_last_error(self._h) or b"").decode())
+
+    def ipc_handle(self) -> bytes:
+        buf = (C.c_ubyte * IPC_HANDLE_BYTES)()
+        self._ck(lib.nvdb_b200_exchange_ipc_handle(self._h, buf))
+        return bytes(buf)
+
+    def window(self) -> int:
+        p, n = _vp(), _u64()
+        self._ck(lib.nvdb_b200_exchange_window(self._h, C.byref(p), C.byref(n)))
+        return int(p.value)
+
+    def connect(self, handles: bytes | None = None, windows=None):
+        """`handles`: world * 64 bytes, rank-major (peers in other processes); `windows`: world device pointers (peers
+        in this process)."""
+        if windows is not None:
+            arr = (_vp * self.world)(*[_vp(w) for w in windows])
+            self._ck(lib.nvdb_b200_exchange_connect(self._h, None, arr))
+        else:
+            if handles is not None and len(handles) != self.world * IPC_HANDLE_BYTES:
+                raise ValueError("handles must hold world * 64 bytes")
+            buf = None if handles is None else (C.c_ubyte * len(handles)).from_buffer_copy(handles)
+            self._ck(lib.nvdb_b200_exchange_connect(self._h, buf, None))
+
+    def merge(self, local_packed_ptr, nq, k, out_ids_ptr, out_scores_ptr, phases=XCHG_FUSED, stream=None):
+        self._ck(lib.nvdb_b200_exchange_merge(self._h, local_packed_ptr, nq, k, out_ids_ptr, out_scores_ptr, phases,
+                                              stream))
+
+    def search(self, index, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
+        """One rank's whole step: local scan of `index` (a FlatIndexCuda, or None for an empty shard) + exchange + merge
+        (nvdb_b200_search_exchange_device); one launch for single-pass streaming scans."""
+        ih = None if index is None else index._h
+        st = lib.nvdb_b200_search_exchange_device(ih, self._h, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream)
+        if st != 0:
+            raise NvdbError(st, (lib.nvdb_b200_last_error(ih) or lib.nvdb_b200_exchange_last_error(self._h) or b"").decode())
+
+    def status(self) -> int:
+        s = _u32()
+        self._ck(lib.nvdb_b200_exchange_status(self._h, C.byref(s)))
+        return int(s.value)
+
+    def close(self):
+        if self._h:
+            lib.nvdb_b200_exchange_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class FlatIndexCuda:

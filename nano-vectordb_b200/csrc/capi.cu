@@ -10,6 +10,7 @@
 
 #include "../../include/nvdb_b200.h"
 #include "common.cuh"
+#include "exchange.h"
 #include "scan.h"
 
 using namespace nvdb_b200;
@@ -711,8 +712,12 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
   return NVDB_B200_OK;
 }
 
+// `xchg` (row-sharded index): when the call is ONE pass with the fused merge, the scan's last CTA also runs the exchange
+// with the peer GPUs and d_out_* receive the merge over all shards (*tail_used = true); otherwise the call behaves as
+// without it and the caller runs the exchange kernel on the local result.
 int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
-                     float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
+                     float* d_out_scores, cudaStream_t stream, uint32_t* launches, nvdb_b200_exchange* xchg = nullptr,
+                     bool* tail_used = nullptr) {
   ScanPlan plan;
   int rc = plan_scan(idx, nq, k, &plan);
   if (rc) return rc;
@@ -745,6 +750,13 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   a.out_ids = nullptr;
   a.out_scores = nullptr;
   a.row_offset = idx->row_offset;
+  a.xchg = ScanXchg{};
+  if (tail_used) *tail_used = false;
+  if (xchg && fused && nq <= (uint32_t)plan.nq_template &&
+      (size_t)xchg->world * k * 12u + 8u <= (size_t)plan.stages * 32768u) {
+    exchange_begin_epoch(xchg, &a.xchg);
+    if (tail_used) *tail_used = true;
+  }
   if (fused) {
     const bool fresh = idx->d_ws[WS_GEMV_CTR] == nullptr;
     if ((rc = ensure_ws(idx, WS_GEMV_CTR, 256))) return rc;
@@ -944,6 +956,51 @@ int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
   return search_device_impl(idx, queries_dev, nq, k, out_ids_dev, out_scores_dev,
                             stream ? (cudaStream_t)stream : idx->stream, nullptr, nullptr);
+}
+
+int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_dev, uint32_t nq,
+                                     uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev, void* stream) {
+  if (!x) return fail(idx, NVDB_B200_ERR_ARG, "exchange is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!out_ids_dev || !out_scores_dev) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+  const size_t nk = (size_t)nq * k, words = nk + (nk + 1) / 2;
+  if (words * 8u > x->slot_bytes) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: packed result larger than the slot");
+  if (!x->connected && x->world > 1) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: exchange is not connected");
+  if (!idx)  // an empty shard contributes padding
+    return nvdb_b200_exchange_merge(x, nullptr, nq, k, out_ids_dev, out_scores_dev, 3, stream);
+  if (!queries_dev) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if (idx->device != x->device) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: index and exchange live on different devices");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  cudaStream_t s = stream ? (cudaStream_t)stream : idx->stream;
+  int path = idx->path;
+  if (path == NVDB_B200_PATH_AUTO)
+    path = (nq >= kMmaCrossover && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
+  uint64_t* l_ids = reinterpret_cast<uint64_t*>(x->staging);
+  float* l_scores = reinterpret_cast<float*>(l_ids + nk);
+  int rc;
+  if (path == NVDB_B200_PATH_GEMV) {
+    // one launch when the call is a single pass: the scan's last CTA exchanges and merges (scan_gemv.cu)
+    bool tail = false;
+    // the tail writes the global result to out_*; without it the local result goes to the staging buffer
+    ScanPlan plan;
+    if ((rc = plan_scan(idx, nq, k, &plan))) return rc;
+    const bool single = nq <= (uint32_t)plan.nq_template;
+    rc = gemv_search_impl(idx, queries_dev, nq, k, single ? out_ids_dev : l_ids, single ? out_scores_dev : l_scores, s,
+                          nullptr, single ? x : nullptr, &tail);
+    if (rc) return rc;
+    if (tail) return NVDB_B200_OK;
+    if (single) {  // not fused after all (knob off, large k): the local result sits in out_*, stage it
+      CK(cudaMemcpyAsync(l_ids, out_ids_dev, nk * 8u, cudaMemcpyDeviceToDevice, s), "stage ids");
+      CK(cudaMemcpyAsync(l_scores, out_scores_dev, nk * 4u, cudaMemcpyDeviceToDevice, s), "stage scores");
+    }
+  } else {
+    rc = search_device_impl(idx, queries_dev, nq, k, l_ids, l_scores, s, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  rc = nvdb_b200_exchange_merge(x, x->staging, nq, k, out_ids_dev, out_scores_dev, 3, s);
+  if (rc) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
+  return NVDB_B200_OK;
 }
 
 int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, uint32_t k, uint64_t* out_ids,

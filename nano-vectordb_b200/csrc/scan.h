@@ -10,6 +10,18 @@ namespace nvdb_b200 {
 constexpr int kScanRowsPerTile = 256;
 constexpr int kScanMaxQueriesPerPass = 8;
 
+// Optional tail of the streaming scan's last CTA: exchange the final lists with the peer GPUs and merge (exchange.cuh).
+constexpr uint32_t kXchgMaxWorld = 16;
+constexpr uint32_t kXchgHeaderBytes = 1024;  // flags[kXchgMaxWorld] (u32) at the start of every window
+struct ScanXchg {
+  unsigned char* win[kXchgMaxWorld];  // windows of all ranks as mapped in this process (win[rank] = own)
+  uint32_t* status;                   // sticky error word (own device): 1 = timed out waiting for a peer
+  unsigned long long timeout_ns;
+  size_t parity_off;                  // kXchgHeaderBytes + (epoch & 1) * world * slot_bytes
+  size_t slot_bytes;
+  uint32_t world = 0, rank = 0, epoch = 0;  // world == 0: no exchange
+};
+
 struct ScanArgs {
   const float* queries;  // [nq][dim] f32, device
   const float* scales;   // [n_rows] (i8) or null
@@ -20,6 +32,7 @@ struct ScanArgs {
   uint32_t* done_counter;  // zero-initialised; the merging CTA resets it
   uint64_t* out_ids;
   float* out_scores;
+  ScanXchg xchg;  // with the fused merge only, single pass: out_* receive the merge over ALL shards
   uint64_t row_offset;
   uint32_t n_rows;
   uint32_t dim;

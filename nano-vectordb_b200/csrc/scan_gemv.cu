@@ -20,6 +20,7 @@
 //
 // HBM traffic = the base payload once per pass (plus 4 B/row of scales for int8): the roofline of this kernel.
 #include "common.cuh"
+#include "exchange.cuh"
 #include "scan.h"
 #include "topk_select.cuh"
 #include "dot_chains.cuh"
@@ -234,15 +235,50 @@ scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a)
     for (uint32_t i = cnt + tid; i < bufn; i += kConsumers) buf[i] = 0ull;
     csync();
     bitonic_sort_desc(buf, bufn, tid, kConsumers, csync);
-    for (uint32_t j = tid; j < a.k; j += kConsumers) {
-      const uint64_t key = j < cnt ? buf[j] : 0ull;
-      const bool ok = key != 0ull;
-      a.out_ids[(size_t)qi * a.k + j] = ok ? a.row_offset + (uint64_t)key_row(key) : ~0ull;
-      a.out_scores[(size_t)qi * a.k + j] = ok ? key_score(key) : -INFINITY;
+    if (a.xchg.world == 0) {
+      for (uint32_t j = tid; j < a.k; j += kConsumers) {
+        const uint64_t key = j < cnt ? buf[j] : 0ull;
+        const bool ok = key != 0ull;
+        a.out_ids[(size_t)qi * a.k + j] = ok ? a.row_offset + (uint64_t)key_row(key) : ~0ull;
+        a.out_scores[(size_t)qi * a.k + j] = ok ? key_score(key) : -INFINITY;
+      }
+    } else {
+      // row-sharded index: this shard's list goes straight into slot `rank` of every GPU's window (NVLink stores),
+      // packed as [nq*k u64 ids][nq*k f32 scores] — no local copy, no exchange launch
+      const size_t slot = a.xchg.parity_off + (size_t)a.xchg.rank * a.xchg.slot_bytes;
+      const size_t nk = (size_t)a.nq * a.k;
+      for (uint32_t j = tid; j < a.k; j += kConsumers) {
+        const uint64_t key = j < cnt ? buf[j] : 0ull;
+        const bool ok = key != 0ull;
+        const uint64_t id = ok ? a.row_offset + (uint64_t)key_row(key) : ~0ull;
+        const float sc = ok ? key_score(key) : -INFINITY;
+        for (uint32_t r = 0; r < a.xchg.world; ++r) {
+          uint64_t* ids = reinterpret_cast<uint64_t*>(a.xchg.win[r] + slot);
+          ids[(size_t)qi * a.k + j] = id;
+          reinterpret_cast<float*>(ids + nk)[(size_t)qi * a.k + j] = sc;
+        }
+      }
     }
     csync();
   }
   if (tid == 0) *a.done_counter = 0u;  // ready for the next launch on this stream
+  if (a.xchg.world == 0) return;
+
+  // ---- exchange tail (exchange.cuh): publish this shard's flag in every window, wait for the peers' flags in the own
+  // window, merge world*k candidates per query under (score desc, global id asc). One CTA, the rest of the GPU is idle
+  // or already running the next kernel's prologue.
+  __shared__ uint32_t s_fail;
+  __threadfence_system();
+  csync();
+  if (tid < a.xchg.world) st_release_sys(reinterpret_cast<uint32_t*>(a.xchg.win[tid]) + a.xchg.rank, a.xchg.epoch);
+  const bool ok = xchg_wait(reinterpret_cast<const uint32_t*>(a.xchg.win[a.xchg.rank]), a.xchg.world, a.xchg.epoch,
+                            a.xchg.status, a.xchg.timeout_ns, tid, &s_fail, csync);
+  const uint32_t Lx = a.xchg.world * a.k;
+  const unsigned char* slots = a.xchg.win[a.xchg.rank] + a.xchg.parity_off;
+  for (uint32_t qi = 0; qi < a.nq; ++qi)
+    xchg_merge_query(slots, a.xchg.slot_bytes, (size_t)a.nq * a.k, a.xchg.world, a.k, qi, buf,
+                     reinterpret_cast<uint32_t*>(buf + Lx), a.out_ids + (size_t)qi * a.k, a.out_scores + (size_t)qi * a.k,
+                     ok, tid, (uint32_t)kConsumers, csync);
 }
 
 // ---- generic fallback for shapes the tensor map cannot describe (row bytes not a multiple of 16, or dims with a
