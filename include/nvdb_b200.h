@@ -148,6 +148,11 @@ int nvdb_b200_exchange_destroy(nvdb_b200_exchange* x);
  * scan into the exchange's staging buffer and then the exchange kernel. Same calling rules as nvdb_b200_exchange_merge. */
 int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_dev, uint32_t nq,
                                      uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+/* Host-buffer form (the shape of nvdb_b200_search; runs on the index's stream and synchronises it): every rank calls it
+ * — in one process, one host thread per device (nano-vectordb_b200/host/nvdb_bench.cpp). out_ids / out_scores may both
+ * be NULL on ranks that do not need the result. A timed-out exchange is an error (NVDB_B200_ERR_CUDA). */
+int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
+                              uint32_t k, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing);
 
 /* Kernel-selection knobs for A/B measurements and tests; results never depend on them. Defaults can also be set with
  * the environment variables NVDB_B200_MMA_SEED / NVDB_B200_GEMV_CTAS / NVDB_B200_MMA_2CTA at index creation. */

@@ -958,21 +958,13 @@ int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint
                             stream ? (cudaStream_t)stream : idx->stream, nullptr, nullptr);
 }
 
-int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_dev, uint32_t nq,
-                                     uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev, void* stream) {
-  if (!x) return fail(idx, NVDB_B200_ERR_ARG, "exchange is NULL");
-  if (nq == 0 || k == 0) return NVDB_B200_OK;
-  if (!out_ids_dev || !out_scores_dev) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+// scan + exchange + merge of one rank; idx->mu held by the caller
+static int search_exchange_impl(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_dev, uint32_t nq,
+                                uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev, cudaStream_t s) {
   const size_t nk = (size_t)nq * k, words = nk + (nk + 1) / 2;
   if (words * 8u > x->slot_bytes) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: packed result larger than the slot");
   if (!x->connected && x->world > 1) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: exchange is not connected");
-  if (!idx)  // an empty shard contributes padding
-    return nvdb_b200_exchange_merge(x, nullptr, nq, k, out_ids_dev, out_scores_dev, 3, stream);
-  if (!queries_dev) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
   if (idx->device != x->device) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: index and exchange live on different devices");
-  std::lock_guard<std::mutex> g(idx->mu);
-  CK(cudaSetDevice(idx->device), "cudaSetDevice");
-  cudaStream_t s = stream ? (cudaStream_t)stream : idx->stream;
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
     path = (nq >= kMmaCrossover && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
@@ -1000,6 +992,70 @@ int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x
   }
   rc = nvdb_b200_exchange_merge(x, x->staging, nq, k, out_ids_dev, out_scores_dev, 3, s);
   if (rc) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_dev, uint32_t nq,
+                                     uint32_t k, uint64_t* out_ids_dev, float* out_scores_dev, void* stream) {
+  if (!x) return fail(idx, NVDB_B200_ERR_ARG, "exchange is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!out_ids_dev || !out_scores_dev) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+  if (!idx) {  // an empty shard contributes padding
+    int rc = nvdb_b200_exchange_merge(x, nullptr, nq, k, out_ids_dev, out_scores_dev, 3, stream);
+    return rc ? fail(nullptr, rc, nvdb_b200_exchange_last_error(x)) : NVDB_B200_OK;
+  }
+  if (!queries_dev) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  return search_exchange_impl(idx, x, queries_dev, nq, k, out_ids_dev, out_scores_dev,
+                              stream ? (cudaStream_t)stream : idx->stream);
+}
+
+int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
+                              uint32_t k, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing) {
+  if (timing) *timing = nvdb_b200_timing{};
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (!x) return fail(idx, NVDB_B200_ERR_ARG, "exchange is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!queries_host) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if ((out_ids == nullptr) != (out_scores == nullptr)) return fail(idx, NVDB_B200_ERR_ARG, "give both output buffers or none");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  const size_t qbytes = (size_t)nq * idx->dim * 4, ibytes = (size_t)nq * k * 8, sbytes = (size_t)nq * k * 4;
+  int rc;
+  if ((rc = ensure_ws(idx, WS_QUERIES, qbytes))) return rc;
+  if ((rc = ensure_ws(idx, WS_OUT_IDS, ibytes + sbytes))) return rc;
+  if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
+  if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
+  cudaStream_t s = idx->stream;
+  uint64_t* d_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
+  float* d_scores = (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
+  std::memcpy(idx->h_pin[0], queries_host, qbytes);
+  if (timing) CK(cudaEventRecord(idx->ev[0], s), "event");
+  CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
+  if (timing) CK(cudaEventRecord(idx->ev[1], s), "event");
+  const uint64_t l0 = g_launches.load(std::memory_order_relaxed);
+  if ((rc = search_exchange_impl(idx, x, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s))) return rc;
+  if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
+  char* hp = (char*)idx->h_pin[1];
+  if (out_ids) CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
+  if (timing) CK(cudaEventRecord(idx->ev[3], s), "event");
+  CK(cudaStreamSynchronize(s), "search sync");
+  uint32_t st = 0;
+  if ((rc = nvdb_b200_exchange_status(x, &st))) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
+  if (st != 0) return fail(idx, NVDB_B200_ERR_CUDA, nvdb_b200_exchange_last_error(x));
+  if (out_ids) {
+    std::memcpy(out_ids, hp, ibytes);
+    std::memcpy(out_scores, hp + ibytes, sbytes);
+  }
+  if (timing) {
+    cudaEventElapsedTime(&timing->h2d_ms, idx->ev[0], idx->ev[1]);
+    cudaEventElapsedTime(&timing->kernel_ms, idx->ev[1], idx->ev[2]);
+    cudaEventElapsedTime(&timing->d2h_ms, idx->ev[2], idx->ev[3]);
+    cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
+    timing->kernel_launches = (uint32_t)(g_launches.load(std::memory_order_relaxed) - l0);  // process-wide: an upper bound
+    timing->path = (uint32_t)idx->path;
+  }
   return NVDB_B200_OK;
 }
 

@@ -29,11 +29,14 @@ double ms_since(std::chrono::steady_clock::time_point a, std::chrono::steady_clo
   return std::chrono::duration<double, std::milli>(b - a).count();
 }
 
-// Row shards on `gpus` devices of this process; per-shard searches run concurrently, results are merged on the host
-// under (score desc, id asc). One shard == plain FlatIndexCuda.
+// Row shards on `gpus` devices of this process; one host thread per device issues its shard's search, and the shards
+// exchange and merge their lists on the devices over NVLink peer memory (csrc/exchange.cu; the reference merges its
+// row blocks serially on the calling thread, src/flat_index_pool.cpp:212-214) — the host only receives shard 0's copy of
+// the final top-k. One shard == plain FlatIndexCuda.
 class ShardedIndex {
  public:
-  ShardedIndex(const nvdb::VectorDataset& base, int gpus, int path) {
+  // shard g lives on device g % ndev (ndev < gpus only with NVDB_BENCH_OVERSUBSCRIBE=1: several shards share a device)
+  ShardedIndex(const nvdb::VectorDataset& base, int gpus, int path, int ndev) {
     const uint64_t n = base.count(), per = (n + gpus - 1) / gpus;
     const size_t row_bytes = (size_t)base.dim() * nvdb::bytes_per_elem(base.dtype());
     for (int g = 0; g < gpus; ++g) {
@@ -42,13 +45,15 @@ class ShardedIndex {
       nvdb_b200_index* h = nullptr;
       const char* payload = static_cast<const char*>(base.data_ptr()) + r0 * row_bytes;
       const float* scales = base.scales_ptr() ? base.scales_ptr() + r0 : nullptr;
-      nvdb::detail::check(nvdb_b200_index_create(payload, scales, base.dtype(), nr, base.dim(), g, r0, &h), nullptr);
+      nvdb::detail::check(nvdb_b200_index_create(payload, scales, base.dtype(), nr, base.dim(), g % ndev, r0, &h), nullptr);
       nvdb::detail::check(nvdb_b200_index_set_path(h, path), h);
       shards_.push_back(h);
+      devices_.push_back(g % ndev);
     }
     n_ = n;
   }
   ~ShardedIndex() {
+    drop_exchange();
     for (auto* h : shards_) nvdb_b200_index_destroy(h);
   }
   // ids/scores: nq*k, padded like nvdb_b200_search
@@ -61,37 +66,52 @@ class ShardedIndex {
       nvdb::detail::check(nvdb_b200_search(shards_[0], q, nq, k, ids.data(), sc.data(), t0), shards_[0]);
       return;
     }
-    tmp_ids_.resize(S * nk);
-    tmp_sc_.resize(S * nk);
+    ensure_exchange(8 * (nk + (nk + 1) / 2));
     std::vector<std::thread> th;
     std::vector<int> rc(S, 0);
     std::vector<nvdb_b200_timing> tt(S);
     for (size_t s = 0; s < S; ++s)
-      th.emplace_back([&, s] { rc[s] = nvdb_b200_search(shards_[s], q, nq, k, &tmp_ids_[s * nk], &tmp_sc_[s * nk], &tt[s]); });
+      th.emplace_back([&, s] {
+        rc[s] = nvdb_b200_search_exchange(shards_[s], xchg_[s], q, nq, k, s == 0 ? ids.data() : nullptr,
+                                          s == 0 ? sc.data() : nullptr, &tt[s]);
+      });
     for (auto& x : th) x.join();
     for (size_t s = 0; s < S; ++s) nvdb::detail::check(rc[s], shards_[s]);
     if (t0) *t0 = tt[0];
-    std::vector<std::pair<float, uint64_t>> c;
-    for (uint32_t qi = 0; qi < nq; ++qi) {
-      c.clear();
-      for (size_t s = 0; s < S; ++s)
-        for (uint32_t j = 0; j < k; ++j) {
-          const uint64_t id = tmp_ids_[s * nk + (size_t)qi * k + j];
-          if (id != UINT64_MAX) c.emplace_back(tmp_sc_[s * nk + (size_t)qi * k + j], id);
-        }
-      std::sort(c.begin(), c.end(), [](const auto& a, const auto& b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
-      for (uint32_t j = 0; j < k; ++j) {
-        ids[(size_t)qi * k + j] = j < c.size() ? c[j].second : UINT64_MAX;
-        sc[(size_t)qi * k + j] = j < c.size() ? c[j].first : -INFINITY;
-      }
-    }
   }
   size_t shards() const { return shards_.size(); }
 
  private:
+  void drop_exchange() {
+    for (auto* x : xchg_) nvdb_b200_exchange_destroy(x);
+    xchg_.clear();
+    slot_bytes_ = 0;
+  }
+  // windows of all shards, mapped into each other by plain device pointers (one process)
+  void ensure_exchange(size_t need) {
+    if (need <= slot_bytes_) return;
+    drop_exchange();
+    size_t slot = 1 << 16;
+    while (slot < need) slot <<= 1;
+    const uint32_t S = (uint32_t)shards_.size();
+    std::vector<void*> wins(S, nullptr);
+    for (uint32_t s = 0; s < S; ++s) {
+      nvdb_b200_exchange* x = nullptr;
+      if (nvdb_b200_exchange_create(devices_[s], S, s, slot, &x) != NVDB_B200_OK)
+        throw std::runtime_error(std::string("exchange_create: ") + nvdb_b200_exchange_last_error(nullptr));
+      xchg_.push_back(x);
+      nvdb_b200_exchange_window(x, &wins[s], nullptr);
+    }
+    for (uint32_t s = 0; s < S; ++s)
+      if (nvdb_b200_exchange_connect(xchg_[s], nullptr, wins.data()) != NVDB_B200_OK)
+        throw std::runtime_error(std::string("exchange_connect: ") + nvdb_b200_exchange_last_error(xchg_[s]));
+    slot_bytes_ = slot;
+  }
+
   std::vector<nvdb_b200_index*> shards_;
-  std::vector<uint64_t> tmp_ids_;
-  std::vector<float> tmp_sc_;
+  std::vector<int> devices_;
+  std::vector<nvdb_b200_exchange*> xchg_;
+  size_t slot_bytes_ = 0;
   uint64_t n_ = 0;
 };
 
@@ -150,10 +170,11 @@ int main(int argc, char** argv) {
     int ndev = 0;
     nvdb::detail::check(nvdb_b200_device_count(&ndev), nullptr);
     if (gpus <= 0) gpus = ndev;
-    if (gpus > ndev) throw std::runtime_error("gpus=" + std::to_string(gpus) + " but only " + std::to_string(ndev) + " CUDA devices");
+    const char* over = std::getenv("NVDB_BENCH_OVERSUBSCRIBE");
+    if (gpus > ndev && !(over && over[0] == '1')) throw std::runtime_error("gpus=" + std::to_string(gpus) + " but only " + std::to_string(ndev) + " CUDA devices");
     std::cout << "mode=" << mode << " gpus=" << gpus << "\n";
     const auto tu0 = std::chrono::steady_clock::now();
-    ShardedIndex index(base, gpus, path);
+    ShardedIndex index(base, gpus, path, ndev);
     const double upload_ms = ms_since(tu0, std::chrono::steady_clock::now());
     std::cout << "Base count=" << base.count() << " dim=" << base.dim() << " | Query count=" << query.count()
               << " | k=" << k << " | warmup=" << warmup << "\n";

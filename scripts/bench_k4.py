@@ -44,7 +44,7 @@ with torch.cuda.stream(stream):
     for i, r in enumerate(qrows):
         nv.synth_fill_device(local_rank, nv.F32, 1, DIM, SEED, r, q[i].data_ptr(), None, stream.cuda_stream)
 stream.synchronize()
-sharded = nv.ShardedFlatIndex(idx, dev)
+sharded = nv.ShardedFlatIndex(idx, dev, exchange=os.environ.get("NVDB_B200_EXCHANGE", "auto"))
 out = {}
 for batch in sorted({1, BATCH}):
     qs = q[:batch].contiguous()
@@ -77,7 +77,10 @@ for batch in sorted({1, BATCH}):
 xq, xf = idx.exact_stats()
 if rank == 0:
     print(json.dumps({"config": f"K4: FP16 top-{K}, {total} x {DIM} rows row-sharded over {world} GPU(s) "
-                                f"({ROWS} rows = {ROWS * DIM * 2 / 1e9:.1f} GB per GPU), local top-k + NCCL all-gather + merge",
+                                f"({ROWS} rows = {ROWS * DIM * 2 / 1e9:.1f} GB per GPU), local top-k + " +
+                                ("peer-memory exchange + merge in one kernel (NVLink stores, no NCCL)" if sharded.exchange == "peer"
+                                 else "NCCL all-gather + merge kernel"),
+                      "exchange": sharded.exchange, "exchange_status": sharded.exchange_status(),
                       "n_gpus": world, "k": K, "results": out,
                       "rank0_exact_path_queries": xq, "rank0_certificate_fallbacks": xf}), flush=True)
 if world > 1:

@@ -80,3 +80,30 @@ def test_nvdb_bench_cuda_matches_reference_gtbin(bench, oracle, tmp_path, dt):
     assert "batch_samples=3" in r.stdout and "Avg_batch:" in r.stdout and "batch_p99:" in r.stdout
     assert float(re.search(r"gt_match=([0-9.]+)", r.stdout).group(1)) >= 0.99
     assert f"path_used={1 if dtype == F32 else 4}" in r.stdout   # AUTO: exact tensor-core path for f16 / i8 batches
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dt,shards,batch", [("f16", 2, 1), ("i8", 3, 1), ("f32", 2, 4), ("f16", 2, 16)])
+def test_nvdb_bench_cuda_row_shards_exchange_on_the_devices(bench, oracle, tmp_path, dt, shards, batch):
+    """gpus > 1: the shards exchange and merge their lists on the devices (NVLink peer memory when they are different
+    GPUs; with NVDB_BENCH_OVERSUBSCRIBE=1 several shards share one GPU) — ids identical to the reference's gtbin."""
+    import torch
+    if not (REF_DIR / "nvdb_gt_build").exists():
+        pytest.skip("oracle/_ref tools not built")
+    dtype = {"f32": F32, "f16": F16, "i8": I8}[dt]
+    n, d, nq, k = 20001, 256, 16, 10
+    base, scales = oracle.synth(dtype, 9, 0, n, d)
+    f = oracle.synth_f32(9, 0, n, d)
+    rng = np.random.default_rng(1)
+    q = f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32)
+    write_vecbin(tmp_path / "b.vecbin", dtype, base, scales)
+    write_raw12(tmp_path / "q.raw12", q)
+    run_ref_tool("nvdb_gt_build", tmp_path / "b.vecbin", tmp_path / "q.raw12", k, tmp_path / "gt.gtbin",
+                 env={"GT_MODE": "st", "WARMUP": "0"})
+    env = {"GT_PATH": str(tmp_path / "gt.gtbin"), "NVDB_B200_XCHG_TIMEOUT_MS": "10000"}
+    if torch.cuda.device_count() < shards:
+        env["NVDB_BENCH_OVERSUBSCRIBE"] = "1"
+    r = run(bench, tmp_path / "b.vecbin", tmp_path / "q.raw12", k, "cuda", shards, 2, batch, env=env)
+    assert r.returncode == 0, r.stderr
+    assert f"shards={shards}" in r.stdout
+    assert float(re.search(r"gt_match=([0-9.]+)", r.stdout).group(1)) >= (1.0 if batch == 1 or dtype == F32 else 0.99)
