@@ -12,6 +12,7 @@ namespace nvdb_b200 {
 namespace {
 
 constexpr int kMergeThreads = 512;
+constexpr uint32_t kSelectMinKeys = 2048;  // below this one bitonic sort of everything is cheaper than 8 histogram passes
 
 // partial: [nq][nlists][k] ordered keys (0 = empty). out: ids = row_offset + row, scores; padded with
 // UINT64_MAX / -inf when fewer than k candidates exist (k > n).
@@ -43,6 +44,92 @@ merge_partials_kernel(const uint64_t* __restrict__ partial, uint32_t nlists, uin
   }
   for (uint32_t j = tid; j < k; j += kMergeThreads) {
     const uint64_t key = (total > 0) ? buf[j] : 0ull;
+    const bool ok = key != 0ull;
+    out_ids[(size_t)q * k + j] = ok ? row_offset + (uint64_t)key_row(key) : ~0ull;
+    out_scores[(size_t)q * k + j] = ok ? key_score(key) : -INFINITY;
+  }
+}
+
+// Large reductions (k = 100 over 148 lists = 14,800 keys): sorting everything costs ~105 bitonic stages of 16 K keys
+// (~0.15 ms on one CTA, a fifth of a batch-1 scan), and the "k-th entry of the luckiest list" floor removes only a
+// quarter of the keys when k is large. Instead: all keys into shared memory once, an MSB-first radix select (8 passes of
+// 8 bits) finds the k-th largest 64-bit key exactly (keys are unique: score | ~row), the k survivors are compacted and
+// only they are sorted. Same outputs as merge_partials_kernel.
+__global__ void __launch_bounds__(kMergeThreads)
+merge_select_kernel(const uint64_t* __restrict__ partial, uint32_t total, uint32_t k, uint32_t kpow2,
+                    uint64_t row_offset, uint64_t* __restrict__ out_ids, float* __restrict__ out_scores,
+                    uint64_t* __restrict__ out_keys, size_t key_stride, float* __restrict__ out_thr) {
+  extern __shared__ uint64_t buf[];  // [total] keys, then [kpow2] survivors
+  __shared__ uint32_t hist[256];
+  __shared__ uint64_t s_prefix;
+  __shared__ uint32_t s_need, s_cnt;
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  const uint64_t* in = partial + (size_t)q * total;
+  uint64_t* sv = buf + total;
+  auto sync = [] { __syncthreads(); };
+  for (uint32_t i = tid; i < total; i += kMergeThreads) buf[i] = in[i];
+  if (tid == 0) {
+    s_prefix = 0ull;
+    s_need = k;
+    s_cnt = 0u;
+  }
+  for (int pass = 0; pass < 8; ++pass) {
+    const int shift = 56 - 8 * pass;
+    for (uint32_t b = tid; b < 256u; b += kMergeThreads) hist[b] = 0u;
+    __syncthreads();
+    const uint64_t prefix = s_prefix;
+    for (uint32_t i = tid; i < total; i += kMergeThreads) {
+      const uint64_t key = buf[i];
+      if (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8))) atomicAdd(&hist[(uint32_t)(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (tid < 32u) {
+      // lane l owns buckets 255-8l .. 248-8l (descending); find the bucket where the count from the top reaches `need`
+      uint32_t c[8], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        c[j] = hist[255u - 8u * tid - (uint32_t)j];
+        sum += c[j];
+      }
+      uint32_t incl = sum;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, off);
+        if (tid >= (uint32_t)off) incl += o;
+      }
+      const uint32_t need = s_need, before = incl - sum;
+      if (before < need && need <= incl) {  // exactly one lane (all keys of the prefix are counted, need <= their number)
+        uint32_t cum = before;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (cum < need && need <= cum + c[j]) {
+            s_prefix = prefix | ((uint64_t)(255u - 8u * tid - (uint32_t)j) << shift);
+            s_need = need - cum;
+          }
+          cum += c[j];
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // total >= k, so the k-th largest key exists; it is 0 (empty) when fewer than k real candidates exist
+  const uint64_t kth = s_prefix;
+  for (uint32_t i = tid; i < total; i += kMergeThreads) {
+    const uint64_t key = buf[i];
+    if (key != 0ull && key >= kth) sv[atomicAdd(&s_cnt, 1u)] = key;
+  }
+  __syncthreads();
+  const uint32_t cnt = s_cnt;  // <= k: keys are unique
+  for (uint32_t i = cnt + tid; i < kpow2; i += kMergeThreads) sv[i] = 0ull;
+  __syncthreads();
+  bitonic_sort_desc(sv, kpow2, tid, kMergeThreads, sync);
+  if (out_keys) {
+    for (uint32_t j = tid; j < k; j += kMergeThreads) out_keys[(size_t)q * key_stride + j] = sv[j];
+    if (tid == 0) out_thr[q] = sv[k - 1] != 0ull ? key_score(sv[k - 1]) : -INFINITY;
+    return;
+  }
+  for (uint32_t j = tid; j < k; j += kMergeThreads) {
+    const uint64_t key = sv[j];
     const bool ok = key != 0ull;
     out_ids[(size_t)q * k + j] = ok ? row_offset + (uint64_t)key_row(key) : ~0ull;
     out_scores[(size_t)q * k + j] = ok ? key_score(key) : -INFINITY;
@@ -97,6 +184,23 @@ static cudaError_t merge_partials_any(const uint64_t* partial, uint32_t nlists, 
                                       uint64_t row_offset, uint64_t* out_ids, float* out_scores, uint64_t* out_keys,
                                       size_t key_stride, float* out_thr, cudaStream_t stream) {
   if (nq == 0 || k == 0) return cudaSuccess;
+  // many keys per query: radix select + sort of the k survivors (merge_select_kernel) when everything fits shared memory
+  {
+    const uint32_t total = nlists * k, kpow2 = next_pow2(k < 2u ? 2u : k);
+    const size_t smem = ((size_t)total + kpow2) * 8u;
+    if (total > kSelectMinKeys && total >= k && smem <= 200u * 1024u) {
+      static bool attr_done = false;  // per process; the attribute is per function and device-wide once set high enough
+      if (!attr_done || smem > 48u * 1024u) {
+        cudaError_t e = cudaFuncSetAttribute(merge_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+      }
+      merge_select_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpow2, row_offset, out_ids, out_scores,
+                                                              out_keys, key_stride, out_thr);
+      count_launch();
+      return cudaGetLastError();
+    }
+  }
   // buffer: at least 2k (so every round makes progress), ideally everything in one round, capped at 16384 keys
   uint32_t bufn = next_pow2(nlists * k);
   if (bufn > 16384u) bufn = 16384u;

@@ -139,3 +139,24 @@ def test_fused_final_merge_equals_separate_merge_kernel(nv, oracle, dt, n, d, k)
             idx.set_tuning(nv.capi.TUNE_FUSED_MERGE, 0)
             b = idx.search_topk_dot_batch(queries, k)
             assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), f"nq={nq}"
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "i8"])
+@pytest.mark.parametrize("n,d,k", [(6000, 64, 300), (40000, 64, 16), (60000, 32, 100), (38000, 64, 128), (5900, 128, 255)])
+def test_radix_select_merge_of_many_lists(nv, oracle, dt, n, d, k):
+    """> 2048 keys per query go through merge_select_kernel (radix select of the k-th key, sort of the survivors only):
+    short lists with empty slots (k > rows per list), k = 100 over 148 lists, powers of two, several queries."""
+    dtype = DT[dt]
+    base, scales = make_base(oracle, dtype, n, d, seed=23)
+    f = oracle.synth_f32(23, 0, n, d)
+    rng = np.random.default_rng(8)
+    for nq in (1, 5):
+        queries = f[rng.integers(0, n, nq)] + (0.01 * rng.standard_normal((nq, d))).astype(np.float32)
+        check(nv, oracle, dtype, base, scales, queries, k)
+
+
+def test_radix_select_merge_all_equal_scores(nv, oracle):
+    """Every row identical: 148 lists of equal scores, the k smallest row ids must win (keys differ only in ~row)."""
+    base = np.tile(np.linspace(-1, 1, 64, dtype=np.float32), (50000, 1))
+    q = np.ones((2, 64), np.float32)
+    check(nv, oracle, F32, base, None, q, 100)
