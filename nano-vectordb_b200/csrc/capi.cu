@@ -615,6 +615,14 @@ int mma_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, u
   auto plan_pass = [&](uint32_t nqp) {
     PassPlan pp;
     pp.G = (nqp + 127u) / 128u;
+    // an odd number (>= 3) of query tiles: one more, empty, tile buys the CTA-pair kernel. Measured
+    // (profiles/r1_ab_pair_pad_odd.jsonl): i8 -7 / -12 / -21 % at 3 / 5 / 7 tiles, f16 top-100 -7 % at 3 tiles, but f16
+    // top-10 +15 / +15 / +7 % (its single-CTA kernel with register lists is the better one there). Knob MMA_2CTA = 2
+    // forces the padding, 1 (default) follows the measurement.
+    const bool pad_default = idx->dtype == kDtI8 || k > 16u;
+    if (pair_ok && pp.G >= 3u && (pp.G % 2u) == 1u && pp.G + 1u <= (uint32_t)idx->num_sms &&
+        (idx->tune_mma_2cta == 2 || (idx->tune_mma_2cta == 1 && pad_default)))
+      pp.G += 1u;
     pp.pair = pair_ok && pp.G >= 2u && (pp.G % 2u) == 0u;
     pp.bn = pp.pair ? pair_bn : block_n;
     pp.tiles = (uint32_t)((idx->n + pp.bn - 1) / pp.bn);

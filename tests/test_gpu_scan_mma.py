@@ -273,7 +273,7 @@ def test_cta_pair_kernel_matches_single_cta_kernel(nv, oracle, k):
     with nv.FlatIndexCuda.synthetic(F16, n, d, 6) as idx:
         base, _ = idx.read_rows(0, n)
         f = oracle.synth_f32(6, 0, n, d)
-        for nq in (256, 200, 1000):       # G = 2, 2 (padded tile), 8
+        for nq in (256, 200, 1000, 300, 600):       # G = 2, 2 (padded tile), 8, 3 -> 4 and 5 -> 6 (an empty tile added)
             queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
             got = {}
             for pair in (0, 2):
@@ -321,7 +321,7 @@ def test_i8_cta_pair_kernel_matches_single_cta_kernel(nv, oracle, k):
         with nv.FlatIndexCuda.synthetic(I8, n, d, 9) as idx:
             base, scales = idx.read_rows(0, n)
             f = oracle.synth_f32(9, 0, n, d)
-            for nq in (256, 130, 1024):   # G = 2, 2 (padded tile), 8
+            for nq in (256, 130, 1024, 330):   # G = 2, 2 (padded tile), 8, 3 -> 4 (an empty tile added)
                 queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
                 got = {}
                 for pair, res in ((0, 1), (2, 1), (2, 2), (2, 0)):   # res 1: first limb resident, 2: both, 0: none
