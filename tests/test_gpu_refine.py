@@ -53,3 +53,43 @@ def test_refine_matches_reference_cuda_arithmetic(nv, oracle):
         ids, dist = idx.refine_l2(queries, cand, K)
     oids, odist = oracle.refine(1, F16, base, None, queries, cand, K)
     compare(ids, dist, oids, odist)
+
+
+def _refcuda():
+    """The UNMODIFIED reference src/cuda_refine.cu, compiled for sm_100a into oracle/_ref (test infrastructure)."""
+    import ctypes as C
+    from _oracle import REFCUDA_SO
+    if not REFCUDA_SO.exists():
+        pytest.skip("oracle/_ref/libnvdb_refcuda.so not built")
+    lib = C.CDLL(str(REFCUDA_SO))
+    lib.refcuda_l2_topk_batch.restype = C.c_int
+    lib.refcuda_l2_topk_batch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32,
+                                          C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+    return lib
+
+
+@pytest.mark.parametrize("d,R,K", [(384, 500, 10), (768, 256, 10), (64, 100, 64)])
+def test_refine_matches_compiled_reference_cuda_kernel(nv, oracle, d, R, K):
+    """Our refine kernel vs the reference's own nvdb::cuda_l2_topk_batch running on the same GPU (f16 base — the only
+    dtype its host code launches, src/cuda_refine.cu:1055-1085): same candidates incl. FAISS '-1' holes and
+    out-of-range ids, distances within FP32 re-association, ids equal modulo near-ties."""
+    lib = _refcuda()
+    n, Q = 30000, 200
+    base, _ = oracle.synth(F16, 33, 0, n, d)
+    f = oracle.synth_f32(33, 0, n, d)
+    rng = np.random.default_rng(4)
+    queries = np.ascontiguousarray(f[rng.integers(0, n, Q)] + (0.05 * rng.standard_normal((Q, d))).astype(np.float32))
+    cand = rng.integers(0, n, (Q, R)).astype(np.uint32)
+    cand[:, ::9] = 0xFFFFFFFF
+    cand[5, :] = 0xFFFFFFFF
+    cand[6, 1::2] = n + 17
+    with nv.FlatIndexCuda.from_host(base, None, F16) as idx:
+        ids, dist = idx.refine_l2(queries, cand, K)
+    rids = np.full((Q, K), 0xFFFFFFFF, np.uint32)
+    rdist = np.full((Q, K), 1e30, np.float32)
+    t4 = np.zeros(4, np.float32)
+    got = lib.refcuda_l2_topk_batch(base.ctypes.data, F16, n, d, queries.ctypes.data, cand.ctypes.data, Q, R, K,
+                                    rids.ctypes.data, rdist.ctypes.data, t4.ctypes.data)
+    assert got == Q * K
+    compare(ids, dist, rids, rdist)
+    assert np.all(ids[5] == 0xFFFFFFFF) and np.all(rids[5] == 0xFFFFFFFF)
