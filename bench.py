@@ -152,10 +152,28 @@ def cpu_reference_run(sample_payload: np.ndarray, queries: np.ndarray, steps: in
         if time.perf_counter() - t0 > budget_s:
             break
     dt = time.perf_counter() - t0
+    # the reference's other multi-threaded variant, FlatIndexPool (pinned persistent workers,
+    # src/flat_index_pool.cpp:94-215), on the same sample — reported beside the OMP figure
+    pool = None
+    if kind == "reference":
+        try:
+            for i in range(min(warmup, 3)):
+                ref.search(h, queries[i % len(queries)], TOPK, "pool", cores)
+            p0, pdone = time.perf_counter(), 0
+            for i in range(min(steps, 200)):
+                ref.search(h, queries[i % len(queries)], TOPK, "pool", cores)
+                pdone += 1
+                if time.perf_counter() - p0 > min(budget_s, 15.0):
+                    break
+            pdt = time.perf_counter() - p0
+            pool = {"value": nbytes * pdone / pdt / 1e9, "unit": "GB/s", "threads": cores, "steps": pdone,
+                    "ms_per_step": pdt / pdone * 1e3, "variant": "FlatIndexPool"}
+        except Exception as e:  # noqa: BLE001
+            pool = {"unavailable": repr(e)}
     if tmpdir is not None:
         tmpdir.cleanup()
     return {"value": nbytes * done / dt / 1e9, "qps_on_sample": done / dt, "ms_per_step": dt / done * 1e3, "steps": done,
-            "kind": kind, "cores": cores,
+            "kind": kind, "cores": cores, "pool": pool,
             "sample": f"first {n} rows x {d} f16 of the synthetic base ({nbytes / 1e6:.0f} MB), {done} single-query "
                       f"top-{TOPK} scans, FlatIndexOMP, OMP_NUM_THREADS={os.environ['OMP_NUM_THREADS']}"}
 
@@ -186,7 +204,8 @@ def run_reference(args):
         "config": {"workload": f"FP16 exact flat-scan top-{TOPK}, {N_ROWS}x{DIM}, batch 1 (BASELINE.json configs[1])",
                    "note": "reference CPU scan is bandwidth-normalised on a bounded row sample; GB/s is size independent"},
         "qps_equiv_full_base": r["value"] * 1e9 / payload_bytes(N_ROWS, DIM, F16),
-        "cpu_baseline": {"value": r["value"], "unit": "GB/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+        "cpu_baseline": {"value": r["value"], "unit": "GB/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
+                         "pool": r.get("pool")},
         "e2e": {"value": r["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -378,7 +397,8 @@ def run_ours(args):
         payload, cq = make_cpu_sample(rows)
         r = cpu_reference_run(payload, cq, steps=400, warmup=3, budget_s=15.0)
         line["cpu_baseline"] = {"value": r["value"], "unit": "GB/s", "cores": r["cores"], "kind": r["kind"],
-                                "sample": r["sample"], "qps_equiv_full_base": r["value"] * 1e9 / nbytes}
+                                "sample": r["sample"], "qps_equiv_full_base": r["value"] * 1e9 / nbytes,
+                                "pool": r.get("pool")}
     idx.close()
     if rank == 0:
         emit(line)
