@@ -399,6 +399,8 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": r["value"], "unit": "GB/s", "cores": r["cores"], "kind": r["kind"],
                                 "sample": r["sample"], "qps_equiv_full_base": r["value"] * 1e9 / nbytes,
                                 "pool": r.get("pool")}
+    if sharded is not None:
+        sharded.close()     # unmap the peers' windows while every rank is still alive
     idx.close()
     if rank == 0:
         emit(line)

@@ -75,12 +75,14 @@ for batch in sorted({1, BATCH}):
                             "base_GBps_aggregate": total * DIM * 2 / (ms * 1e-3) / 1e9,
                             "self_top1_hits": ok, "queries": batch}
 xq, xf = idx.exact_stats()
+xstatus, xkind = sharded.exchange_status(), sharded.exchange
+sharded.close()
 if rank == 0:
     print(json.dumps({"config": f"K4: FP16 top-{K}, {total} x {DIM} rows row-sharded over {world} GPU(s) "
                                 f"({ROWS} rows = {ROWS * DIM * 2 / 1e9:.1f} GB per GPU), local top-k + " +
-                                ("peer-memory exchange + merge in one kernel (NVLink stores, no NCCL)" if sharded.exchange == "peer"
+                                ("peer-memory exchange + merge in one kernel (NVLink stores, no NCCL)" if xkind == "peer"
                                  else "NCCL all-gather + merge kernel"),
-                      "exchange": sharded.exchange, "exchange_status": sharded.exchange_status(),
+                      "exchange": xkind, "exchange_status": xstatus,
                       "n_gpus": world, "k": K, "results": out,
                       "rank0_exact_path_queries": xq, "rank0_certificate_fallbacks": xf}), flush=True)
 if world > 1:
