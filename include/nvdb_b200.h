@@ -161,13 +161,18 @@ enum {
   NVDB_B200_TUNE_GEMV_CTAS = 2, /* CTAs per SM of the single-query streaming scan: 1 (default) | 2 */
   NVDB_B200_TUNE_FUSED_MERGE = 4, /* final merge inside the streaming scan's last CTA: 0 never, 1 auto (default), 2 always */
   NVDB_B200_TUNE_MMA_RESIDENT = 5, /* i8 tensor scan, query limbs resident in shared memory: 0 none, 1 the first (default), 2 both when they fit (CTA pairs) */
+  NVDB_B200_TUNE_EXACT_TIER2 = 6, /* exact path: queries whose certificate failed get a second tensor-core pass with wider candidate lists before the streaming scan: 0 off, 1 on (default); env NVDB_B200_EXACT_TIER2 */
   NVDB_B200_TUNE_MMA_2CTA = 3   /* CTA-pair (cta_group::2) tensor-core scan (f16, i8): 0 never, 1 (default) / 2 whenever the batch has an even number of 128-query tiles */
 };
 int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value);
 
 /* Certificate statistics of NVDB_B200_PATH_MMA_EXACT since creation / the last reset: queries answered through it and
- * how many of them failed the certificate and were re-run on the streaming scan. */
+ * how many of them failed the (first) certificate and were re-run. */
 int nvdb_b200_index_exact_stats(nvdb_b200_index* idx, uint64_t* queries, uint64_t* fallbacks, int reset);
+/* Where the `fallbacks` of nvdb_b200_index_exact_stats went: `tier2` of them were re-run on the tensor-core scan with
+ * wider candidate lists, `streamed` were (finally) answered by the bit-exact streaming scan — the ones the second
+ * certificate rejected too, or all of them when no wider list is available. Read BEFORE a resetting exact_stats call. */
+int nvdb_b200_index_exact_tiers(nvdb_b200_index* idx, uint64_t* tier2, uint64_t* streamed);
 
 /* Two-stage search (coarse scan + exact re-rank, both on the device): `coarse` and `fine` are two indexes over the SAME
  * rows on one device (e.g. the INT8 and the FP16 copy of a base); the coarse scan keeps R >= k candidates per query

@@ -15,7 +15,7 @@ import numpy as np
 
 F32, F16, I8 = 1, 2, 3
 PATH_AUTO, PATH_GEMV, PATH_MMA, PATH_MMA_FAST, PATH_MMA_EXACT = 0, 1, 2, 3, 4
-TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA, TUNE_FUSED_MERGE, TUNE_MMA_RESIDENT = 1, 2, 3, 4, 5
+TUNE_MMA_SEED, TUNE_GEMV_CTAS, TUNE_MMA_2CTA, TUNE_FUSED_MERGE, TUNE_MMA_RESIDENT, TUNE_EXACT_TIER2 = 1, 2, 3, 4, 5, 6
 _NP = {F32: np.float32, F16: np.uint16, I8: np.int8}
 
 lib_path = Path(os.environ.get("NVDB_B200_LIB", Path(__file__).resolve().parent / "lib" / "libnvdb_b200.so"))
@@ -57,6 +57,7 @@ _sig = {
     "nvdb_b200_debug_mma_accumulators": (_i, [_vp, _vp, _u32, _i, _vp]),
     "nvdb_b200_index_set_tuning": (_i, [_vp, _i, _i]),
     "nvdb_b200_index_exact_stats": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), _i]),
+    "nvdb_b200_index_exact_tiers": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64)]),
     "nvdb_b200_merge_topk_device": (_i, [_i, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_merge_topk_packed_device": (_i, [_i, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
@@ -260,6 +261,12 @@ class FlatIndexCuda:
         q, f = C.c_uint64(0), C.c_uint64(0)
         _check(lib.nvdb_b200_index_exact_stats(self._h, C.byref(q), C.byref(f), int(reset)), self._h)
         return q.value, f.value
+
+    def exact_tiers(self):
+        """of the certificate failures: (re-run on the tensor-core scan with wider lists, answered by the streaming scan)"""
+        t, g = C.c_uint64(0), C.c_uint64(0)
+        _check(lib.nvdb_b200_index_exact_tiers(self._h, C.byref(t), C.byref(g)), self._h)
+        return t.value, g.value
 
     def read_rows(self, row0, nrows):
         payload = np.empty((nrows, self.dim), _NP[self.dtype])

@@ -54,12 +54,14 @@ struct nvdb_b200_index {
   bool norms_ready = false;
   float max_l2 = 0.f, max_l1 = 0.f;
   uint64_t exact_queries = 0, exact_fallbacks = 0;
+  uint64_t exact_tier2 = 0, exact_gemv = 0;  // flagged queries re-run with wider lists / on the streaming scan
   // tuning knobs (nvdb_b200_index_set_tuning; defaults may be overridden by environment variables at creation)
   int tune_mma_seed = 1;   // 0 off, 1 auto (>= 256 queries and >= 32 tiles per CTA), 2 whenever there are >= 2 tiles per CTA
   int tune_mma_resident = 1; // i8 tensor scan: query limb 0 resident in shared memory (0: stream both limbs)
   int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
   int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 (default) / 2 whenever the shape allows
+  int tune_exact_tier2 = 1; // exact path: flagged queries get a second tensor-core pass with wider candidate lists (0: off)
   std::mutex mu;
   mutable std::string err;
   // optional per-kernel event timing (bench.py's roofline figure)
@@ -73,7 +75,7 @@ namespace {
 thread_local std::string t_err;
 enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5, WS_MMA_A = 6,
        WS_MMA_QS = 7, WS_DBG = 8, WS_X_IDS = 9, WS_X_APX = 10, WS_X_FLAGS = 11, WS_X_Q = 12, WS_X_OUT_IDS = 13,
-       WS_X_OUT_SC = 14, WS_SEED = 15, WS_GEMV_CTR = 16 };
+       WS_X_OUT_SC = 14, WS_SEED = 15, WS_GEMV_CTR = 16, WS_X_LIST = 17, WS_X_Q2 = 18, WS_X_OUT2 = 19 };
 
 int fail(const nvdb_b200_index* idx, int code, const std::string& msg) {
   t_err = msg;
@@ -230,6 +232,7 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
   if (const char* ev = getenv("NVDB_B200_GEMV_CTAS")) h->tune_gemv_ctas = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_MMA_2CTA")) h->tune_mma_2cta = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_FUSED_MERGE")) h->tune_fused_merge = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_EXACT_TIER2")) h->tune_exact_tier2 = atoi(ev);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
   if (e != cudaSuccess) {
@@ -860,20 +863,14 @@ bool mma_exact_supported(const nvdb_b200_index* idx, uint32_t k) {
 int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
                      float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* fallbacks);
 
-// `deferred` != null: only enqueue (scan, re-score, D2H of the flag count) and set *deferred; the caller synchronises the
-// stream together with its own copies and then calls mma_exact_finish (the host-buffer API does this, so the common
-// no-fallback case costs ONE stream sync per search). deferred == null: finish here (device-buffer API).
-int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
-                          float* d_out_scores, cudaStream_t stream, uint32_t* launches, bool* deferred) {
-  if (!mma_exact_supported(idx, k))
-    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "exact tensor-core scan: unsupported base layout or k too large");
-  const uint32_t kp = exact_kprime(k);
+// Candidate scan with k' = kp entries per query + exact re-score + certificate, enqueued on `stream`; the number of
+// flagged queries lands in the pinned word h_pin[2][0] (flags per query stay on the device, WS_X_FLAGS + 4).
+int mma_exact_enqueue(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint32_t kp,
+                      uint64_t* d_out_ids, float* d_out_scores, cudaStream_t stream, uint32_t* launches) {
   int rc;
-  if ((rc = ensure_norms(idx, stream))) return rc;
   if ((rc = ensure_ws(idx, WS_X_IDS, (size_t)nq * kp * 8))) return rc;
   if ((rc = ensure_ws(idx, WS_X_APX, (size_t)nq * kp * 4))) return rc;
   if ((rc = ensure_ws(idx, WS_X_FLAGS, ((size_t)nq + 4) * 4))) return rc;
-  if ((rc = ensure_pin(idx, 2, ((size_t)nq + 4) * 4))) return rc;
   uint64_t* cand_ids = (uint64_t*)idx->d_ws[WS_X_IDS];
   float* cand_apx = (float*)idx->d_ws[WS_X_APX];
   uint32_t* nflag = (uint32_t*)idx->d_ws[WS_X_FLAGS];
@@ -905,8 +902,43 @@ int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t
                   : (float)((D / 8.0 + 16.0) * u24);
   CK(rescore_exact_launch((int)idx->dtype, r, nq, stream), "rescore launch");
   if (launches) ++*launches;
-  uint32_t* h = (uint32_t*)idx->h_pin[2];
-  CK(cudaMemcpyAsync(h, nflag, 4, cudaMemcpyDeviceToHost, stream), "D2H flag count");
+  CK(cudaMemcpyAsync(idx->h_pin[2], nflag, 4, cudaMemcpyDeviceToHost, stream), "D2H flag count");
+  return NVDB_B200_OK;
+}
+
+// Second tier for queries whose first certificate failed: the same one-limb candidate scan with much wider lists
+// (k' = 64 for k <= 12, else the widest list the scan's shared memory holds, about 1.5 k). The certificate fails when
+// fewer than k' - k rows separate the k-th exact score from (k'-th approximate score + margin); bases whose rows cluster
+// (hundreds of near-equal scores around the k-th) do that to 13 % (k = 10) - 61 % (k = 100) of the queries of an FP16
+// 2.9 M-row base with 256 clusters, and the streaming scan at 8 queries per pass then costs 10 - 30x the tensor-core
+// scan (profiles/r1_clustered_2p9M_before_tier2.jsonl). 0 = no wider list available.
+uint32_t exact_kprime2(const nvdb_b200_index* idx, uint32_t k) {
+  if (!idx->tune_exact_tier2) return 0u;
+  const uint32_t kp = exact_kprime(k);
+  const uint32_t want[4] = {k <= 12u ? 64u : 4u * k, 2u * k, k + k / 2u + 8u, k + k / 3u + 8u};
+  const int limbs = idx->dtype == kDtF16 ? 1 : 2;
+  for (uint32_t w : want) {
+    uint32_t bn;
+    int st;
+    if (w > kp && scan_mma_plan((int)idx->dtype, limbs, w, idx->max_smem, &bn, &st) &&
+        ((size_t)idx->dim * 4u + 15u) + (size_t)next_pow2(w) * 8u <= 200u * 1024u)
+      return w;
+  }
+  return 0u;
+}
+
+// `deferred` != null: only enqueue (scan, re-score, D2H of the flag count) and set *deferred; the caller synchronises the
+// stream together with its own copies and then calls mma_exact_finish (the host-buffer API does this, so the common
+// no-fallback case costs ONE stream sync per search). deferred == null: finish here (device-buffer API).
+int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
+                          float* d_out_scores, cudaStream_t stream, uint32_t* launches, bool* deferred) {
+  if (!mma_exact_supported(idx, k))
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "exact tensor-core scan: unsupported base layout or k too large");
+  int rc;
+  if ((rc = ensure_norms(idx, stream))) return rc;
+  // pinned words: [0] flag count, [4, 4 + nq) flags, then two index lists of up to nq entries (mma_exact_finish)
+  if ((rc = ensure_pin(idx, 2, (3 * (size_t)nq + 8) * 4))) return rc;
+  if ((rc = mma_exact_enqueue(idx, d_queries, nq, k, exact_kprime(k), d_out_ids, d_out_scores, stream, launches))) return rc;
   if (deferred) {
     *deferred = true;
     return NVDB_B200_OK;
@@ -915,44 +947,80 @@ int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t
   return mma_exact_finish(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches, nullptr);
 }
 
-// After the stream has been synchronised: read the flag count and re-run flagged queries on the streaming scan
+// After the stream has been synchronised: read the flag count and re-run flagged queries — first on the tensor-core
+// scan with wider lists (exact_kprime2), and what that cannot certify either on the streaming scan
 // (asynchronous on `stream`; *fallbacks tells the caller whether the outputs were rewritten).
 int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
                      float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* fallbacks) {
   int rc;
   uint32_t* h = (uint32_t*)idx->h_pin[2];
-  uint32_t* flags = (uint32_t*)idx->d_ws[WS_X_FLAGS] + 4;
   const uint32_t nf = h[0];
   idx->exact_queries += nq;
   idx->exact_fallbacks += nf;
   if (fallbacks) *fallbacks = nf;
   if (nf == 0) return NVDB_B200_OK;
 
-  // ---- fallback: flagged queries go through the streaming scan ------------------------------------------------
-  if (nf == nq) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
-  CK(cudaMemcpyAsync(h + 4, flags, (size_t)nq * 4, cudaMemcpyDeviceToHost, stream), "D2H flags");
-  CK(cudaStreamSynchronize(stream), "exact scan sync");
-  std::vector<uint32_t> list;
-  list.reserve(nf);
-  for (uint32_t q = 0; q < nq; ++q)
-    if (h[4 + q]) list.push_back(q);
+  const uint32_t kp2 = exact_kprime2(idx, k);
+  if (nf == nq && !kp2) {
+    idx->exact_gemv += nf;
+    return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
+  }
+  // flags -> host -> ascending list of flagged queries (pinned) -> device; returns the list length
+  auto fetch_list = [&](uint32_t n, uint32_t* h_list, uint32_t* d_list, uint32_t* count) -> int {
+    uint32_t* flags = (uint32_t*)idx->d_ws[WS_X_FLAGS] + 4;
+    CK(cudaMemcpyAsync(h + 4, flags, (size_t)n * 4, cudaMemcpyDeviceToHost, stream), "D2H flags");
+    CK(cudaStreamSynchronize(stream), "exact scan sync");
+    uint32_t m = 0;
+    for (uint32_t q = 0; q < n; ++q)
+      if (h[4 + q]) h_list[m++] = q;
+    if (m) CK(cudaMemcpyAsync(d_list, h_list, (size_t)m * 4, cudaMemcpyHostToDevice, stream), "H2D flagged list");
+    *count = m;
+    return NVDB_B200_OK;
+  };
   const size_t qb = (size_t)idx->dim * 4;
-  if ((rc = ensure_ws(idx, WS_X_Q, list.size() * qb))) return rc;
-  if ((rc = ensure_ws(idx, WS_X_OUT_IDS, list.size() * k * 8))) return rc;
-  if ((rc = ensure_ws(idx, WS_X_OUT_SC, list.size() * k * 4))) return rc;
-  char* gq = (char*)idx->d_ws[WS_X_Q];
-  for (size_t j = 0; j < list.size(); ++j)
-    CK(cudaMemcpyAsync(gq + j * qb, (const char*)d_queries + (size_t)list[j] * qb, qb, cudaMemcpyDeviceToDevice, stream),
-       "gather flagged queries");
+  if ((rc = ensure_ws(idx, WS_X_LIST, 2 * (size_t)nq * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_Q, (size_t)nf * qb))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_OUT_IDS, (size_t)nf * k * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_OUT_SC, (size_t)nf * k * 4))) return rc;
+  uint32_t* d_list1 = (uint32_t*)idx->d_ws[WS_X_LIST];
+  uint32_t* d_list2 = d_list1 + nq;
+  uint32_t* h_list1 = h + 4 + nq;
+  uint32_t* h_list2 = h_list1 + nq;
+  float* gq = (float*)idx->d_ws[WS_X_Q];
   uint64_t* fo_ids = (uint64_t*)idx->d_ws[WS_X_OUT_IDS];
   float* fo_sc = (float*)idx->d_ws[WS_X_OUT_SC];
-  if ((rc = gemv_search_impl(idx, (const float*)gq, (uint32_t)list.size(), k, fo_ids, fo_sc, stream, launches))) return rc;
-  for (size_t j = 0; j < list.size(); ++j) {
-    CK(cudaMemcpyAsync(d_out_ids + (size_t)list[j] * k, fo_ids + j * k, (size_t)k * 8, cudaMemcpyDeviceToDevice, stream),
-       "scatter fallback ids");
-    CK(cudaMemcpyAsync(d_out_scores + (size_t)list[j] * k, fo_sc + j * k, (size_t)k * 4, cudaMemcpyDeviceToDevice, stream),
-       "scatter fallback scores");
+  uint32_t n1 = 0;
+  if ((rc = fetch_list(nq, h_list1, d_list1, &n1))) return rc;
+  if (n1 != nf) return fail(idx, NVDB_B200_ERR_CUDA, "exact path: flag count and flags disagree");
+  CK(gather_queries_launch(d_queries, d_list1, n1, idx->dim, gq, stream), "gather flagged queries");
+  if (launches) ++*launches;
+
+  if (!kp2) {  // no wider list: flagged queries go straight to the streaming scan
+    idx->exact_gemv += n1;
+    if ((rc = gemv_search_impl(idx, gq, n1, k, fo_ids, fo_sc, stream, launches))) return rc;
+  } else {
+    idx->exact_tier2 += n1;
+    if ((rc = mma_exact_enqueue(idx, gq, n1, k, kp2, fo_ids, fo_sc, stream, launches))) return rc;
+    CK(cudaStreamSynchronize(stream), "exact tier-2 sync");
+    const uint32_t nf2 = h[0];
+    if (nf2) {  // still not certified (exact duplicates, pathological ties): the bit-exact streaming scan settles them
+      idx->exact_gemv += nf2;
+      if ((rc = ensure_ws(idx, WS_X_Q2, (size_t)nf2 * qb))) return rc;
+      if ((rc = ensure_ws(idx, WS_X_OUT2, (size_t)nf2 * k * 12))) return rc;
+      float* gq2 = (float*)idx->d_ws[WS_X_Q2];
+      uint64_t* f2_ids = (uint64_t*)idx->d_ws[WS_X_OUT2];
+      float* f2_sc = (float*)((char*)idx->d_ws[WS_X_OUT2] + (size_t)nf2 * k * 8);
+      uint32_t n2 = 0;
+      if ((rc = fetch_list(n1, h_list2, d_list2, &n2))) return rc;
+      if (n2 != nf2) return fail(idx, NVDB_B200_ERR_CUDA, "exact path: tier-2 flag count and flags disagree");
+      CK(gather_queries_launch(gq, d_list2, n2, idx->dim, gq2, stream), "gather tier-2 queries");
+      if ((rc = gemv_search_impl(idx, gq2, n2, k, f2_ids, f2_sc, stream, launches))) return rc;
+      CK(scatter_topk_launch(f2_ids, f2_sc, d_list2, n2, k, fo_ids, fo_sc, stream), "scatter tier-2 results");
+      if (launches) *launches += 2;
+    }
   }
+  CK(scatter_topk_launch(fo_ids, fo_sc, d_list1, n1, k, d_out_ids, d_out_scores, stream), "scatter fallback results");
+  if (launches) ++*launches;
   return NVDB_B200_OK;
 }
 
@@ -1160,6 +1228,7 @@ int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value) {
     case NVDB_B200_TUNE_MMA_2CTA: idx->tune_mma_2cta = value; break;
     case NVDB_B200_TUNE_FUSED_MERGE: idx->tune_fused_merge = value; break;
     case NVDB_B200_TUNE_MMA_RESIDENT: idx->tune_mma_resident = value; break;
+    case NVDB_B200_TUNE_EXACT_TIER2: idx->tune_exact_tier2 = value; break;
     default: return fail(idx, NVDB_B200_ERR_ARG, "unknown tuning knob");
   }
   return NVDB_B200_OK;
@@ -1170,7 +1239,15 @@ int nvdb_b200_index_exact_stats(nvdb_b200_index* idx, uint64_t* queries, uint64_
   std::lock_guard<std::mutex> g(idx->mu);
   if (queries) *queries = idx->exact_queries;
   if (fallbacks) *fallbacks = idx->exact_fallbacks;
-  if (reset) idx->exact_queries = idx->exact_fallbacks = 0;
+  if (reset) idx->exact_queries = idx->exact_fallbacks = idx->exact_tier2 = idx->exact_gemv = 0;
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_exact_tiers(nvdb_b200_index* idx, uint64_t* tier2, uint64_t* streamed) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  if (tier2) *tier2 = idx->exact_tier2;
+  if (streamed) *streamed = idx->exact_gemv;
   return NVDB_B200_OK;
 }
 

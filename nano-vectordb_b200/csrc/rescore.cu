@@ -223,7 +223,42 @@ __global__ void __launch_bounds__(256) row_norm_max_kernel(const void* __restric
   }
 }
 
+// flagged queries of the exact path: gather their FP32 rows into a dense batch / scatter the re-run results back.
+// One CTA per listed query; `list` holds indices into the source batch (ascending).
+__global__ void __launch_bounds__(128)
+gather_queries_kernel(const float* __restrict__ src, const uint32_t* __restrict__ list, uint32_t dim, float* __restrict__ dst) {
+  const float* s = src + (size_t)list[blockIdx.x] * dim;
+  float* d = dst + (size_t)blockIdx.x * dim;
+  for (uint32_t i = threadIdx.x; i < dim; i += 128u) d[i] = s[i];
+}
+__global__ void __launch_bounds__(128)
+scatter_topk_kernel(const uint64_t* __restrict__ src_ids, const float* __restrict__ src_scores,
+                    const uint32_t* __restrict__ list, uint32_t k, uint64_t* __restrict__ dst_ids,
+                    float* __restrict__ dst_scores) {
+  const size_t so = (size_t)blockIdx.x * k, dof = (size_t)list[blockIdx.x] * k;
+  for (uint32_t i = threadIdx.x; i < k; i += 128u) {
+    dst_ids[dof + i] = src_ids[so + i];
+    dst_scores[dof + i] = src_scores[so + i];
+  }
+}
+
 }  // namespace
+
+cudaError_t gather_queries_launch(const float* src, const uint32_t* list, uint32_t n, uint32_t dim, float* dst,
+                                  cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  gather_queries_kernel<<<n, 128, 0, stream>>>(src, list, dim, dst);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t scatter_topk_launch(const uint64_t* src_ids, const float* src_scores, const uint32_t* list, uint32_t n,
+                                uint32_t k, uint64_t* dst_ids, float* dst_scores, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  scatter_topk_kernel<<<n, 128, 0, stream>>>(src_ids, src_scores, list, k, dst_ids, dst_scores);
+  count_launch();
+  return cudaGetLastError();
+}
 
 cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, cudaStream_t stream) {
   if (nq == 0 || a.k == 0) return cudaSuccess;

@@ -123,6 +123,11 @@ struct RescoreArgs {
 cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, cudaStream_t stream);
 cudaError_t row_norm_max_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim, uint32_t* out2,
                                 int num_sms, cudaStream_t stream);
+// dst[j] = src[list[j]] (rows of `dim` floats) / dst[list[j]] = src[j] (k ids + k scores per query)
+cudaError_t gather_queries_launch(const float* src, const uint32_t* list, uint32_t n, uint32_t dim, float* dst,
+                                  cudaStream_t stream);
+cudaError_t scatter_topk_launch(const uint64_t* src_ids, const float* src_scores, const uint32_t* list, uint32_t n,
+                                uint32_t k, uint64_t* dst_ids, float* dst_scores, cudaStream_t stream);
 
 // CTA-pair variant (scan_mma2.cu): a.G even, a.P = clusters per pair column, tmap_b with scan_mma2_half_n(dtype)-row
 // boxes (f16: 128 of a 256-row tile; i8: 64 of a 128-row tile). Tile rows = 2 * scan_mma2_half_n(dtype).

@@ -70,10 +70,11 @@ def test_clustered_exact_tensor_path_bit_exact(nv, oracle, dt, n, d, k):
     rng = np.random.default_rng(43)
     with nv.FlatIndexCuda.from_host(base, scales, dtype) as idx:
         idx.set_path(nv.PATH_MMA_EXACT)
-        fallbacks = 0
+        fallbacks = streamed = 0
         for nq in (4, 130):
             queries = queries_from(f, nq, rng)
             ids, sc = idx.search_topk_dot_batch(queries, k)
+            streamed += idx.exact_tiers()[1]
             nquery, nfall = idx.exact_stats(reset=True)
             assert nquery == nq
             fallbacks += nfall
@@ -82,6 +83,7 @@ def test_clustered_exact_tensor_path_bit_exact(nv, oracle, dt, n, d, k):
                 assert_topk_equal(ids[qi], sc[qi], oids[qi], osc[qi], what=f"nq={nq} q{qi}")
     # wide neighbour gaps: the certificate should almost never send a query to the streaming-scan fallback
     assert fallbacks <= 13, f"{fallbacks} of 134 queries fell back"
+    assert streamed <= 2, f"{streamed} queries ended on the streaming scan"
 
 
 @pytest.mark.parametrize("dt", ["f16", "i8"])

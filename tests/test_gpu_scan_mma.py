@@ -210,6 +210,57 @@ def test_exact_path_partial_fallback_and_row_offset(nv, oracle):
     assert nfall == 2
 
 
+def test_exact_path_certificate_tiers(nv, oracle):
+    """40 copies of a row defeat the first certificate (k' = 16) but not the second (k' = 64); 90 copies defeat both and
+    end on the streaming scan. Either way, and with the second tier switched off, the answer is the oracle's."""
+    n, d, k = 4000, 128, 10
+    base, _ = oracle.synth(F16, 4, 0, n, d)
+    base = base.copy()
+    base[100:140] = base[100]
+    base[1000:1090] = base[1000]
+    f = oracle.synth_f32(4, 0, n, d)
+    queries = np.ascontiguousarray(f[[7, 100, 2000, 1000, 3999, 100]])
+    oids, osc = oracle.search_batch(F16, base, None, queries, k)
+    with nv.FlatIndexCuda.from_host(base, None, F16, row_offset=77) as idx:
+        idx.set_path(nv.PATH_MMA_EXACT)
+        for tier2, want in ((1, (3, 1)), (0, (0, 3))):
+            idx.set_tuning(nv.capi.TUNE_EXACT_TIER2, tier2)
+            ids, sc = idx.search_topk_dot_batch(queries, k)
+            assert idx.exact_tiers() == want
+            assert idx.exact_stats(reset=True) == (6, 3)
+            assert np.array_equal(ids, oids + 77)
+            assert np.array_equal(sc.view(np.uint32), osc.view(np.uint32))
+        # a batch of more than one 128-query tile, half of it flagged
+        idx.set_tuning(nv.capi.TUNE_EXACT_TIER2, 1)
+        many = np.ascontiguousarray(np.concatenate([queries] * 30))        # 180 queries, 90 flagged
+        ids, sc = idx.search_topk_dot_batch(many, k)
+        assert idx.exact_tiers() == (90, 30)
+        assert np.array_equal(ids, np.concatenate([oids + 77] * 30))
+        assert np.array_equal(sc.view(np.uint32), np.concatenate([osc] * 30).view(np.uint32))
+
+
+@pytest.mark.parametrize("k", [13, 100])
+def test_exact_path_second_tier_large_k(nv, oracle, k):
+    """k > 12: the second tier's lists are the widest the scan's shared memory holds (heap lists)"""
+    n, d = 6000, 128
+    base, _ = oracle.synth(F16, 8, 0, n, d)
+    base = base.copy()
+    m = k + k // 4 + 12            # more copies than the first tier's k' - k slack, fewer than the second's
+    base[500:500 + m] = base[500]
+    f = oracle.synth_f32(8, 0, n, d)
+    base[3000] = oracle.to_f16(f[500:501])[0]       # a far-away copy as well
+    queries = np.ascontiguousarray(f[[500, 10, 500, 4000]])
+    oids, osc = oracle.search_batch(F16, base, None, queries, k)
+    with nv.FlatIndexCuda.from_host(base, None, F16) as idx:
+        idx.set_path(nv.PATH_MMA_EXACT)
+        ids, sc = idx.search_topk_dot_batch(queries, k)
+        nq_, nfall = idx.exact_stats()
+        t2, streamed = idx.exact_tiers()
+    assert np.array_equal(ids, oids)
+    assert np.array_equal(sc.view(np.uint32), osc.view(np.uint32))
+    assert nq_ == 4 and nfall >= 2 and t2 == nfall and streamed <= nfall
+
+
 def test_exact_path_random_data_rarely_falls_back(nv, oracle):
     n, d = 200_000, 128
     with nv.FlatIndexCuda.synthetic(F16, n, d, 77) as idx:
