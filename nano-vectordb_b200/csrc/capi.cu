@@ -61,7 +61,8 @@ struct nvdb_b200_index {
   int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
   int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 (default) / 2 whenever the shape allows
-  int tune_exact_tier2 = 1; // exact path: flagged queries get a second tensor-core pass with wider candidate lists (0: off)
+  int tune_exact_tier2 = 1; // exact path: flagged queries get a second tensor-core pass with wider candidate lists (0: off;
+                            // > 1: that many list entries instead of the default width, for A/B measurements)
   std::mutex mu;
   mutable std::string err;
   // optional per-kernel event timing (bench.py's roofline figure)
@@ -915,7 +916,8 @@ int mma_exact_enqueue(nvdb_b200_index* idx, const float* d_queries, uint32_t nq,
 uint32_t exact_kprime2(const nvdb_b200_index* idx, uint32_t k) {
   if (!idx->tune_exact_tier2) return 0u;
   const uint32_t kp = exact_kprime(k);
-  const uint32_t want[4] = {k <= 12u ? 64u : 4u * k, 2u * k, k + k / 2u + 8u, k + k / 3u + 8u};
+  const uint32_t want[4] = {idx->tune_exact_tier2 > 1 ? (uint32_t)idx->tune_exact_tier2 : (k <= 12u ? 64u : 4u * k), 2u * k,
+                            k + k / 2u + 8u, k + k / 3u + 8u};
   const int limbs = idx->dtype == kDtF16 ? 1 : 2;
   for (uint32_t w : want) {
     uint32_t bn;

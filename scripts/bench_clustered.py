@@ -23,6 +23,8 @@ nv = importlib.import_module("nano-vectordb_b200")
 N = int(os.environ.get("NVDB_BENCH_ROWS", 2_903_054))
 D, K, SEED = 768, int(os.environ.get("NVDB_K", 10)), 20240229
 BATCHES = [int(b) for b in os.environ.get("NVDB_BATCHES", "1,8,128,1024").split(",")]
+DTYPES = os.environ.get("NVDB_DTYPES", "f16,i8").split(",")
+KINDS = os.environ.get("NVDB_KINDS", "isotropic,clustered").split(",")
 dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 
@@ -81,7 +83,9 @@ def run(idx, qs, nq, iters):
 
 
 for dtype, name in ((nv.F16, "f16"), (nv.I8, "i8")):
-    for kind in ("isotropic", "clustered"):
+    if name not in DTYPES:
+        continue
+    for kind in KINDS:
         idx, queries = make_base(kind, dtype)
         for b in BATCHES:
             line = {"dtype": name, "base": kind, "rows": N, "batch": b, "k": K}
