@@ -556,7 +556,43 @@ def run_extras(nv, torch, idx16, dev, local_rank, stream, q_dev, args):
               ("mma_exact", nv.PATH_MMA_EXACT, 8), ("mma_exact", nv.PATH_MMA_EXACT, 128),
               ("mma_exact", nv.PATH_MMA_EXACT, 1024)]
     ex["fp16_batch_sweep"] = sweep(idx16, nb16, plan16, lambda p_: 2 if p_ == "mma" else 1)
+    # second distribution of SURVEY.md 8(d): rows around 256 Gaussian centres (sigma 0.3, re-normalised). A query's own
+    # cluster packs ~11 K scores close together, which is what the exact path's certificate has to separate: the rates
+    # say how many queries needed the second tier / the streaming scan (scripts/bench_clustered.py is the full sweep).
+    try:
+        ex["fp16_clustered_exact_b1024"] = clustered_extra(nv, torch, dev, local_rank, stream, n)
+    except Exception as e:  # an explanatory extra must never cost the headline line
+        ex["fp16_clustered_exact_b1024"] = {"error": repr(e)[:200]}
     return ex
+
+
+def clustered_extra(nv, torch, dev, local_rank, stream, n):
+    gen = torch.Generator(device=dev).manual_seed(SEED)
+    centres = torch.randn((256, DIM), device=dev, generator=gen)
+    centres /= centres.norm(dim=1, keepdim=True)
+    payload = torch.empty((n, DIM), dtype=torch.float16, device=dev)
+    qrows = torch.arange(1024, device=dev) * 2833 % n
+    queries = torch.empty((1024, DIM), dtype=torch.float32, device=dev)
+    for lo in range(0, n, 131072):
+        hi = min(n, lo + 131072)
+        owner = torch.randint(0, 256, (hi - lo,), device=dev, generator=gen)
+        x = centres[owner] + (0.3 / DIM ** 0.5) * torch.randn((hi - lo, DIM), device=dev, generator=gen)
+        x /= x.norm(dim=1, keepdim=True)
+        sel = (qrows >= lo) & (qrows < hi)
+        queries[sel] = x[qrows[sel] - lo]
+        payload[lo:hi] = x.half()
+    torch.cuda.synchronize(dev)
+    out = {}
+    with nv.FlatIndexCuda.from_device(payload.data_ptr(), None, F16, n, DIM, device=local_rank, keepalive=payload) as idx:
+        idx.set_path(nv.PATH_MMA_EXACT)
+        for k in (10, 100):
+            ms, _ = _time_search(torch, idx, stream, queries, 1024, k, iters=5)
+            nq_, nf = idx.exact_stats()
+            t2, streamed = idx.exact_tiers()
+            idx.exact_stats(reset=True)
+            out[f"k{k}"] = {"ms_per_batch": ms, "qps": 1024 / ms * 1e3, "first_certificate_failures": nf / max(nq_, 1),
+                            "second_tier": t2 / max(nq_, 1), "streaming_scan": streamed / max(nq_, 1)}
+    return out
 
 
 def main():
