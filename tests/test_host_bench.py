@@ -103,6 +103,9 @@ def test_nvdb_bench_cuda_row_shards_exchange_on_the_devices(bench, oracle, tmp_p
     env = {"GT_PATH": str(tmp_path / "gt.gtbin"), "NVDB_B200_XCHG_TIMEOUT_MS": "10000"}
     if torch.cuda.device_count() < shards:
         env["NVDB_BENCH_OVERSUBSCRIBE"] = "1"
+        # shards sharing a GPU spin for each other's results: nothing may wait for the whole device meanwhile — the
+        # harness grows the workspaces beforehand, and kernels are loaded at start-up instead of at first launch
+        env["CUDA_MODULE_LOADING"] = "EAGER"
     r = run(bench, tmp_path / "b.vecbin", tmp_path / "q.raw12", k, "cuda", shards, 2, batch, env=env)
     assert r.returncode == 0, r.stderr
     assert f"shards={shards}" in r.stdout
