@@ -103,7 +103,10 @@ int nvdb_b200_index_read_rows(const nvdb_b200_index* idx, uint64_t row0, uint64_
  * score = -inf (the reference clamps k to n, src/flat_index.cpp:24). k == 0 or nq == 0 is a no-op. */
 int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, uint32_t k, uint64_t* out_ids,
                      float* out_scores, nvdb_b200_timing* timing);
-/* Same, all buffers in device memory, asynchronous on `stream` (a cudaStream_t; NULL = the index's stream). */
+/* Same, all buffers in device memory, asynchronous on `stream` (a cudaStream_t; NULL = the index's stream).
+ * One search of an index is in flight at a time: its workspaces are per index, so a call that arrives on another stream
+ * than the previous one is ordered behind it with an event, never overlapped. NVDB_B200_PATH_MMA_EXACT (what AUTO picks
+ * for >= 3 queries) synchronises `stream` once per call (the certificate verdict comes back to the host). */
 int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
                             uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
 /* Merge `nlists` per-shard results (each [nq][k], laid out list-major: [nlists][nq][k]) into one [nq][k]
@@ -140,6 +143,9 @@ int nvdb_b200_exchange_connect(nvdb_b200_exchange* x, const unsigned char* handl
 int nvdb_b200_exchange_merge(nvdb_b200_exchange* x, const void* local_packed_dev, uint32_t nq, uint32_t k,
                              uint64_t* out_ids_dev, float* out_scores_dev, int phases, void* stream);
 int nvdb_b200_exchange_status(nvdb_b200_exchange* x, uint32_t* status);
+/* Collective recovery after a timed-out exchange: every rank calls it (no rank inside an exchange call, and a barrier
+ * between the resets and the next search); clears the sticky status, the flags of the own window and the epochs. */
+int nvdb_b200_exchange_reset(nvdb_b200_exchange* x);
 const char* nvdb_b200_exchange_last_error(const nvdb_b200_exchange* x);
 int nvdb_b200_exchange_destroy(nvdb_b200_exchange* x);
 /* The whole step of one rank of a row-sharded index: local scan of `idx` (NULL = this rank's shard is empty) + exchange

@@ -83,6 +83,7 @@ _sig = {
     "nvdb_b200_exchange_connect": (_i, [_vp, _vp, _vp]),
     "nvdb_b200_exchange_merge": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _i, _vp]),
     "nvdb_b200_exchange_status": (_i, [_vp, C.POINTER(_u32)]),
+    "nvdb_b200_exchange_reset": (_i, [_vp]),
     "nvdb_b200_exchange_last_error": (C.c_char_p, [_vp]),
     "nvdb_b200_exchange_destroy": (_i, [_vp]),
     "nvdb_b200_search_exchange_device": (_i, [_vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
@@ -184,6 +185,10 @@ class PeerExchange:
         s = _u32()
         self._ck(lib.nvdb_b200_exchange_status(self._h, C.byref(s)))
         return int(s.value)
+
+    def reset(self):
+        """collective recovery after a timed-out exchange (every rank, with a barrier before the next search)"""
+        self._ck(lib.nvdb_b200_exchange_reset(self._h))
 
     def close(self):
         if self._h:

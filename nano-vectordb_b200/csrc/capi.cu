@@ -1,5 +1,6 @@
 // capi.cu — the C ABI (include/nvdb_b200.h): index handle, uploads, search / refine orchestration.
 // No CPU compute path lives here: every result is produced by the kernels in this directory.
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cmath>
@@ -35,6 +36,14 @@ struct nvdb_b200_index {
   int max_smem = 227 * 1024;
   int max_smem_sm = 228 * 1024;  // per SM (all resident CTAs together)
   cudaStream_t stream = nullptr;
+  // One stream per index: the workspaces, the streaming scan's done-counter and the query tensor map are per index, so
+  // two searches of one index must not overlap. `cur_stream` is the stream of the latest call; a call on another
+  // stream is ordered after it with an event (adopt_stream), never run concurrently.
+  cudaStream_t cur_stream = nullptr;
+  cudaEvent_t ev_switch = nullptr;
+  // debug guard (env NVDB_B200_XCHG_NO_ALLOC=1): while an exchange call is in flight a workspace may not grow — ranks
+  // sharing one device would dead-lock behind a spinning peer kernel
+  bool guard_no_alloc = false, in_exchange = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   bool tma_ok = false;
   CUtensorMap tmap;
@@ -122,8 +131,11 @@ size_t elem_size(uint32_t dtype) { return dtype == kDtF32 ? 4 : dtype == kDtF16 
 
 int ensure_ws(nvdb_b200_index* idx, int which, size_t bytes) {
   if (bytes <= idx->d_ws_bytes[which]) return NVDB_B200_OK;
+  if (idx->guard_no_alloc && idx->in_exchange)
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "workspace " + std::to_string(which) + " would grow inside an exchange call (NVDB_B200_XCHG_NO_ALLOC)");
   if (idx->d_ws[which]) {
     CK(cudaStreamSynchronize(idx->stream), "sync before workspace grow");
+    if (idx->cur_stream && idx->cur_stream != idx->stream) CK(cudaStreamSynchronize(idx->cur_stream), "sync before workspace grow");
     cudaFree(idx->d_ws[which]);
     idx->d_ws[which] = nullptr;
     idx->d_ws_bytes[which] = 0;
@@ -136,8 +148,11 @@ int ensure_ws(nvdb_b200_index* idx, int which, size_t bytes) {
 }
 int ensure_pin(nvdb_b200_index* idx, int which, size_t bytes) {
   if (bytes <= idx->h_pin_bytes[which]) return NVDB_B200_OK;
+  if (idx->guard_no_alloc && idx->in_exchange)
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "pinned buffer would grow inside an exchange call (NVDB_B200_XCHG_NO_ALLOC)");
   if (idx->h_pin[which]) {
     CK(cudaStreamSynchronize(idx->stream), "sync before pinned grow");
+    if (idx->cur_stream && idx->cur_stream != idx->stream) CK(cudaStreamSynchronize(idx->cur_stream), "sync before pinned grow");
     cudaFreeHost(idx->h_pin[which]);
     idx->h_pin[which] = nullptr;
     idx->h_pin_bytes[which] = 0;
@@ -146,6 +161,19 @@ int ensure_pin(nvdb_b200_index* idx, int which, size_t bytes) {
   while (cap < bytes) cap <<= 1;
   CK(cudaMallocHost(&idx->h_pin[which], cap), "cudaMallocHost");
   idx->h_pin_bytes[which] = cap;
+  return NVDB_B200_OK;
+}
+
+// Calls of one index run on ONE stream at a time (the per-index state above): a call that arrives on another stream is
+// ordered behind everything enqueued so far.
+int adopt_stream(nvdb_b200_index* idx, cudaStream_t s) {
+  if (idx->cur_stream == s) return NVDB_B200_OK;
+  if (idx->cur_stream != nullptr || s != idx->stream) {
+    cudaStream_t prev = idx->cur_stream ? idx->cur_stream : idx->stream;
+    CK(cudaEventRecord(idx->ev_switch, prev), "stream switch record");
+    CK(cudaStreamWaitEvent(s, idx->ev_switch, 0), "stream switch wait");
+  }
+  idx->cur_stream = s;
   return NVDB_B200_OK;
 }
 
@@ -234,7 +262,9 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
   if (const char* ev = getenv("NVDB_B200_MMA_2CTA")) h->tune_mma_2cta = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_FUSED_MERGE")) h->tune_fused_merge = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_EXACT_TIER2")) h->tune_exact_tier2 = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_XCHG_NO_ALLOC")) h->guard_no_alloc = atoi(ev) != 0;
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_switch, cudaEventDisableTiming);
   for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
   if (e != cudaSuccess) {
     delete h;
@@ -281,6 +311,7 @@ int nvdb_b200_index_destroy(nvdb_b200_index* idx) {
   if (!idx) return NVDB_B200_OK;
   cudaSetDevice(idx->device);
   if (idx->stream) cudaStreamSynchronize(idx->stream);
+  if (idx->cur_stream && idx->cur_stream != idx->stream) cudaStreamSynchronize(idx->cur_stream);
   if (idx->owns) {
     if (idx->payload) cudaFree(idx->payload);
     if (idx->scales) cudaFree(idx->scales);
@@ -292,6 +323,7 @@ int nvdb_b200_index_destroy(nvdb_b200_index* idx) {
   for (auto& e : idx->ev)
     if (e) cudaEventDestroy(e);
   for (auto& e : idx->prof_ev) cudaEventDestroy(e);
+  if (idx->ev_switch) cudaEventDestroy(idx->ev_switch);
   if (idx->stream) cudaStreamDestroy(idx->stream);
   delete idx;
   return NVDB_B200_OK;
@@ -527,6 +559,7 @@ int nvdb_b200_index_read_rows(const nvdb_b200_index* idx, uint64_t row0, uint64_
   if (row0 + nrows > idx->n) return fail(idx, NVDB_B200_ERR_ARG, "Index out of range");
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
   CK(cudaStreamSynchronize(idx->stream), "sync");
+  if (idx->cur_stream && idx->cur_stream != idx->stream) CK(cudaStreamSynchronize(idx->cur_stream), "sync");
   const size_t rb = (size_t)idx->dim * elem_size(idx->dtype);
   if (payload_host && nrows)
     CK(cudaMemcpy(payload_host, (const char*)idx->payload + row0 * rb, nrows * rb, cudaMemcpyDeviceToHost), "D2H rows");
@@ -541,6 +574,16 @@ int nvdb_b200_index_read_rows(const nvdb_b200_index* idx, uint64_t row0, uint64_
 // flat scan
 // =====================================================================================================
 namespace {
+
+// done-counter of the streaming scan's fused merge: zeroed once, on the stream of the call that creates it (the merging
+// CTA resets it after every launch)
+int ensure_gemv_ctr(nvdb_b200_index* idx, cudaStream_t stream) {
+  if (idx->d_ws[WS_GEMV_CTR] != nullptr) return NVDB_B200_OK;
+  int rc = ensure_ws(idx, WS_GEMV_CTR, 256);
+  if (rc) return rc;
+  CK(cudaMemsetAsync(idx->d_ws[WS_GEMV_CTR], 0, 256, stream), "memset merge counter");
+  return NVDB_B200_OK;
+}
 
 struct ScanPlan {
   int nq_template = 1;
@@ -790,19 +833,20 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   a.row_offset = idx->row_offset;
   a.xchg = ScanXchg{};
   if (tail_used) *tail_used = false;
-  if (xchg && fused && nq <= (uint32_t)plan.nq_template &&
-      (size_t)xchg->world * k * 12u + 8u <= (size_t)plan.stages * 32768u) {
-    exchange_begin_epoch(xchg, &a.xchg);
-    if (tail_used) *tail_used = true;
-  }
   if (fused) {
-    const bool fresh = idx->d_ws[WS_GEMV_CTR] == nullptr;
-    if ((rc = ensure_ws(idx, WS_GEMV_CTR, 256))) return rc;
-    if (fresh) CK(cudaMemsetAsync(idx->d_ws[WS_GEMV_CTR], 0, 256, stream), "memset merge counter");
+    if ((rc = ensure_gemv_ctr(idx, stream))) return rc;
     a.done_counter = (uint32_t*)idx->d_ws[WS_GEMV_CTR];
   }
   cudaEvent_t* pev = nullptr;
   if ((rc = prof_begin(idx, stream, &pev))) return rc;
+  // The epoch of a row-sharded search starts only now, after everything that can fail without a launch: a rank that
+  // bumped its epoch and then returned an error would be one epoch ahead of its peers for good.
+  const bool tail = xchg && fused && nq <= (uint32_t)plan.nq_template &&
+                    (size_t)xchg->world * k * 12u + 8u <= (size_t)plan.stages * 32768u;
+  if (tail) {
+    exchange_begin_epoch(xchg, &a.xchg);
+    if (tail_used) *tail_used = true;
+  }
   for (uint32_t q0 = 0; q0 < nq; q0 += (uint32_t)plan.nq_template) {
     const uint32_t left = nq - q0;
     // shrink the template for the remainder so a tail of 1-2 queries does not pay for 8
@@ -815,7 +859,13 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
       a.out_ids = d_out_ids + (size_t)q0 * k;
       a.out_scores = d_out_scores + (size_t)q0 * k;
     }
-    CK(scan_gemv_launch(L, a, t), "scan_gemv launch");
+    {
+      const cudaError_t le = scan_gemv_launch(L, a, t);
+      if (le != cudaSuccess) {
+        if (tail) xchg->epoch -= 1u;  // nothing was launched for this epoch (a tail call is a single pass)
+        return fail_cuda(idx, le, "scan_gemv launch");
+      }
+    }
     count_launch();
     if (launches) ++*launches;
   }
@@ -929,6 +979,43 @@ uint32_t exact_kprime2(const nvdb_b200_index* idx, uint32_t k) {
   return 0u;
 }
 
+// Every workspace the exact path can touch for a batch of nq queries, sized for the worst case (all nq queries flagged by
+// the first certificate, all of them again by the second) BEFORE anything is launched. Which queries fail a certificate
+// is data dependent, and a workspace that grows in the middle of a row-sharded search (cudaFree / cudaMalloc wait for
+// the whole device) dead-locks ranks that share a GPU behind a spinning peer kernel; sized like this, one
+// plain search of a (nq, k) shape grows everything any later search of that shape can need.
+int reserve_exact_ws(nvdb_b200_index* idx, uint32_t nq, uint32_t k, cudaStream_t stream) {
+  const uint32_t kp = exact_kprime(k), kp2 = exact_kprime2(idx, k), kw = kp2 > kp ? kp2 : kp;
+  const size_t qb = (size_t)idx->dim * 4, es = elem_size(idx->dtype);
+  const int limbs = idx->dtype == kDtF16 ? 1 : 2;
+  int rc;
+  if ((rc = ensure_ws(idx, WS_X_IDS, (size_t)nq * kw * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_APX, (size_t)nq * kw * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_FLAGS, ((size_t)nq + 4) * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_LIST, 2 * (size_t)nq * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_Q, (size_t)nq * qb))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_OUT_IDS, (size_t)nq * k * 8))) return rc;
+  if ((rc = ensure_ws(idx, WS_X_OUT_SC, (size_t)nq * k * 4))) return rc;
+  if (kp2) {
+    if ((rc = ensure_ws(idx, WS_X_Q2, (size_t)nq * qb))) return rc;
+    if ((rc = ensure_ws(idx, WS_X_OUT2, (size_t)nq * k * 12))) return rc;
+  }
+  // per-CTA candidate lists: a tensor-core pass of m queries writes m * (P + 1) lists with P <= num_sms / ceil(m / 128),
+  // i.e. at most 128 * num_sms + m lists (m * (num_sms + 1) for a single query tile); the streaming-scan fallback writes
+  // nq * grid lists of k entries
+  const size_t sms = (size_t)idx->num_sms;
+  const size_t lists_mma = nq <= 128u * sms ? std::min((size_t)nq * (sms + 1), 128u * sms + nq + 128u) : (size_t)nq * (sms + 1);
+  ScanPlan plan;
+  if ((rc = plan_scan(idx, nq, k, &plan))) return rc;
+  const size_t part = std::max(lists_mma * kw * 8, (size_t)nq * plan.grid * k * 8);
+  if ((rc = ensure_ws(idx, WS_PARTIAL, part))) return rc;
+  if ((rc = ensure_ws(idx, WS_SEED, lists_mma * kw * 8))) return rc;
+  const size_t mpad = (((size_t)(nq < 128u * sms ? nq : 128u * sms) + 127u) / 128u + 1u) * 128u;  // + 1: CTA-pair padding tile
+  if ((rc = ensure_ws(idx, WS_MMA_A, (size_t)limbs * mpad * idx->dim * es))) return rc;
+  if ((rc = ensure_ws(idx, WS_MMA_QS, 3 * mpad * 4))) return rc;
+  return ensure_gemv_ctr(idx, stream);
+}
+
 // `deferred` != null: only enqueue (scan, re-score, D2H of the flag count) and set *deferred; the caller synchronises the
 // stream together with its own copies and then calls mma_exact_finish (the host-buffer API does this, so the common
 // no-fallback case costs ONE stream sync per search). deferred == null: finish here (device-buffer API).
@@ -940,6 +1027,7 @@ int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t
   if ((rc = ensure_norms(idx, stream))) return rc;
   // pinned words: [0] flag count, [4, 4 + nq) flags, then two index lists of up to nq entries (mma_exact_finish)
   if ((rc = ensure_pin(idx, 2, (3 * (size_t)nq + 8) * 4))) return rc;
+  if ((rc = reserve_exact_ws(idx, nq, k, stream))) return rc;
   if ((rc = mma_exact_enqueue(idx, d_queries, nq, k, exact_kprime(k), d_out_ids, d_out_scores, stream, launches))) return rc;
   if (deferred) {
     *deferred = true;
@@ -1058,8 +1146,10 @@ int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint
   if (!out_ids_dev || !out_scores_dev) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
   std::lock_guard<std::mutex> g(idx->mu);
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
-  return search_device_impl(idx, queries_dev, nq, k, out_ids_dev, out_scores_dev,
-                            stream ? (cudaStream_t)stream : idx->stream, nullptr, nullptr);
+  cudaStream_t s = stream ? (cudaStream_t)stream : idx->stream;
+  int rc = adopt_stream(idx, s);
+  if (rc) return rc;
+  return search_device_impl(idx, queries_dev, nq, k, out_ids_dev, out_scores_dev, s, nullptr, nullptr);
 }
 
 // scan + exchange + merge of one rank; idx->mu held by the caller
@@ -1111,8 +1201,13 @@ int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x
   if (!queries_dev) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
   std::lock_guard<std::mutex> g(idx->mu);
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
-  return search_exchange_impl(idx, x, queries_dev, nq, k, out_ids_dev, out_scores_dev,
-                              stream ? (cudaStream_t)stream : idx->stream);
+  cudaStream_t s = stream ? (cudaStream_t)stream : idx->stream;
+  int rc = adopt_stream(idx, s);
+  if (rc) return rc;
+  idx->in_exchange = true;
+  rc = search_exchange_impl(idx, x, queries_dev, nq, k, out_ids_dev, out_scores_dev, s);
+  idx->in_exchange = false;
+  return rc;
 }
 
 int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
@@ -1132,6 +1227,7 @@ int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const
   if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
   if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
   cudaStream_t s = idx->stream;
+  if ((rc = adopt_stream(idx, s))) return rc;
   uint64_t* d_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
   float* d_scores = (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
   std::memcpy(idx->h_pin[0], queries_host, qbytes);
@@ -1139,7 +1235,10 @@ int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
   if (timing) CK(cudaEventRecord(idx->ev[1], s), "event");
   const uint64_t l0 = g_launches.load(std::memory_order_relaxed);
-  if ((rc = search_exchange_impl(idx, x, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s))) return rc;
+  idx->in_exchange = true;
+  rc = search_exchange_impl(idx, x, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s);
+  idx->in_exchange = false;
+  if (rc) return rc;
   if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
   char* hp = (char*)idx->h_pin[1];
   if (out_ids) CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
@@ -1181,6 +1280,7 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
   if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
   cudaStream_t s = idx->stream;
+  if ((rc = adopt_stream(idx, s))) return rc;
   uint64_t* d_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
   float* d_scores = (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
   par_memcpy(idx->h_pin[0], queries_host, qbytes);
@@ -1283,6 +1383,8 @@ int nvdb_b200_search_two_stage(nvdb_b200_index* coarse, nvdb_b200_index* fine, c
   if ((rc = ensure_pin(idx, 0, qbytes))) return rc;
   if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
   cudaStream_t s = idx->stream;
+  if ((rc = adopt_stream(idx, s))) return rc;
+  if ((rc = adopt_stream(fine, s))) return rc;
   std::memcpy(idx->h_pin[0], queries_host, qbytes);
   CK(cudaEventRecord(idx->ev[0], s), "event");
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
@@ -1355,6 +1457,7 @@ int nvdb_b200_debug_mma_accumulators(nvdb_b200_index* idx, const float* queries_
   if ((rc = ensure_ws(idx, WS_OUT_SCORES, (size_t)nq * 4))) return rc;
   if ((rc = ensure_ws(idx, WS_DBG, dbytes))) return rc;
   cudaStream_t s = idx->stream;
+  if ((rc = adopt_stream(idx, s))) return rc;
   CK(cudaMemsetAsync(idx->d_ws[WS_DBG], 0, dbytes, s), "memset");
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], queries_host, qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
   rc = mma_search_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, 1, (uint64_t*)idx->d_ws[WS_OUT_IDS],
@@ -1417,6 +1520,7 @@ int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, c
   if (rc) return rc;
   std::lock_guard<std::mutex> g(idx->mu);
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  // stateless on the index (no workspace): any stream, no ordering against the index's searches needed
   CK(refine_l2_launch((int)idx->dtype, idx->payload, idx->scales, idx->n, idx->dim, queries_dev, cand_ids_dev, Q, R, K,
                       out_ids_dev, out_dist_dev, stream ? (cudaStream_t)stream : idx->stream),
      "refine launch");
@@ -1441,6 +1545,7 @@ int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const u
   if ((rc = ensure_pin(idx, 0, qb + cb))) return rc;
   if ((rc = ensure_pin(idx, 1, 2 * ob))) return rc;
   cudaStream_t s = idx->stream;
+  if ((rc = adopt_stream(idx, s))) return rc;
   char* hin = (char*)idx->h_pin[0];
   char* hout = (char*)idx->h_pin[1];
   // Chunks of queries flow through staging copy -> H2D -> kernel -> D2H, so the host's copy of chunk c+1 into pinned

@@ -244,8 +244,27 @@ int nvdb_b200_exchange_merge(nvdb_b200_exchange* x, const void* local_packed_dev
   if ((phases & 1) && push_ctas > grid) grid = push_ctas;
   if (grid > (size_t)x->num_sms) grid = (size_t)x->num_sms;
   exchange_merge_kernel<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(p);
+  const cudaError_t le = cudaGetLastError();
+  if (le != cudaSuccess) {
+    if (phases & 1) x->epoch -= 1u;  // nothing was launched for this epoch: stay in step with the peers
+    return xfail(x, NVDB_B200_ERR_CUDA, std::string("exchange_merge launch: ") + cudaGetErrorString(le));
+  }
   count_launch(1);
-  XCK(cudaGetLastError(), "exchange_merge launch");
+  return NVDB_B200_OK;
+}
+
+// Collective: after a timed-out exchange (status 1) every rank calls reset before the next search. Clears the sticky
+// status word, the CTA counter and this rank's flags, and restarts the epochs at 0 — callers must make sure (barrier)
+// that no rank is still inside an exchange call and that every rank resets before any rank searches again.
+int nvdb_b200_exchange_reset(nvdb_b200_exchange* x) {
+  if (!x) return xfail(x, NVDB_B200_ERR_ARG, "exchange_reset: exchange is NULL");
+  XCK(cudaSetDevice(x->device), "cudaSetDevice");
+  XCK(cudaDeviceSynchronize(), "exchange_reset sync");
+  XCK(cudaMemset(x->counter, 0, 2 * sizeof(uint32_t)), "exchange_reset status");
+  XCK(cudaMemset(x->window, 0, kHeaderBytes), "exchange_reset flags");
+  XCK(cudaDeviceSynchronize(), "exchange_reset sync");
+  x->epoch = 0;
+  x->err.clear();
   return NVDB_B200_OK;
 }
 

@@ -966,6 +966,15 @@ int nvdb_b200_ivfpq_import(int device, uint32_t dim, uint32_t nlist, uint32_t pq
   if (list_off[0] != 0 || list_off[nlist] != n) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: list offsets do not cover n");
   for (uint32_t l = 0; l < nlist; ++l)
     if (list_off[l] > list_off[l + 1]) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: list offsets not ascending");
+  {  // the selectors rank candidates by (distance, id) keys and assume them unique: every row id once, all below n
+    std::vector<uint64_t> seen((n + 63) / 64, 0ull);
+    for (uint64_t i = 0; i < n; ++i) {
+      const uint32_t id = ids[i];
+      if (id >= n) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: row id out of range");
+      if (seen[id >> 6] & (1ull << (id & 63))) return ifail(nullptr, NVDB_B200_ERR_ARG, "ivfpq import: duplicate row id");
+      seen[id >> 6] |= 1ull << (id & 63);
+    }
+  }
   h = new nvdb_b200_ivfpq();
   h->device = device;
   h->d = dim;
@@ -1038,7 +1047,8 @@ int nvdb_b200_ivfpq_search_device(nvdb_b200_ivfpq* h, const float* queries_dev, 
   if (!h || !queries_dev || !cand_ids_dev) return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search: NULL argument");
   std::lock_guard<std::mutex> lock(h->mu);
   ICK(cudaSetDevice(h->device), "cudaSetDevice");
-  return search_device_impl(h, queries_dev, nq, nprobe, R, cand_ids_dev, cand_dist_dev, (cudaStream_t)stream);
+  return search_device_impl(h, queries_dev, nq, nprobe, R, cand_ids_dev, cand_dist_dev,
+                            stream ? (cudaStream_t)stream : h->stream);  // NULL = the handle's own stream, as in the index API
 }
 
 int nvdb_b200_ivfpq_search(nvdb_b200_ivfpq* h, const float* queries_host, uint32_t nq, uint32_t nprobe, uint32_t R,
@@ -1072,6 +1082,14 @@ int nvdb_b200_ivfpq_search_refine(nvdb_b200_ivfpq* h, nvdb_b200_index* base, con
   if (!h || !base || !queries_host || !out_ids) return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search_refine: NULL argument");
   if (nq == 0) return NVDB_B200_OK;
   if (k == 0 || k > R) return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search_refine: need 1 <= k <= R");
+  {  // `base` must be the rows this index was built over, on this index's device (its stream and workspaces are used)
+    uint64_t bn = 0;
+    uint32_t bd = 0;
+    int bdev = -1;
+    if (nvdb_b200_index_info(base, &bn, &bd, nullptr, &bdev, nullptr, nullptr, nullptr) != NVDB_B200_OK || bdev != h->device ||
+        bd != h->d || bn != h->n)
+      return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search_refine: base does not match the index (device, dim or row count)");
+  }
   std::lock_guard<std::mutex> lock(h->mu);
   ICK(cudaSetDevice(h->device), "cudaSetDevice");
   int rc;

@@ -116,10 +116,13 @@ merge_select_kernel(const uint64_t* __restrict__ partial, uint32_t total, uint32
   const uint64_t kth = s_prefix;
   for (uint32_t i = tid; i < total; i += kMergeThreads) {
     const uint64_t key = buf[i];
-    if (key != 0ull && key >= kth) sv[atomicAdd(&s_cnt, 1u)] = key;
+    if (key != 0ull && key >= kth) {  // <= k survivors when keys are unique; duplicates (untrusted input) are dropped, not written past sv
+      const uint32_t slot = atomicAdd(&s_cnt, 1u);
+      if (slot < kpow2) sv[slot] = key;
+    }
   }
   __syncthreads();
-  const uint32_t cnt = s_cnt;  // <= k: keys are unique
+  const uint32_t cnt = s_cnt < kpow2 ? s_cnt : kpow2;  // <= k when keys are unique
   for (uint32_t i = cnt + tid; i < kpow2; i += kMergeThreads) sv[i] = 0ull;
   __syncthreads();
   bitonic_sort_desc(sv, kpow2, tid, kMergeThreads, sync);

@@ -92,6 +92,17 @@ inline nvdb_b200_ivfpq* ivfpq_load(const std::string& path, int device) {
   in.read(reinterpret_cast<char*>(&h), sizeof(h));
   if (!in || h.magic != kIvfPqMagic || h.version != 1 || h.pq_bits != 8 || h.pq_m == 0 || h.dim % h.pq_m != 0)
     throw std::runtime_error("Bad IVF-PQ index header: " + path);
+  {  // the arrays are sized from the header: refuse a header the file cannot back before allocating anything
+    in.seekg(0, std::ios::end);
+    const uint64_t file_bytes = (uint64_t)in.tellg();
+    in.seekg(sizeof(h), std::ios::beg);
+    const uint64_t dsub = h.dim / h.pq_m;
+    const uint64_t want = sizeof(h) + (uint64_t)h.nlist * h.dim * 4 + (uint64_t)h.pq_m * 256 * dsub * 4 +
+                          ((uint64_t)h.nlist + 1) * 4 + (uint64_t)h.n * 4 + (uint64_t)h.n * h.pq_m +
+                          (h.has_opq ? (uint64_t)h.dim * h.dim * 4 : 0);
+    if (h.nlist == 0 || h.n == 0 || file_bytes != want)
+      throw std::runtime_error("IVF-PQ index file size does not match its header: " + path);
+  }
   IvfPqArrays a;
   a.dim = h.dim;
   a.nlist = h.nlist;

@@ -16,6 +16,7 @@
 #include <iomanip>
 #include <iostream>
 #include <memory>
+#include <set>
 #include <string>
 #include <thread>
 #include <vector>
@@ -68,15 +69,16 @@ class ShardedIndex {
       return;
     }
     ensure_exchange(8 * (nk + (nk + 1) / 2));
-    // Shards that share one device (NVDB_BENCH_OVERSUBSCRIBE): a shard's first call of a shape grows its workspaces, and
-    // cudaMalloc / cudaFree wait for the whole device — including the other shard's kernel, which is spinning for this
-    // shard's result. Grow everything with one plain search per shard first (no exchange, one shard at a time).
-    if (shared_device_ && (nq > warm_nq_ || k > warm_k_)) {
+    // A shard's first call of a shape grows its workspaces, and cudaMalloc / cudaFree wait for the whole device —
+    // including, when shards share one device (NVDB_BENCH_OVERSUBSCRIBE), the other shard's kernel, which is spinning
+    // for this shard's result (and with peer access enabled a free may wait on the peers as well). Grow everything with
+    // one plain search per shard first (no exchange, one shard at a time): the library sizes every workspace of a
+    // (nq, k) shape for its worst case on that first call (capi.cu: reserve_exact_ws), so no later search of the shape
+    // allocates (NVDB_B200_XCHG_NO_ALLOC=1 turns that into a checked error).
+    if (warmed_.insert({nq, k}).second) {
       std::vector<uint64_t> wi(nk);
       std::vector<float> wsc(nk);
       for (auto* h : shards_) nvdb::detail::check(nvdb_b200_search(h, q, nq, k, wi.data(), wsc.data(), nullptr), h);
-      warm_nq_ = std::max(warm_nq_, nq);
-      warm_k_ = std::max(warm_k_, k);
     }
     std::vector<std::thread> th;
     std::vector<int> rc(S, 0);
@@ -125,7 +127,7 @@ class ShardedIndex {
   size_t slot_bytes_ = 0;
   uint64_t n_ = 0;
   bool shared_device_ = false;
-  uint32_t warm_nq_ = 0, warm_k_ = 0;
+  std::set<std::pair<uint32_t, uint32_t>> warmed_;  // (nq, k) shapes whose workspaces have been grown
 };
 
 // gtbin (include/nvdb/gtbin_format.h:18-35): 64-byte header {u64 magic "NVDBGT01", u32 version, u32 metric, u32 k,
