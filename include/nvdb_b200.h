@@ -160,6 +160,13 @@ int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x
 int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
                               uint32_t k, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing);
 
+/* The same step in two calls, for logical ranks that SHARE one GPU (kernels that wait for one another must not be separate
+ * launches on one device — nothing guarantees that they are resident together): phase 1 = local scan + push, called for
+ * every rank first; phase 2 = wait (finds every flag) + merge + results, called for every rank afterwards. queries_host
+ * is read by phase 1 only. */
+int nvdb_b200_search_exchange_split(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
+                                    uint32_t k, uint64_t* out_ids, float* out_scores, int phase);
+
 /* Kernel-selection knobs for A/B measurements and tests; results never depend on them. Defaults can also be set with
  * the environment variables NVDB_B200_MMA_SEED / NVDB_B200_GEMV_CTAS / NVDB_B200_MMA_2CTA at index creation. */
 enum {

@@ -88,6 +88,7 @@ _sig = {
     "nvdb_b200_exchange_destroy": (_i, [_vp]),
     "nvdb_b200_search_exchange_device": (_i, [_vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_search_exchange": (_i, [_vp, _vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
+    "nvdb_b200_search_exchange_split": (_i, [_vp, _vp, _vp, _u32, _u32, _vp, _vp, _i]),
     "nvdb_b200_launch_count": (_u64, []),
     "nvdb_b200_index_profile": (_i, [_vp, _i]),
     "nvdb_b200_index_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_u32)]),

@@ -1210,13 +1210,15 @@ int nvdb_b200_search_exchange_device(nvdb_b200_index* idx, nvdb_b200_exchange* x
   return rc;
 }
 
-int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
-                              uint32_t k, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing) {
+// phases: 3 = the whole step (scan + push + wait + merge, results to the host); 1 = local scan + push only; 2 = wait +
+// merge + results of the epoch a phase-1 call of this rank started.
+static int search_exchange_host(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
+                                uint32_t k, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing, int phases) {
   if (timing) *timing = nvdb_b200_timing{};
   if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
   if (!x) return fail(idx, NVDB_B200_ERR_ARG, "exchange is NULL");
   if (nq == 0 || k == 0) return NVDB_B200_OK;
-  if (!queries_host) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if ((phases & 1) && !queries_host) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
   if ((out_ids == nullptr) != (out_scores == nullptr)) return fail(idx, NVDB_B200_ERR_ARG, "give both output buffers or none");
   std::lock_guard<std::mutex> g(idx->mu);
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
@@ -1230,26 +1232,43 @@ int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const
   if ((rc = adopt_stream(idx, s))) return rc;
   uint64_t* d_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
   float* d_scores = (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
-  std::memcpy(idx->h_pin[0], queries_host, qbytes);
-  if (timing) CK(cudaEventRecord(idx->ev[0], s), "event");
-  CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
-  if (timing) CK(cudaEventRecord(idx->ev[1], s), "event");
   const uint64_t l0 = g_launches.load(std::memory_order_relaxed);
-  idx->in_exchange = true;
-  rc = search_exchange_impl(idx, x, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s);
-  idx->in_exchange = false;
-  if (rc) return rc;
+  if (timing) CK(cudaEventRecord(idx->ev[0], s), "event");
+  if (phases & 1) {
+    std::memcpy(idx->h_pin[0], queries_host, qbytes);
+    CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
+  }
+  if (timing) CK(cudaEventRecord(idx->ev[1], s), "event");
+  if (phases == 3) {
+    idx->in_exchange = true;
+    rc = search_exchange_impl(idx, x, (const float*)idx->d_ws[WS_QUERIES], nq, k, d_ids, d_scores, s);
+    idx->in_exchange = false;
+    if (rc) return rc;
+  } else if (phases == 1) {  // local result into the exchange's staging buffer, then push without waiting
+    const size_t nk = (size_t)nq * k, words = nk + (nk + 1) / 2;
+    if (words * 8u > x->slot_bytes) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: packed result larger than the slot");
+    if (idx->device != x->device) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: index and exchange live on different devices");
+    uint64_t* l_ids = reinterpret_cast<uint64_t*>(x->staging);
+    if ((rc = search_device_impl(idx, (const float*)idx->d_ws[WS_QUERIES], nq, k, l_ids, reinterpret_cast<float*>(l_ids + nk), s,
+                                 nullptr, nullptr)))
+      return rc;
+    if ((rc = nvdb_b200_exchange_merge(x, x->staging, nq, k, nullptr, nullptr, 1, s))) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
+  } else {
+    if ((rc = nvdb_b200_exchange_merge(x, nullptr, nq, k, d_ids, d_scores, 2, s))) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
+  }
   if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
   char* hp = (char*)idx->h_pin[1];
-  if (out_ids) CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
+  if (out_ids && (phases & 2)) CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
   if (timing) CK(cudaEventRecord(idx->ev[3], s), "event");
   CK(cudaStreamSynchronize(s), "search sync");
-  uint32_t st = 0;
-  if ((rc = nvdb_b200_exchange_status(x, &st))) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
-  if (st != 0) return fail(idx, NVDB_B200_ERR_CUDA, nvdb_b200_exchange_last_error(x));
-  if (out_ids) {
-    std::memcpy(out_ids, hp, ibytes);
-    std::memcpy(out_scores, hp + ibytes, sbytes);
+  if (phases & 2) {
+    uint32_t st = 0;
+    if ((rc = nvdb_b200_exchange_status(x, &st))) return fail(idx, rc, nvdb_b200_exchange_last_error(x));
+    if (st != 0) return fail(idx, NVDB_B200_ERR_CUDA, nvdb_b200_exchange_last_error(x));
+    if (out_ids) {
+      std::memcpy(out_ids, hp, ibytes);
+      std::memcpy(out_scores, hp + ibytes, sbytes);
+    }
   }
   if (timing) {
     cudaEventElapsedTime(&timing->h2d_ms, idx->ev[0], idx->ev[1]);
@@ -1260,6 +1279,17 @@ int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const
     timing->path = (uint32_t)idx->path;
   }
   return NVDB_B200_OK;
+}
+
+int nvdb_b200_search_exchange(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
+                              uint32_t k, uint64_t* out_ids, float* out_scores, nvdb_b200_timing* timing) {
+  return search_exchange_host(idx, x, queries_host, nq, k, out_ids, out_scores, timing, 3);
+}
+
+int nvdb_b200_search_exchange_split(nvdb_b200_index* idx, nvdb_b200_exchange* x, const float* queries_host, uint32_t nq,
+                                    uint32_t k, uint64_t* out_ids, float* out_scores, int phase) {
+  if (phase != 1 && phase != 2) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange_split: phase must be 1 (scan + push) or 2 (merge)");
+  return search_exchange_host(idx, x, queries_host, nq, k, out_ids, out_scores, nullptr, phase);
 }
 
 int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t nq, uint32_t k, uint64_t* out_ids,

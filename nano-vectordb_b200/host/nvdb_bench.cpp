@@ -80,6 +80,17 @@ class ShardedIndex {
       std::vector<float> wsc(nk);
       for (auto* h : shards_) nvdb::detail::check(nvdb_b200_search(h, q, nq, k, wi.data(), wsc.data(), nullptr), h);
     }
+    if (shared_device_) {
+      // Shards sharing a device (NVDB_BENCH_OVERSUBSCRIBE): kernels that wait for one another must not be separate
+      // launches on one GPU, so every shard scans + pushes first and only then every shard waits + merges.
+      for (size_t s = 0; s < S; ++s)
+        nvdb::detail::check(nvdb_b200_search_exchange_split(shards_[s], xchg_[s], q, nq, k, nullptr, nullptr, 1), shards_[s]);
+      for (size_t s = 0; s < S; ++s)
+        nvdb::detail::check(nvdb_b200_search_exchange_split(shards_[s], xchg_[s], q, nq, k, s == 0 ? ids.data() : nullptr,
+                                                            s == 0 ? sc.data() : nullptr, 2), shards_[s]);
+      if (t0) *t0 = nvdb_b200_timing{};
+      return;
+    }
     std::vector<std::thread> th;
     std::vector<int> rc(S, 0);
     std::vector<nvdb_b200_timing> tt(S);

@@ -117,30 +117,36 @@ def test_peer_exchange_logical_ranks_equal_packed_merge(nv, S, nq, k):
             x.close()
 
 
-def test_peer_exchange_fused_two_ranks_two_streams(nv, monkeypatch):
-    """The fused form (push + wait + merge in ONE launch per rank): two ranks on one GPU, each on its own stream, so the
-    two kernels are resident together and really wait for each other's flags."""
+def test_peer_exchange_fused_kernel_with_posted_peers(nv, monkeypatch):
+    """The fused form (push + wait + merge in ONE launch) of one rank at a time. Kernels that wait for one another must
+    never be separate launches on one GPU (nothing guarantees that they are resident together), so the other ranks of
+    the epoch run the split form on the SAME stream: their pushes are enqueued before the fused launch, whose wait then
+    finds every flag, and their merges after it. The rank that runs fused rotates over the epochs."""
     monkeypatch.setenv("NVDB_B200_XCHG_TIMEOUT_MS", "5000")
     dev = torch.device("cuda", 0)
-    S, nq, k = 2, 64, 10
+    S, nq, k = 3, 64, 10
     xs = [nv.capi.PeerExchange(0, S, r, 8 * nv.packed_words(nq, k)) for r in range(S)]
     wins = [x.window() for x in xs]
     for x in xs:
         x.connect(windows=wins)
-    streams = [torch.cuda.Stream(device=dev) for _ in range(S)]
+    sp = torch.cuda.current_stream().cuda_stream
     try:
-        for epoch in range(4):
+        for epoch in range(6):
+            fused = epoch % S
             packed = _packed_lists(S, nq, k, 7 + epoch, dev)
             ref_ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
             ref_sc = torch.empty((nq, k), dtype=torch.float32, device=dev)
-            nv.merge_topk_packed_device(0, packed.data_ptr(), S, nq, k, ref_ids.data_ptr(), ref_sc.data_ptr(),
-                                        torch.cuda.current_stream().cuda_stream)
-            torch.cuda.synchronize()
+            nv.merge_topk_packed_device(0, packed.data_ptr(), S, nq, k, ref_ids.data_ptr(), ref_sc.data_ptr(), sp)
             outs = [(torch.zeros((nq, k), dtype=torch.int64, device=dev), torch.zeros((nq, k), dtype=torch.float32, device=dev))
                     for _ in range(S)]
             for r, x in enumerate(xs):
-                x.merge(packed[r].data_ptr(), nq, k, outs[r][0].data_ptr(), outs[r][1].data_ptr(), phases=nv.capi.XCHG_FUSED,
-                        stream=streams[r].cuda_stream)
+                if r != fused:
+                    x.merge(packed[r].data_ptr(), nq, k, None, None, phases=nv.capi.XCHG_PUSH, stream=sp)
+            xs[fused].merge(packed[fused].data_ptr(), nq, k, outs[fused][0].data_ptr(), outs[fused][1].data_ptr(),
+                            phases=nv.capi.XCHG_FUSED, stream=sp)
+            for r, x in enumerate(xs):
+                if r != fused:
+                    x.merge(None, nq, k, outs[r][0].data_ptr(), outs[r][1].data_ptr(), phases=nv.capi.XCHG_MERGE, stream=sp)
             torch.cuda.synchronize()
             for r in range(S):
                 assert xs[r].status() == 0, "a rank timed out waiting for its peer"
@@ -207,12 +213,25 @@ def test_two_process_peer_exchange_equals_nccl_and_unsharded():
     assert "PEER_EXCHANGE_OK" in r.stdout
 
 
+def _split_rank_push(nv, x, idx, q_dev, nq, k, packed, sp):
+    """a rank in the split form: local scan into a packed buffer + push (no wait)"""
+    if idx is None:
+        x.merge(None, nq, k, None, None, phases=nv.capi.XCHG_PUSH, stream=sp)
+        return
+    ids_view = packed[:nq * k].view(nq, k)
+    sc_view = packed[nq * k:].view(torch.float32)[:nq * k].view(nq, k)
+    idx.search_device(q_dev.data_ptr(), nq, k, ids_view.data_ptr(), sc_view.data_ptr(), sp)
+    x.merge(packed.data_ptr(), nq, k, None, None, phases=nv.capi.XCHG_PUSH, stream=sp)
+
+
 @pytest.mark.parametrize("dt", ["f16", "i8", "f32"])
 @pytest.mark.parametrize("n_total,k,nq", [(40_000, 10, 1), (30_001, 100, 1), (20_000, 10, 5), (9_000, 16, 40)])
 def test_search_exchange_one_call_per_rank(nv, oracle, monkeypatch, dt, n_total, k, nq):
-    """nvdb_b200_search_exchange_device: scan + exchange + merge per rank (ONE launch when the streaming scan is a single
-    pass: its last CTA pushes, waits and merges). Two logical ranks on one GPU, each on its own stream, twice (slot
-    parity) == the oracle's top-k of the whole base, on both ranks."""
+    """nvdb_b200_search_exchange_device: scan + exchange + merge of one rank (ONE launch when the streaming scan is a
+    single pass: its last CTA pushes, waits and merges). Two logical ranks on one GPU and ONE stream: the rank under test
+    runs the one-call form after its peer's split-form push and before the peer's merge (no kernel ever waits for a
+    launch that is not in front of it); the fused rank alternates, three rounds (slot parity) == the oracle's top-k of
+    the whole base, on both ranks."""
     monkeypatch.setenv("NVDB_B200_XCHG_TIMEOUT_MS", "10000")
     dtype, d, S = DT[dt], 128, 2
     dev = torch.device("cuda", 0)
@@ -230,21 +249,25 @@ def test_search_exchange_one_call_per_rank(nv, oracle, monkeypatch, dt, n_total,
                                          row_offset=r0)
         idx.set_path(nv.PATH_GEMV)
         shards.append(idx)
-    streams = [torch.cuda.Stream(device=dev) for _ in range(S)]
+    stream = torch.cuda.Stream(device=dev)
+    sp = stream.cuda_stream
+    packed = torch.zeros(nv.packed_words(nq, k), dtype=torch.int64, device=dev)
     try:
-        for rep in range(3):
+        for rep in range(4):
+            fused = rep % S
+            other = 1 - fused
             queries = np.ascontiguousarray(f[rng.integers(0, n_total, nq)] + (0.01 * rng.standard_normal((nq, d))).astype(np.float32))
             q_dev = torch.from_numpy(queries).to(dev)
             outs = [(torch.zeros((nq, k), dtype=torch.int64, device=dev), torch.zeros((nq, k), dtype=torch.float32, device=dev))
                     for _ in range(S)]
             torch.cuda.synchronize()
+            _split_rank_push(nv, xs[other], shards[other], q_dev, nq, k, packed, sp)
             l0 = nv.launch_count()
-            for r in range(S):
-                xs[r].search(shards[r], q_dev.data_ptr(), nq, k, outs[r][0].data_ptr(), outs[r][1].data_ptr(),
-                             streams[r].cuda_stream)
-            torch.cuda.synchronize()
+            xs[fused].search(shards[fused], q_dev.data_ptr(), nq, k, outs[fused][0].data_ptr(), outs[fused][1].data_ptr(), sp)
             if nq <= 4 and k <= 16:
-                assert nv.launch_count() - l0 == S, "single-pass streaming scans must take ONE launch per rank"
+                assert nv.launch_count() - l0 == 1, "a single-pass streaming scan must take ONE launch per rank"
+            xs[other].merge(None, nq, k, outs[other][0].data_ptr(), outs[other][1].data_ptr(), phases=nv.capi.XCHG_MERGE, stream=sp)
+            torch.cuda.synchronize()
             oids, osc = oracle.search_batch(dtype, base, scales, queries, k)
             for r in range(S):
                 assert xs[r].status() == 0
@@ -261,7 +284,8 @@ def test_search_exchange_one_call_per_rank(nv, oracle, monkeypatch, dt, n_total,
 
 
 def test_search_exchange_empty_shard_contributes_padding(nv, oracle):
-    """idx == NULL (a rank whose shard is empty) pushes padding; the other rank's result is its own top-k."""
+    """idx == NULL (a rank whose shard is empty) pushes padding; the other rank's result is its own top-k. Both orders:
+    the empty rank in the split form around the full rank's one-call form, then the other way round."""
     dev = torch.device("cuda", 0)
     n, d, k, nq = 300, 64, 10, 2
     base, _ = oracle.synth(F16, 5, 0, n, d)
@@ -271,17 +295,24 @@ def test_search_exchange_empty_shard_contributes_padding(nv, oracle):
     wins = [x.window() for x in xs]
     for x in xs:
         x.connect(windows=wins)
-    streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
-    outs = [(torch.zeros((nq, k), dtype=torch.int64, device=dev), torch.zeros((nq, k), dtype=torch.float32, device=dev)) for _ in range(2)]
+    stream = torch.cuda.Stream(device=dev)
+    sp = stream.cuda_stream
+    packed = torch.zeros(nv.packed_words(nq, k), dtype=torch.int64, device=dev)
     with nv.FlatIndexCuda.from_host(base, None, F16) as idx:
-        xs[0].search(idx, q_dev.data_ptr(), nq, k, outs[0][0].data_ptr(), outs[0][1].data_ptr(), streams[0].cuda_stream)
-        xs[1].search(None, q_dev.data_ptr(), nq, k, outs[1][0].data_ptr(), outs[1][1].data_ptr(), streams[1].cuda_stream)
-        torch.cuda.synchronize()
         oids, osc = oracle.search_batch(F16, base, None, queries, k)
-        for r in range(2):
-            assert xs[r].status() == 0
-            for qi in range(nq):
-                assert_topk_equal(outs[r][0].cpu().numpy().view(np.uint64)[qi], outs[r][1].cpu().numpy()[qi], oids[qi], osc[qi],
-                                  what=f"rank {r} q{qi}")
+        shards = [idx, None]
+        for fused in (0, 1):
+            other = 1 - fused
+            outs = [(torch.zeros((nq, k), dtype=torch.int64, device=dev), torch.zeros((nq, k), dtype=torch.float32, device=dev))
+                    for _ in range(2)]
+            _split_rank_push(nv, xs[other], shards[other], q_dev, nq, k, packed, sp)
+            xs[fused].search(shards[fused], q_dev.data_ptr(), nq, k, outs[fused][0].data_ptr(), outs[fused][1].data_ptr(), sp)
+            xs[other].merge(None, nq, k, outs[other][0].data_ptr(), outs[other][1].data_ptr(), phases=nv.capi.XCHG_MERGE, stream=sp)
+            torch.cuda.synchronize()
+            for r in range(2):
+                assert xs[r].status() == 0
+                for qi in range(nq):
+                    assert_topk_equal(outs[r][0].cpu().numpy().view(np.uint64)[qi], outs[r][1].cpu().numpy()[qi], oids[qi], osc[qi],
+                                      what=f"fused {fused} rank {r} q{qi}")
     for x in xs:
         x.close()
