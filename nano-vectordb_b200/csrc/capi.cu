@@ -70,6 +70,7 @@ struct nvdb_b200_index {
   int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
   int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 (default) / 2 whenever the shape allows
+  int tune_rows = 1;       // small batches of the exact path on the row-tile tensor kernel (scan_rows.cu): 0 never, 1 when the batch fits
   int tune_exact_tier2 = 1; // exact path: flagged queries get a second tensor-core pass with wider candidate lists (0: off;
                             // > 1: that many list entries instead of the default width, for A/B measurements)
   std::mutex mu;
@@ -262,6 +263,7 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
   if (const char* ev = getenv("NVDB_B200_MMA_2CTA")) h->tune_mma_2cta = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_FUSED_MERGE")) h->tune_fused_merge = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_EXACT_TIER2")) h->tune_exact_tier2 = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_ROWS")) h->tune_rows = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_XCHG_NO_ALLOC")) h->guard_no_alloc = atoi(ev) != 0;
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_switch, cudaEventDisableTiming);
@@ -914,6 +916,46 @@ bool mma_exact_supported(const nvdb_b200_index* idx, uint32_t k) {
 int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
                      float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* fallbacks);
 
+// Small batches: candidate scan on the row-tile kernel (scan_rows.cu: base rows on M, the whole batch resident as the B
+// operand) — one HBM pass, tensor work proportional to the batch. false = the batch / k' does not fit, use scan_mma*.
+bool rows_kernel_fits(const nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t kp, RowsPlan* plan) {
+  if (!idx->mma_ok || !idx->tune_rows) return false;
+  if ((reinterpret_cast<uintptr_t>(d_queries) & 15u) || (idx->dim % 4u)) return false;  // float4 reads of the queries
+  return scan_rows_plan((int)idx->dtype, nq, kp, idx->dim, idx->max_smem, plan);
+}
+
+int rows_candidate_scan(nvdb_b200_index* idx, const RowsPlan& plan, const float* d_queries, uint32_t nq, uint32_t kp,
+                        uint64_t* cand_ids, float* cand_apx, cudaStream_t stream, uint32_t* launches) {
+  const uint32_t tiles = (uint32_t)((idx->n + 127u) / 128u);
+  const int grid = (int)(tiles < (uint32_t)idx->num_sms ? tiles : (uint32_t)idx->num_sms);
+  int rc;
+  if ((rc = ensure_ws(idx, WS_PARTIAL, (size_t)nq * grid * kp * 8))) return rc;
+  cudaEvent_t* pev = nullptr;
+  if ((rc = prof_begin(idx, stream, &pev))) return rc;
+  RowsArgs a{};
+  a.queries = d_queries;
+  a.scales = idx->scales;
+  a.thr_init = nullptr;
+  a.partial = (uint64_t*)idx->d_ws[WS_PARTIAL];
+  a.n_rows = (uint32_t)idx->n;
+  a.dim = idx->dim;
+  a.kp = kp;
+  a.nq = nq;
+  a.num_tiles = tiles;
+  a.kchunks = (uint32_t)(((size_t)idx->dim * elem_size(idx->dtype) + 127) / 128);
+  a.lists = (uint32_t)grid;
+  a.bp = plan.bp;
+  a.nb = plan.nb;
+  a.cap = plan.cap;
+  a.stages = plan.stages;
+  CK(scan_rows_launch((int)idx->dtype, &idx->tmap_mma_b, a, grid, stream), "scan_rows launch");
+  if (pev) CK(cudaEventRecord(pev[1], stream), "profile event record");
+  CK(merge_partials_launch(a.partial, a.lists, nq, kp, 0, cand_ids, cand_apx, stream), "merge_partials launch");
+  if (pev) CK(cudaEventRecord(pev[2], stream), "profile event record");
+  if (launches) *launches += 2;
+  return NVDB_B200_OK;
+}
+
 // Candidate scan with k' = kp entries per query + exact re-score + certificate, enqueued on `stream`; the number of
 // flagged queries lands in the pinned word h_pin[2][0] (flags per query stay on the device, WS_X_FLAGS + 4).
 int mma_exact_enqueue(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint32_t kp,
@@ -928,7 +970,12 @@ int mma_exact_enqueue(nvdb_b200_index* idx, const float* d_queries, uint32_t nq,
   uint32_t* flags = nflag + 4;
   CK(cudaMemsetAsync(nflag, 0, 4, stream), "memset flag count");
   const int limbs = idx->dtype == kDtF16 ? 1 : 2;
-  if ((rc = mma_search_impl(idx, d_queries, nq, kp, cand_ids, cand_apx, stream, launches, limbs, nullptr, 0))) return rc;
+  RowsPlan rplan;
+  if (rows_kernel_fits(idx, d_queries, nq, kp, &rplan)) {
+    if ((rc = rows_candidate_scan(idx, rplan, d_queries, nq, kp, cand_ids, cand_apx, stream, launches))) return rc;
+  } else if ((rc = mma_search_impl(idx, d_queries, nq, kp, cand_ids, cand_apx, stream, launches, limbs, nullptr, 0))) {
+    return rc;
+  }
 
   RescoreArgs r{};
   r.base = idx->payload;
@@ -1361,6 +1408,7 @@ int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value) {
     case NVDB_B200_TUNE_FUSED_MERGE: idx->tune_fused_merge = value; break;
     case NVDB_B200_TUNE_MMA_RESIDENT: idx->tune_mma_resident = value; break;
     case NVDB_B200_TUNE_EXACT_TIER2: idx->tune_exact_tier2 = value; break;
+    case NVDB_B200_TUNE_ROWS: idx->tune_rows = value; break;
     default: return fail(idx, NVDB_B200_ERR_ARG, "unknown tuning knob");
   }
   return NVDB_B200_OK;

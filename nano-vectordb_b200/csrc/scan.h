@@ -103,6 +103,30 @@ cudaError_t scan_mma_prep_launch(int dtype, int limbs, const float* queries, uin
 cudaError_t scan_mma_launch(int dtype, int limbs, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, const MmaArgs& a,
                             cudaStream_t stream);
 
+// ---- tensor-core scan for small batches, base rows on M / queries on N (scan_rows.cu)
+struct RowsPlan {
+  uint32_t bp;      // queries padded to a multiple of 16 (columns per limb)
+  uint32_t nb;      // MMA N: f16 bp, i8 2 * bp
+  uint32_t cap;     // candidate-list capacity per query (power of two >= 4 * kp)
+  int stages;       // ring depth (16 KB per stage)
+  uint32_t smem_bytes;
+};
+struct RowsArgs {
+  const float* queries;   // [nq][dim] f32, 16-byte aligned
+  const float* scales;    // [n_rows] row scales (i8) or null
+  const float* thr_init;  // [nq] admission threshold seeds or null
+  uint64_t* partial;      // [nq][lists][kp] ordered keys (0 = empty); CTA j writes list j
+  uint32_t n_rows, dim, kp, nq;
+  uint32_t num_tiles;     // ceil(n_rows / 128)
+  uint32_t kchunks;       // ceil(dim * elem_size / 128)
+  uint32_t lists;         // lists per query in `partial` (>= grid)
+  uint32_t bp, nb, cap;
+  int stages;
+};
+bool scan_rows_plan(int dtype, uint32_t nq, uint32_t kp, uint32_t dim, int max_smem, RowsPlan* out);
+// tmap_base128: the base tensor map with 128-row boxes
+cudaError_t scan_rows_launch(int dtype, const CUtensorMap* tmap_base128, const RowsArgs& a, int grid, cudaStream_t stream);
+
 // ---- exact re-score + certificate of tensor-core candidates (rescore.cu)
 struct RescoreArgs {
   const void* base;          // payload

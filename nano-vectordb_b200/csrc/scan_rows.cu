@@ -1,0 +1,503 @@
+// scan_rows.cu — tensor-core flat scan for SMALL query batches (3 .. ~80 queries): BASE ROWS ON M, QUERIES ON N.
+//
+// Replaces the bench-side batched scan of the reference in the regime the reference itself measured (batch <= 8:
+// apps/nvdb_bench.cpp:99-131, Performance.md:289-290,395-402) and up to the point where a batch stops fitting in one
+// SM's shared memory. scan_mma.cu puts the queries on M: a batch of 8 still pays for a 128-row query tile, the query
+// tile(s) are re-streamed from L2 with every base tile (INT8: two limbs = twice the base bytes) and every admitted row
+// costs a 16-entry register-list insert in a divergent warp. Here the orientation is swapped:
+//
+//   A operand (M = 128, TMEM lanes)   = a tile of 128 BASE ROWS, streamed once from HBM by TMA (16 KB per 128-byte K chunk)
+//   B operand (N = 16 .. 256 columns) = ALL query limbs of the batch, converted once per CTA and RESIDENT in shared memory
+//                                       (f16: one fp16 limb per query; i8: two int8 limbs per query, limb 2 at column bp + q)
+//   D (TMEM, FP32 / S32)              = 128 rows x N scores, double buffered
+//
+// so the tensor work is 128 x N x D per tile instead of 128 x 256 x D, L2 -> SM traffic is the base bytes only, and the
+// kernel is bound by the HBM stream like the streaming scan (scan_gemv.cu) — one pass over the base for the whole batch.
+//
+//   warp 0      : TMA producer (base tiles only), STAGES-deep mbarrier ring, L2 evict_first
+//   warp 1      : tcgen05.mma issuer (one elected lane), 4 MMAs per K chunk
+//   warps 2..5  : epilogue, ONE THREAD PER BASE ROW: tcgen05.ld of its lane (its row's scores against every query), compare
+//                 with the query's threshold (a broadcast shared-memory word) and — rarely — append an ordered key to the
+//                 query's candidate list in shared memory (atomic slot). A list is compacted by one warp (bitonic sort, keep
+//                 the best k', raise the threshold) when it is half full. An append that finds its list full is kept as a
+//                 pending bit and retried after the compaction from the accumulators, which stay in TMEM until the tile is
+//                 done: nothing is ever dropped, whatever the data (first tile: every row qualifies for every query).
+//
+// Numerics are those of scan_mma.cu (same limb schemes, same FP32 epilogue order), so the candidates carry the same
+// approximate scores and the exact path's certificate (rescore.cu) holds unchanged.
+#include "common.cuh"
+#include "scan.h"
+#include "scan_mma_common.cuh"
+#include "tc_common.cuh"
+
+namespace nvdb_b200 {
+namespace {
+
+constexpr int kRowsThreads = 192;
+constexpr uint32_t kRowsTile = 128;          // base rows per tile == TMEM lanes == epilogue threads
+constexpr uint32_t kRowsStageBytes = kRowsTile * 128u;
+constexpr uint32_t kRowsMaxStages = 12;
+
+struct RowsSmem {
+  uint32_t stages_off, b_off, keys_off, par_off, cnt_off, bars_off, tmem_off, total, b_chunk_bytes;
+};
+
+__host__ __device__ inline RowsSmem rows_layout(uint32_t nb, uint32_t bp, uint32_t cap, uint32_t kchunks, int stages) {
+  RowsSmem L;
+  uint32_t off = 0;
+  L.stages_off = off;
+  off += (uint32_t)stages * kRowsStageBytes;
+  L.b_off = off;  // kchunks blocks of nb rows x 128 B, SWIZZLE_128B atoms of 8 rows (nb % 16 == 0 -> 1024-byte aligned blocks)
+  L.b_chunk_bytes = nb * 128u;
+  off += kchunks * L.b_chunk_bytes;
+  L.keys_off = off;  // [bp][cap] u64 candidate keys
+  off += bp * cap * 8u;
+  L.par_off = off;   // [bp] float4 {qs1, qs2, thr, -}
+  off += bp * 16u;
+  L.cnt_off = off;   // [bp] u32
+  off += bp * 4u;
+  off = (off + 7u) & ~7u;
+  L.bars_off = off;  // full[stages], empty[stages], tfull[2], tempty[2]
+  off += (2u * (uint32_t)stages + 4u) * 8u;
+  L.tmem_off = off;
+  off += 16u;
+  L.total = off + 1024u;  // slack for the 1024-byte alignment of the swizzled regions
+  return L;
+}
+
+// byte offset of (row r, byte c of the 128-byte K chunk) inside a SWIZZLE_128B block: 16-byte piece index XOR (r & 7)
+__device__ __forceinline__ uint32_t swz128(uint32_t r, uint32_t c) {
+  return (r >> 3) * 1024u + (r & 7u) * 128u + ((((c >> 4) ^ (r & 7u)) << 4) | (c & 15u));
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t atom_add_shared(uint32_t addr, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(addr), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// barrier over the 128 epilogue threads that also counts a predicate
+__device__ __forceinline__ uint32_t epi_bar_count(bool p) {
+  uint32_t n;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t"
+      "bar.red.popc.u32 %0, 1, 128, p;\n\t}"
+      : "=r"(n)
+      : "r"((uint32_t)p)
+      : "memory");
+  return n;
+}
+
+// One warp sorts list q (cap keys, entries >= c cleared) descending in shared memory, keeps the best kp and publishes the
+// new count and threshold. All 32 lanes call with the same arguments.
+__device__ __noinline__ void warp_compact(uint32_t keys_q, uint32_t cap, uint32_t c, uint32_t kp, uint32_t cnt_addr,
+                                          uint32_t thr_addr, uint32_t lane) {
+  for (uint32_t i = c + lane; i < cap; i += 32) sts_u64(keys_q + i * 8u, 0ull);
+  __syncwarp();
+  for (uint32_t size = 2; size <= cap; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t t = lane; t < (cap >> 1); t += 32) {
+        const uint32_t lo = 2 * t - (t & (stride - 1));
+        const uint32_t hi = lo + stride;
+        const bool desc = ((lo & size) == 0);
+        const uint64_t a = lds_u64(keys_q + lo * 8u), b = lds_u64(keys_q + hi * 8u);
+        if ((a < b) == desc) {
+          sts_u64(keys_q + lo * 8u, b);
+          sts_u64(keys_q + hi * 8u, a);
+        }
+      }
+      __syncwarp();
+    }
+  }
+  if (lane == 0) {
+    const uint32_t nc = c < kp ? c : kp;
+    sts_u32(cnt_addr, nc);
+    // admission is `>=` so that rows tying with the k'-th best reach the exact (score, id) ordering of the next sort
+    sts_f32(thr_addr, nc == kp ? key_score(lds_u64(keys_q + (kp - 1u) * 8u)) : -INFINITY);
+  }
+  __syncwarp();
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid_constant__ CUtensorMap tmap_base, const RowsArgs a) {
+  constexpr bool kI8 = (DT == kDtI8);
+  constexpr uint32_t ES = kI8 ? 1u : 2u, EPC = 128u / ES;  // elements per 128-byte chunk
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const RowsSmem L = rows_layout(a.nb, a.bp, a.cap, a.kchunks, a.stages);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars_off);
+  uint64_t* empty = full + a.stages;
+  uint64_t* tfull = empty + a.stages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
+  const uint32_t b_u32 = smem_u32(smem + L.b_off), keys_u32 = smem_u32(smem + L.keys_off);
+  const uint32_t par_u32 = smem_u32(smem + L.par_off), cnt_u32 = smem_u32(smem + L.cnt_off);
+
+  const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t j = blockIdx.x, P = gridDim.x;
+
+  if (tid == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull[b], 1);
+      mbar_init(&tempty[b], 4);  // one arrival per epilogue warp
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tc::tmem_alloc(tmem_slot, kTmemCols);
+  // the resident query operand starts as zeros: padding rows (columns past the batch), and the tail of a ragged last chunk
+  {
+    const uint32_t pieces = a.kchunks * L.b_chunk_bytes / 16u;
+    for (uint32_t i = tid; i < pieces; i += kRowsThreads) sts_v4(b_u32 + i * 16u, make_uint4(0u, 0u, 0u, 0u));
+  }
+  tc::fence_before_thread_sync();
+  __syncthreads();
+  tc::fence_after_thread_sync();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+  // The HBM stream starts before the queries are converted: every ring slot is free, so the producer lane can issue the
+  // first `stages` loads without waiting.
+  const uint64_t pol = l2_policy_evict_first();
+  uint32_t p_stage = 0, p_phase = 0, p_tile = j, p_kc = 0;  // producer position (warp 0, all lanes keep it in step)
+  if (warp == 0) {
+    if (lane == 0) tma_prefetch_desc(&tmap_base);
+    for (int s = 0; s < a.stages && p_tile < a.num_tiles; ++s) {
+      if (tc::elect_one_sync()) {
+        mbar_arrive_expect_tx(&full[p_stage], kRowsStageBytes);
+        tma_load_2d_hint(smem + L.stages_off + p_stage * kRowsStageBytes, &tmap_base, &full[p_stage], (int)(p_kc * EPC),
+                         (int)(p_tile * kRowsTile), pol);
+      }
+      __syncwarp();
+      if (++p_stage == (uint32_t)a.stages) {
+        p_stage = 0;
+        p_phase ^= 1;
+      }
+      if (++p_kc == a.kchunks) {
+        p_kc = 0;
+        p_tile += P;
+      }
+    }
+  }
+
+  // ---- query preparation: FP32 queries -> limb rows of the B operand (swizzled, K-major) + per-query scales. Same
+  // arithmetic as scan_mma.cu's prep kernels (oracle/nvdb_oracle.c: orc_query_limbs_f16 / _i8 restate it).
+  for (uint32_t q = warp; q < a.bp; q += kRowsThreads / 32) {
+    float qs1 = 0.f, qs2 = 0.f, thr0 = INFINITY;  // padding columns: zero rows, nothing is ever admitted
+    if (q < a.nq) {
+      const float* src = a.queries + (size_t)q * a.dim;
+      float amax = 0.f;
+      for (uint32_t i = lane * 4u; i < a.dim; i += 128u) {
+        const float4 v = *reinterpret_cast<const float4*>(src + i);
+        amax = fmaxf(fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+      thr0 = a.thr_init ? a.thr_init[q] : -INFINITY;
+      if constexpr (!kI8) {
+        int e = 0;
+        if (amax > 0.f && amax < INFINITY) {
+          e = -(ilogbf(amax) + 1);  // amax * 2^e in [0.5, 1)
+          e = e > 100 ? 100 : (e < -100 ? -100 : e);
+        }
+        qs1 = scalbnf(1.0f, -e);
+        for (uint32_t p8 = lane; p8 * 8u < a.dim; p8 += 32u) {  // 8 elements = one 16-byte piece of the fp16 row
+          const float4 v0 = *reinterpret_cast<const float4*>(src + p8 * 8u);
+          const float4 v1 = *reinterpret_cast<const float4*>(src + p8 * 8u + 4u);
+          const __half2 h0 = __floats2half2_rn(scalbnf(v0.x, e), scalbnf(v0.y, e));
+          const __half2 h1 = __floats2half2_rn(scalbnf(v0.z, e), scalbnf(v0.w, e));
+          const __half2 h2 = __floats2half2_rn(scalbnf(v1.x, e), scalbnf(v1.y, e));
+          const __half2 h3 = __floats2half2_rn(scalbnf(v1.z, e), scalbnf(v1.w, e));
+          uint4 w;
+          w.x = *reinterpret_cast<const uint32_t*>(&h0);
+          w.y = *reinterpret_cast<const uint32_t*>(&h1);
+          w.z = *reinterpret_cast<const uint32_t*>(&h2);
+          w.w = *reinterpret_cast<const uint32_t*>(&h3);
+          const uint32_t byte = p8 * 16u, kc = byte >> 7, c = byte & 127u;
+          sts_v4(b_u32 + kc * L.b_chunk_bytes + swz128(q, c), w);
+        }
+      } else {
+        const float s1 = (amax > 0.f && amax < INFINITY) ? __fdiv_rn(amax, 127.f) : 1.f;
+        const float inv1 = __fdiv_rn(1.f, s1);
+        const float s2 = __fdiv_rn(s1, 254.f);
+        const float inv2 = __fdiv_rn(1.f, s2);
+        qs1 = s1;
+        qs2 = s2;
+        for (uint32_t p16 = lane; p16 * 16u < a.dim; p16 += 32u) {  // 16 elements = one 16-byte piece of each int8 limb row
+          uint32_t w1[4], w2[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const float4 v = *reinterpret_cast<const float4*>(src + p16 * 16u + g * 4);
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+            uint32_t b1 = 0, b2 = 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              int x = __float2int_rn(__fmul_rn(vv[u], inv1));
+              x = x > 127 ? 127 : (x < -127 ? -127 : x);
+              const float r = __fmaf_rn(-(float)x, s1, vv[u]);
+              int y = __float2int_rn(__fmul_rn(r, inv2));
+              y = y > 127 ? 127 : (y < -127 ? -127 : y);
+              b1 |= ((uint32_t)x & 0xFFu) << (8 * u);
+              b2 |= ((uint32_t)y & 0xFFu) << (8 * u);
+            }
+            w1[g] = b1;
+            w2[g] = b2;
+          }
+          const uint32_t byte = p16 * 16u, kc = byte >> 7, c = byte & 127u;
+          sts_v4(b_u32 + kc * L.b_chunk_bytes + swz128(q, c), make_uint4(w1[0], w1[1], w1[2], w1[3]));
+          sts_v4(b_u32 + kc * L.b_chunk_bytes + swz128(a.bp + q, c), make_uint4(w2[0], w2[1], w2[2], w2[3]));
+        }
+      }
+    }
+    if (lane == 0) {
+      asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(par_u32 + q * 16u), "f"(qs1), "f"(qs2), "f"(thr0), "f"(0.f) : "memory");
+      sts_u32(cnt_u32 + q * 4u, 0u);
+    }
+  }
+  // generic-proxy writes of the B operand -> visible to the tensor core's (async proxy) shared-memory reads
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+
+  if (warp == 0) {
+    // ===== TMA producer (continues after the prologue's first loads) =====
+    while (p_tile < a.num_tiles) {
+      mbar_wait(&empty[p_stage], p_phase ^ 1);
+      if (tc::elect_one_sync()) {
+        mbar_arrive_expect_tx(&full[p_stage], kRowsStageBytes);
+        tma_load_2d_hint(smem + L.stages_off + p_stage * kRowsStageBytes, &tmap_base, &full[p_stage], (int)(p_kc * EPC),
+                         (int)(p_tile * kRowsTile), pol);
+      }
+      __syncwarp();
+      if (++p_stage == (uint32_t)a.stages) {
+        p_stage = 0;
+        p_phase ^= 1;
+      }
+      if (++p_kc == a.kchunks) {
+        p_kc = 0;
+        p_tile += P;
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====
+    const uint32_t idesc = kI8 ? tc::idesc_s8_s32(kRowsTile, a.nb) : tc::idesc_f16_f32(kRowsTile, a.nb);
+    uint32_t stage = 0, phase = 0, it = 0;
+    for (uint32_t tile = j; tile < a.num_tiles; tile += P, ++it) {
+      const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
+      mbar_wait(&tempty[buf], bphase ^ 1);
+      tc::fence_after_thread_sync();
+      const uint32_t acc = tmem_base + buf * kAccColsPerBuf;
+      for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
+        mbar_wait(&full[stage], phase);
+        tc::fence_after_thread_sync();
+        const uint64_t adesc = tc::smem_desc_k128(smem_u32(smem + L.stages_off + stage * kRowsStageBytes));
+        const uint64_t bdesc = tc::smem_desc_k128(b_u32 + kc * L.b_chunk_bytes);
+        if (tc::elect_one_sync()) {
+#pragma unroll
+          for (uint32_t k4 = 0; k4 < 4; ++k4) {  // 4 x 32 bytes of K per 128-byte chunk (UMMA_K = 16 f16 / 32 i8)
+            const uint32_t accumulate = (uint32_t)(kc > 0 || k4 > 0);
+            if constexpr (kI8)
+              tc::mma_i8_ss(acc, adesc + 2 * k4, bdesc + 2 * k4, idesc, accumulate);
+            else
+              tc::mma_f16_ss(acc, adesc + 2 * k4, bdesc + 2 * k4, idesc, accumulate);
+          }
+          tc::mma_commit(&empty[stage]);
+          if (kc + 1 == a.kchunks) tc::mma_commit(&tfull[buf]);
+        }
+        __syncwarp();
+        if (++stage == (uint32_t)a.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===== epilogue: one thread per base row (== TMEM lane) =====
+    const uint32_t qd = warp & 3;                // the TMEM lane quadrant this warp may read
+    const uint32_t rl = qd * 32 + lane;          // row within the tile
+    const uint32_t ew = warp - 2;                // 0..3: compaction duty for queries ew, ew + 4, ...
+    const uint32_t lane_addr = tmem_base + ((qd * 32u) << 16);
+    const uint32_t ngroups = a.bp >> 4;          // groups of 16 queries
+    const uint32_t half_cap = a.cap >> 1;
+
+    // score of (this row, query q) from the raw accumulators, in scan_mma.cu's fixed FP32 order
+    auto score_of = [&](const float4& p, uint32_t v, uint32_t w, float rs) -> float {
+      if constexpr (kI8) {
+        const float t = __fmul_rn(p.x, (float)(int)v);  // |I| < 2^24: exact conversions
+        return __fmul_rn(__fmaf_rn(p.y, (float)(int)w, t), rs);
+      } else {
+        return __fmul_rn(__uint_as_float(v), p.x);      // power-of-two rescale: exact
+      }
+    };
+
+    uint32_t it = 0;
+    for (uint32_t tile = j; tile < a.num_tiles; tile += P, ++it) {
+      const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
+      const uint32_t row = tile * kRowsTile + rl;
+      const bool row_ok = row < a.n_rows;
+      float rs = 1.f;
+      if constexpr (kI8) rs = row_ok ? __ldg(a.scales + row) : 0.f;
+      mbar_wait(&tfull[buf], bphase);
+      tc::fence_after_thread_sync();
+      const uint32_t acc = lane_addr + buf * kAccColsPerBuf;
+      uint64_t pend_lo = 0ull, pend_hi = 0ull;  // queries whose append found the list full (bit q)
+      bool pushed = false;
+
+      // ---- offers
+#pragma unroll 1
+      for (uint32_t g = 0; g < ngroups; ++g) {
+        uint32_t v[16], w[16];
+        tmem_ld16(acc + g * 16u, v);
+        if constexpr (kI8) tmem_ld16(acc + a.bp + g * 16u, w);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const uint32_t q = g * 16u + (uint32_t)i;
+          const float4 p = lds_f4(par_u32 + q * 16u);
+          const float s = score_of(p, v[i], kI8 ? w[i] : 0u, rs);
+          if (s >= p.z && row_ok) {
+            const uint32_t slot = atom_add_shared(cnt_u32 + q * 4u, 1u);
+            if (slot < a.cap) {
+              sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
+              pushed = true;
+            } else if (q < 64u) {
+              pend_lo |= 1ull << q;
+            } else {
+              pend_hi |= 1ull << (q - 64u);
+            }
+          }
+        }
+      }
+
+      // ---- list maintenance; appends that found their list full are retried from TMEM after the compaction
+      for (;;) {
+        if (epi_bar_count(pushed || (pend_lo | pend_hi) != 0ull) == 0u) break;  // nothing touched a list in this round
+        for (uint32_t q = ew; q < a.nq; q += 4) {
+          const uint32_t c = lds_u32(cnt_u32 + q * 4u);
+          if (c >= half_cap)
+            warp_compact(keys_u32 + q * a.cap * 8u, a.cap, c < a.cap ? c : a.cap, a.kp, cnt_u32 + q * 4u, par_u32 + q * 16u + 8u, lane);
+        }
+        if (epi_bar_count((pend_lo | pend_hi) != 0ull) == 0u) break;            // compactions visible; nobody is waiting
+        pushed = false;
+#pragma unroll 1
+        for (uint32_t g = 0; g < ngroups; ++g) {
+          const uint32_t bits = (uint32_t)(((g < 4u) ? (pend_lo >> (g * 16u)) : (pend_hi >> ((g - 4u) * 16u))) & 0xFFFFull);
+          if (!__any_sync(0xffffffffu, bits != 0u)) continue;  // tcgen05.ld is warp-collective: a warp-uniform decision
+          uint32_t v[16], w[16];
+          tmem_ld16(acc + g * 16u, v);
+          if constexpr (kI8) tmem_ld16(acc + a.bp + g * 16u, w);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            if (bits & (1u << i)) {
+              const uint32_t q = g * 16u + (uint32_t)i;
+              const float4 p = lds_f4(par_u32 + q * 16u);
+              const float s = score_of(p, v[i], kI8 ? w[i] : 0u, rs);
+              bool done = true;
+              if (s >= p.z) {
+                const uint32_t slot = atom_add_shared(cnt_u32 + q * 4u, 1u);
+                if (slot < a.cap) {
+                  sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
+                  pushed = true;
+                } else {
+                  done = false;
+                }
+              }
+              if (done) {
+                if (q < 64u) pend_lo &= ~(1ull << q);
+                else pend_hi &= ~(1ull << (q - 64u));
+              }
+            }
+          }
+        }
+      }
+      tc::fence_before_thread_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[buf]);
+    }
+
+    // ---- this CTA's best k' per query -> partial[q][cta][k'] (sorted descending, 0 = empty)
+    named_bar_sync(1, 128);
+    for (uint32_t q = ew; q < a.nq; q += 4) {
+      const uint32_t c = lds_u32(cnt_u32 + q * 4u);
+      warp_compact(keys_u32 + q * a.cap * 8u, a.cap, c < a.cap ? c : a.cap, a.kp, cnt_u32 + q * 4u, par_u32 + q * 16u + 8u, lane);
+      const uint32_t nc = lds_u32(cnt_u32 + q * 4u);
+      uint64_t* out = a.partial + ((size_t)q * a.lists + j) * a.kp;
+      for (uint32_t jj = lane; jj < a.kp; jj += 32) out[jj] = jj < nc ? lds_u64(keys_u32 + (q * a.cap + jj) * 8u) : 0ull;
+    }
+  }
+
+  tc::fence_before_thread_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, kTmemCols);
+}
+
+}  // namespace
+
+// Shapes this kernel takes: nq queries whose limb rows (+ candidate lists) fit next to a >= 4-deep ring.
+bool scan_rows_plan(int dtype, uint32_t nq, uint32_t kp, uint32_t dim, int max_smem, RowsPlan* out) {
+  if (dtype != kDtF16 && dtype != kDtI8) return false;
+  if (nq == 0 || nq > 128u) return false;
+  const uint32_t es = dtype == kDtF16 ? 2u : 1u;
+  const uint32_t bp = (nq + 15u) & ~15u;
+  const uint32_t nb = dtype == kDtF16 ? bp : 2u * bp;
+  if (nb > kAccColsPerBuf) return false;
+  uint32_t cap = 64;
+  while (cap < 4u * kp) cap <<= 1;  // a list is compacted when half full: at least k' free slots afterwards
+  if (cap > 4096u) return false;
+  const uint32_t kchunks = (dim * es + 127u) / 128u;
+  for (int st = (int)kRowsMaxStages; st >= 4; --st) {
+    if (rows_layout(nb, bp, cap, kchunks, st).total <= (uint32_t)max_smem) {
+      out->bp = bp;
+      out->nb = nb;
+      out->cap = cap;
+      out->stages = st;
+      out->smem_bytes = rows_layout(nb, bp, cap, kchunks, st).total;
+      return true;
+    }
+  }
+  return false;
+}
+
+cudaError_t scan_rows_launch(int dtype, const CUtensorMap* tmap_base128, const RowsArgs& a, int grid, cudaStream_t stream) {
+  const RowsSmem L = rows_layout(a.nb, a.bp, a.cap, a.kchunks, a.stages);
+  cudaError_t e;
+  if (dtype == kDtF16) {
+    auto kern = scan_rows_kernel<kDtF16>;
+    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total)) != cudaSuccess) return e;
+    kern<<<grid, kRowsThreads, L.total, stream>>>(*tmap_base128, a);
+  } else if (dtype == kDtI8) {
+    auto kern = scan_rows_kernel<kDtI8>;
+    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total)) != cudaSuccess) return e;
+    kern<<<grid, kRowsThreads, L.total, stream>>>(*tmap_base128, a);
+  } else {
+    return cudaErrorInvalidValue;
+  }
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace nvdb_b200

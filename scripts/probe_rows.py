@@ -1,0 +1,83 @@
+#!/usr/bin/env python
+"""Row-tile kernel probe: parity on a small case, then ms per batch at full size (2,903,054 x 768) with the knob on / off.
+  python scripts/probe_rows.py [small|perf] ..."""
+import importlib
+import json
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+nv = importlib.import_module("nano-vectordb_b200")
+dev = torch.device("cuda", 0)
+SEED, DIM = 20240229, 768
+
+
+def queries(n, d, nq, stream):
+    q = torch.empty((nq, d), dtype=torch.float32, device=dev)
+    for i in range(nq):
+        nv.synth_fill_device(0, nv.F32, 1, d, SEED, (i * 104729) % n, q[i].data_ptr(), None, stream.cuda_stream)
+    stream.synchronize()
+    return q + 1e-3 * torch.randn_like(q)
+
+
+def small():
+    st = torch.cuda.Stream(device=dev)
+    for dt in (nv.F16, nv.I8):
+        for n, d in ((20000, 128), (3000, 768)):
+            with nv.FlatIndexCuda.synthetic(dt, n, d, SEED) as idx:
+                for nq in (3, 8, 64):
+                    q = queries(n, d, nq, st).cpu().numpy()
+                    idx.set_path(nv.PATH_GEMV)
+                    g = idx.search_topk_dot_batch(q, 10)
+                    idx.set_path(nv.PATH_MMA_EXACT)
+                    x = idx.search_topk_dot_batch(q, 10)
+                    ok = np.array_equal(g[0], x[0]) and np.array_equal(g[1].view(np.uint32), x[1].view(np.uint32))
+                    print(f"small dt={dt} n={n} d={d} nq={nq}: {'OK' if ok else 'MISMATCH'} stats={idx.exact_stats(reset=True)}", flush=True)
+                    if not ok:
+                        print(g[0][0], x[0][0], g[1][0], x[1][0])
+                        sys.exit(1)
+
+
+def perf():
+    st = torch.cuda.Stream(device=dev)
+    n = 2_903_054
+    for dt, name in ((nv.F16, "f16"), (nv.I8, "i8")):
+        with nv.FlatIndexCuda.synthetic(dt, n, DIM, SEED) as idx:
+            q = queries(n, DIM, 128, st)
+            qh = q.cpu().numpy()
+            out_ids = torch.empty((128, 10), dtype=torch.int64, device=dev)
+            out_sc = torch.empty((128, 10), dtype=torch.float32, device=dev)
+            for rows in (1, 0):
+                idx.set_tuning(7, rows)
+                for b in (2, 3, 8, 16, 32, 64, 80, 128):
+                    idx.set_path(nv.PATH_MMA_EXACT)
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    with torch.cuda.stream(st):
+                        for _ in range(3):
+                            idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                        st.synchronize()
+                        idx.profile(True)
+                        e0.record(st)
+                        for _ in range(20):
+                            idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                        e1.record(st)
+                        st.synchronize()
+                    scan_ms, merge_ms, calls = idx.profile_read()
+                    idx.profile(False)
+                    import time
+                    t0 = time.perf_counter()
+                    for _ in range(10):
+                        idx.search_topk_dot_batch(qh[:b], 10)
+                    e2e = (time.perf_counter() - t0) * 100
+                    print(json.dumps({"dtype": name, "rows_kernel": rows, "batch": b, "ms": e0.elapsed_time(e1) / 20,
+                                      "scan_ms": scan_ms / max(calls, 1), "merge_ms": merge_ms / max(calls, 1), "e2e_ms": e2e,
+                                      "fallbacks": idx.exact_stats(reset=True)[1]}), flush=True)
+
+
+if __name__ == "__main__":
+    for w in sys.argv[1:] or ["small"]:
+        globals()[w]()

@@ -98,7 +98,8 @@ def exchange():
     wins = [x.window() for x in xs]
     for x in xs:
         x.connect(windows=wins)
-    sp = torch.cuda.current_stream().cuda_stream
+    stream = torch.cuda.Stream(device=dev)   # a real stream: handle 0 means "the index's own stream" to the C ABI
+    sp = stream.cuda_stream
     n, d = 9000, 128
     shards = []
     for r in range(S):
