@@ -33,13 +33,17 @@
 namespace nvdb_b200 {
 namespace {
 
-constexpr int kRowsThreads = 192;
-constexpr uint32_t kRowsTile = 128;          // base rows per tile == TMEM lanes == epilogue threads
-constexpr uint32_t kRowsStageBytes = kRowsTile * 128u;
-constexpr uint32_t kRowsMaxStages = 12;
+constexpr int kRowsEpiWarps = 8;             // two per TMEM lane quadrant: each takes every other group of 16 queries
+constexpr int kRowsEpiThreads = kRowsEpiWarps * 32;
+constexpr int kRowsThreads = 64 + kRowsEpiThreads;
+constexpr uint32_t kRowsTile = 128;          // base rows per tile == TMEM lanes
+constexpr uint32_t kRowsChunkBytes = kRowsTile * 128u;  // one 128-byte K chunk of a tile: one TMA box
+constexpr uint32_t kRowsCps = 2;             // K chunks per ring stage (one barrier round trip per 32 KB)
+constexpr uint32_t kRowsStageBytes = kRowsCps * kRowsChunkBytes;
+constexpr uint32_t kRowsMaxStages = 6;
 
 struct RowsSmem {
-  uint32_t stages_off, b_off, keys_off, par_off, cnt_off, bars_off, tmem_off, total, b_chunk_bytes;
+  uint32_t stages_off, b_off, keys_off, par_off, cnt_off, wl_off, bars_off, tmem_off, total, b_chunk_bytes;
 };
 
 __host__ __device__ inline RowsSmem rows_layout(uint32_t nb, uint32_t bp, uint32_t cap, uint32_t kchunks, int stages) {
@@ -56,6 +60,8 @@ __host__ __device__ inline RowsSmem rows_layout(uint32_t nb, uint32_t bp, uint32
   off += bp * 16u;
   L.cnt_off = off;   // [bp] u32
   off += bp * 4u;
+  L.wl_off = off;    // compaction work lists: [2][4] {count, head, -, -} then [2][bp] query numbers
+  off += 32u + 2u * bp * 4u;
   off = (off + 7u) & ~7u;
   L.bars_off = off;  // full[stages], empty[stages], tfull[2], tempty[2]
   off += (2u * (uint32_t)stages + 4u) * 8u;
@@ -98,14 +104,14 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 __device__ __forceinline__ void sts_v4(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
-// barrier over the 128 epilogue threads that also counts a predicate
+// barrier over the epilogue threads that also counts a predicate
 __device__ __forceinline__ uint32_t epi_bar_count(bool p) {
   uint32_t n;
   asm volatile(
       "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t"
-      "bar.red.popc.u32 %0, 1, 128, p;\n\t}"
+      "bar.red.popc.u32 %0, 1, %2, p;\n\t}"
       : "=r"(n)
-      : "r"((uint32_t)p)
+      : "r"((uint32_t)p), "n"(kRowsEpiThreads)
       : "memory");
   return n;
 }
@@ -140,6 +146,47 @@ __device__ __noinline__ void warp_compact(uint32_t keys_q, uint32_t cap, uint32_
   __syncwarp();
 }
 
+// cap == 64 (k' <= 16): the same compaction in registers — two keys per lane, bitonic sort over shuffles (no shared-memory
+// round trip per stage: ~4x faster than the loop above, and compactions are what the epilogue waits for at its barrier).
+__device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, uint32_t m) {
+  const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, m), hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), m);
+  return ((uint64_t)hi << 32) | lo;
+}
+__device__ __noinline__ void warp_compact64(uint32_t keys_q, uint32_t c, uint32_t kp, uint32_t cnt_addr, uint32_t thr_addr,
+                                            uint32_t lane) {
+  uint64_t k0 = lane < c ? lds_u64(keys_q + lane * 8u) : 0ull;              // element lane
+  uint64_t k1 = lane + 32u < c ? lds_u64(keys_q + (lane + 32u) * 8u) : 0ull;  // element lane + 32
+#pragma unroll
+  for (uint32_t size = 2; size <= 64; size <<= 1) {
+#pragma unroll
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride == 32) {  // size == 64: partner lives in the same lane; descending -> the larger key at the lower element
+        if (k0 < k1) {
+          const uint64_t t = k0;
+          k0 = k1;
+          k1 = t;
+        }
+      } else {
+        const bool lower = (lane & stride) == 0;
+        const uint64_t o0 = shfl_xor_u64(k0, stride), o1 = shfl_xor_u64(k1, stride);
+        const bool desc0 = (lane & size) == 0 || size == 64;           // element lane:      (e & size) == 0
+        const bool desc1 = ((lane + 32u) & size) == 0 || size == 64;   // element lane + 32
+        const bool max0 = lower == desc0, max1 = lower == desc1;
+        k0 = max0 ? (k0 > o0 ? k0 : o0) : (k0 < o0 ? k0 : o0);
+        k1 = max1 ? (k1 > o1 ? k1 : o1) : (k1 < o1 ? k1 : o1);
+      }
+    }
+  }
+  const uint32_t nc = c < kp ? c : kp;
+  if (lane < kp) sts_u64(keys_q + lane * 8u, k0);                       // kp <= 16: the best kp sit in lanes 0 .. kp-1
+  const uint64_t kth = __shfl_sync(0xffffffffu, (uint32_t)(k0 >> 32), kp - 1u);
+  if (lane == 0) {
+    sts_u32(cnt_addr, nc);
+    sts_f32(thr_addr, nc == kp ? ordered_to_float((uint32_t)kth) : -INFINITY);
+  }
+  __syncwarp();
+}
+
 template <int DT>
 __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid_constant__ CUtensorMap tmap_base, const RowsArgs a) {
   constexpr bool kI8 = (DT == kDtI8);
@@ -154,9 +201,11 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
   const uint32_t b_u32 = smem_u32(smem + L.b_off), keys_u32 = smem_u32(smem + L.keys_off);
   const uint32_t par_u32 = smem_u32(smem + L.par_off), cnt_u32 = smem_u32(smem + L.cnt_off);
+  const uint32_t wl_u32 = smem_u32(smem + L.wl_off);   // [2] {count, head, -, -}, then [2][bp] queued query numbers
 
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t j = blockIdx.x, P = gridDim.x;
+  const uint32_t nsg = (a.kchunks + kRowsCps - 1u) / kRowsCps;  // ring stages per tile
 
   if (tid == 0) {
     for (int s = 0; s < a.stages; ++s) {
@@ -165,10 +214,11 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull[b], 1);
-      mbar_init(&tempty[b], 4);  // one arrival per epilogue warp
+      mbar_init(&tempty[b], kRowsEpiWarps);  // one arrival per epilogue warp
     }
     mbar_fence_init();
   }
+  if (tid < 8) sts_u32(wl_u32 + tid * 4u, 0u);
   if (warp == 2) tc::tmem_alloc(tmem_slot, kTmemCols);
   // the resident query operand starts as zeros: padding rows (columns past the batch), and the tail of a ragged last chunk
   {
@@ -180,28 +230,33 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
   tc::fence_after_thread_sync();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
-  // The HBM stream starts before the queries are converted: every ring slot is free, so the producer lane can issue the
-  // first `stages` loads without waiting.
+  // One ring stage = up to kRowsCps K chunks of one tile (one box each). The producer position is kept by all lanes.
   const uint64_t pol = l2_policy_evict_first();
-  uint32_t p_stage = 0, p_phase = 0, p_tile = j, p_kc = 0;  // producer position (warp 0, all lanes keep it in step)
+  uint32_t p_stage = 0, p_phase = 0, p_tile = j, p_sg = 0;
+  auto produce = [&]() {  // issue the loads of stage (p_tile, p_sg) into ring slot p_stage and advance; whole warp
+    const uint32_t c0 = p_sg * kRowsCps;
+    const uint32_t nch = a.kchunks - c0 < kRowsCps ? a.kchunks - c0 : kRowsCps;
+    if (tc::elect_one_sync()) {
+      mbar_arrive_expect_tx(&full[p_stage], nch * kRowsChunkBytes);
+      for (uint32_t i = 0; i < nch; ++i)
+        tma_load_2d_hint(smem + L.stages_off + p_stage * kRowsStageBytes + i * kRowsChunkBytes, &tmap_base, &full[p_stage],
+                         (int)((c0 + i) * EPC), (int)(p_tile * kRowsTile), pol);
+    }
+    __syncwarp();
+    if (++p_stage == (uint32_t)a.stages) {
+      p_stage = 0;
+      p_phase ^= 1;
+    }
+    if (++p_sg == nsg) {
+      p_sg = 0;
+      p_tile += P;
+    }
+  };
+  // The HBM stream starts before the queries are converted: every ring slot is free, so the first `stages` loads need
+  // no wait.
   if (warp == 0) {
     if (lane == 0) tma_prefetch_desc(&tmap_base);
-    for (int s = 0; s < a.stages && p_tile < a.num_tiles; ++s) {
-      if (tc::elect_one_sync()) {
-        mbar_arrive_expect_tx(&full[p_stage], kRowsStageBytes);
-        tma_load_2d_hint(smem + L.stages_off + p_stage * kRowsStageBytes, &tmap_base, &full[p_stage], (int)(p_kc * EPC),
-                         (int)(p_tile * kRowsTile), pol);
-      }
-      __syncwarp();
-      if (++p_stage == (uint32_t)a.stages) {
-        p_stage = 0;
-        p_phase ^= 1;
-      }
-      if (++p_kc == a.kchunks) {
-        p_kc = 0;
-        p_tile += P;
-      }
-    }
+    for (int s = 0; s < a.stages && p_tile < a.num_tiles; ++s) produce();
   }
 
   // ---- query preparation: FP32 queries -> limb rows of the B operand (swizzled, K-major) + per-query scales. Same
@@ -286,20 +341,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     // ===== TMA producer (continues after the prologue's first loads) =====
     while (p_tile < a.num_tiles) {
       mbar_wait(&empty[p_stage], p_phase ^ 1);
-      if (tc::elect_one_sync()) {
-        mbar_arrive_expect_tx(&full[p_stage], kRowsStageBytes);
-        tma_load_2d_hint(smem + L.stages_off + p_stage * kRowsStageBytes, &tmap_base, &full[p_stage], (int)(p_kc * EPC),
-                         (int)(p_tile * kRowsTile), pol);
-      }
-      __syncwarp();
-      if (++p_stage == (uint32_t)a.stages) {
-        p_stage = 0;
-        p_phase ^= 1;
-      }
-      if (++p_kc == a.kchunks) {
-        p_kc = 0;
-        p_tile += P;
-      }
+      produce();
     }
   } else if (warp == 1) {
     // ===== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====
@@ -310,22 +352,27 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       mbar_wait(&tempty[buf], bphase ^ 1);
       tc::fence_after_thread_sync();
       const uint32_t acc = tmem_base + buf * kAccColsPerBuf;
-      for (uint32_t kc = 0; kc < a.kchunks; ++kc) {
+      for (uint32_t sg = 0; sg < nsg; ++sg) {
+        const uint32_t c0 = sg * kRowsCps;
+        const uint32_t nch = a.kchunks - c0 < kRowsCps ? a.kchunks - c0 : kRowsCps;
         mbar_wait(&full[stage], phase);
         tc::fence_after_thread_sync();
-        const uint64_t adesc = tc::smem_desc_k128(smem_u32(smem + L.stages_off + stage * kRowsStageBytes));
-        const uint64_t bdesc = tc::smem_desc_k128(b_u32 + kc * L.b_chunk_bytes);
+        const uint32_t st_u32 = smem_u32(smem + L.stages_off + stage * kRowsStageBytes);
         if (tc::elect_one_sync()) {
+          for (uint32_t i = 0; i < nch; ++i) {
+            const uint64_t adesc = tc::smem_desc_k128(st_u32 + i * kRowsChunkBytes);
+            const uint64_t bdesc = tc::smem_desc_k128(b_u32 + (c0 + i) * L.b_chunk_bytes);
 #pragma unroll
-          for (uint32_t k4 = 0; k4 < 4; ++k4) {  // 4 x 32 bytes of K per 128-byte chunk (UMMA_K = 16 f16 / 32 i8)
-            const uint32_t accumulate = (uint32_t)(kc > 0 || k4 > 0);
-            if constexpr (kI8)
-              tc::mma_i8_ss(acc, adesc + 2 * k4, bdesc + 2 * k4, idesc, accumulate);
-            else
-              tc::mma_f16_ss(acc, adesc + 2 * k4, bdesc + 2 * k4, idesc, accumulate);
+            for (uint32_t k4 = 0; k4 < 4; ++k4) {  // 4 x 32 bytes of K per 128-byte chunk (UMMA_K = 16 f16 / 32 i8)
+              const uint32_t accumulate = (uint32_t)(c0 + i > 0 || k4 > 0);
+              if constexpr (kI8)
+                tc::mma_i8_ss(acc, adesc + 2 * k4, bdesc + 2 * k4, idesc, accumulate);
+              else
+                tc::mma_f16_ss(acc, adesc + 2 * k4, bdesc + 2 * k4, idesc, accumulate);
+            }
           }
           tc::mma_commit(&empty[stage]);
-          if (kc + 1 == a.kchunks) tc::mma_commit(&tfull[buf]);
+          if (sg + 1 == nsg) tc::mma_commit(&tfull[buf]);
         }
         __syncwarp();
         if (++stage == (uint32_t)a.stages) {
@@ -335,13 +382,15 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       }
     }
   } else {
-    // ===== epilogue: one thread per base row (== TMEM lane) =====
+    // ===== epilogue: one thread per base row (== TMEM lane); the two warps of a lane quadrant split the query groups =====
+    const uint32_t ew = warp - 2;                // 0..7
     const uint32_t qd = warp & 3;                // the TMEM lane quadrant this warp may read
+    const uint32_t hf = ew >> 2;                 // groups hf, hf + 2, ... of 16 queries are this warp's
     const uint32_t rl = qd * 32 + lane;          // row within the tile
-    const uint32_t ew = warp - 2;                // 0..3: compaction duty for queries ew, ew + 4, ...
     const uint32_t lane_addr = tmem_base + ((qd * 32u) << 16);
     const uint32_t ngroups = a.bp >> 4;          // groups of 16 queries
     const uint32_t half_cap = a.cap >> 1;
+    uint32_t rp = 0;                             // parity of the compaction work list appends go to
 
     // score of (this row, query q) from the raw accumulators, in scan_mma.cu's fixed FP32 order
     auto score_of = [&](const float4& p, uint32_t v, uint32_t w, float rs) -> float {
@@ -351,6 +400,14 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       } else {
         return __fmul_rn(__uint_as_float(v), p.x);      // power-of-two rescale: exact
       }
+    };
+    auto compact = [&](uint32_t q) {  // whole warp
+      const uint32_t c0 = lds_u32(cnt_u32 + q * 4u);
+      const uint32_t c = c0 < a.cap ? c0 : a.cap;
+      if (a.cap == 64u)
+        warp_compact64(keys_u32 + q * 512u, c, a.kp, cnt_u32 + q * 4u, par_u32 + q * 16u + 8u, lane);
+      else
+        warp_compact(keys_u32 + q * a.cap * 8u, a.cap, c, a.kp, cnt_u32 + q * 4u, par_u32 + q * 16u + 8u, lane);
     };
 
     uint32_t it = 0;
@@ -364,46 +421,78 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       tc::fence_after_thread_sync();
       const uint32_t acc = lane_addr + buf * kAccColsPerBuf;
       uint64_t pend_lo = 0ull, pend_hi = 0ull;  // queries whose append found the list full (bit q)
-      bool pushed = false;
+      bool enq = false;                         // this thread queued a list for compaction in this round
 
-      // ---- offers
+      // An append takes a slot of the query's list; the one that makes the list half full queues it for compaction;
+      // one that finds the list full stays pending.
+      auto append = [&](uint32_t q, float s) {
+        const uint32_t slot = atom_add_shared(cnt_u32 + q * 4u, 1u);
+        if (slot < a.cap) {
+          sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
+          if (slot + 1u == half_cap) {
+            const uint32_t e = atom_add_shared(wl_u32 + rp * 16u, 1u);
+            sts_u32(wl_u32 + 32u + (rp * a.bp + e) * 4u, q);
+            enq = true;
+          }
+        } else if (q < 64u) {
+          pend_lo |= 1ull << q;
+        } else {
+          pend_hi |= 1ull << (q - 64u);
+        }
+      };
+
+      // ---- offers. Fast path, branch free: thresholds / scales of 8 queries at a time come from shared memory with
+      // back-to-back broadcast loads, the compares build a bit mask; the append path runs only for set bits (rare
+      // after the first tiles: P(admit) ~ k' / rows seen).
 #pragma unroll 1
-      for (uint32_t g = 0; g < ngroups; ++g) {
+      for (uint32_t g = hf; g < ngroups; g += 2) {
         uint32_t v[16], w[16];
         tmem_ld16(acc + g * 16u, v);
         if constexpr (kI8) tmem_ld16(acc + a.bp + g * 16u, w);
-        tc::tmem_ld_wait();
+        float s[16];
+        uint32_t mask = 0;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const uint32_t q = g * 16u + (uint32_t)i;
-          const float4 p = lds_f4(par_u32 + q * 16u);
-          const float s = score_of(p, v[i], kI8 ? w[i] : 0u, rs);
-          if (s >= p.z && row_ok) {
-            const uint32_t slot = atom_add_shared(cnt_u32 + q * 4u, 1u);
-            if (slot < a.cap) {
-              sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
-              pushed = true;
-            } else if (q < 64u) {
-              pend_lo |= 1ull << q;
-            } else {
-              pend_hi |= 1ull << (q - 64u);
-            }
+        for (int h = 0; h < 2; ++h) {
+          float4 p[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) p[i] = lds_f4(par_u32 + (g * 16u + (uint32_t)(h * 8 + i)) * 16u);
+          if (h == 0) tc::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            s[h * 8 + i] = score_of(p[i], v[h * 8 + i], kI8 ? w[h * 8 + i] : 0u, rs);
+            mask |= (s[h * 8 + i] >= p[i].z) ? (1u << (h * 8 + i)) : 0u;
           }
+        }
+        if (!row_ok) mask = 0u;
+        if (mask) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (mask & (1u << i)) append(g * 16u + (uint32_t)i, s[i]);
         }
       }
 
-      // ---- list maintenance; appends that found their list full are retried from TMEM after the compaction
+      // ---- list maintenance, only when a list became half full or an append is pending: the queued lists are compacted
+      // (any warp takes the next one), pending appends are retried from TMEM against the raised thresholds.
       for (;;) {
-        if (epi_bar_count(pushed || (pend_lo | pend_hi) != 0ull) == 0u) break;  // nothing touched a list in this round
-        for (uint32_t q = ew; q < a.nq; q += 4) {
-          const uint32_t c = lds_u32(cnt_u32 + q * 4u);
-          if (c >= half_cap)
-            warp_compact(keys_u32 + q * a.cap * 8u, a.cap, c < a.cap ? c : a.cap, a.kp, cnt_u32 + q * 4u, par_u32 + q * 16u + 8u, lane);
+        if (epi_bar_count(enq || (pend_lo | pend_hi) != 0ull) == 0u) break;
+        if (tid == 64u) {  // the other work list: last read before the previous round's second barrier
+          sts_u32(wl_u32 + (rp ^ 1u) * 16u, 0u);
+          sts_u32(wl_u32 + (rp ^ 1u) * 16u + 4u, 0u);
         }
-        if (epi_bar_count((pend_lo | pend_hi) != 0ull) == 0u) break;            // compactions visible; nobody is waiting
-        pushed = false;
+        const uint32_t nwork = lds_u32(wl_u32 + rp * 16u);
+        for (;;) {
+          uint32_t idx = 0;
+          if (lane == 0) idx = atom_add_shared(wl_u32 + rp * 16u + 4u, 1u);
+          idx = __shfl_sync(0xffffffffu, idx, 0);
+          if (idx >= nwork) break;
+          compact(lds_u32(wl_u32 + 32u + (rp * a.bp + idx) * 4u));
+        }
+        const uint32_t npend = epi_bar_count((pend_lo | pend_hi) != 0ull);  // compactions visible
+        rp ^= 1u;
+        enq = false;
+        if (npend == 0u) break;
 #pragma unroll 1
-        for (uint32_t g = 0; g < ngroups; ++g) {
+        for (uint32_t g = hf; g < ngroups; g += 2) {
           const uint32_t bits = (uint32_t)(((g < 4u) ? (pend_lo >> (g * 16u)) : (pend_hi >> ((g - 4u) * 16u))) & 0xFFFFull);
           if (!__any_sync(0xffffffffu, bits != 0u)) continue;  // tcgen05.ld is warp-collective: a warp-uniform decision
           uint32_t v[16], w[16];
@@ -414,22 +503,11 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
           for (int i = 0; i < 16; ++i) {
             if (bits & (1u << i)) {
               const uint32_t q = g * 16u + (uint32_t)i;
+              if (q < 64u) pend_lo &= ~(1ull << q);
+              else pend_hi &= ~(1ull << (q - 64u));
               const float4 p = lds_f4(par_u32 + q * 16u);
               const float s = score_of(p, v[i], kI8 ? w[i] : 0u, rs);
-              bool done = true;
-              if (s >= p.z) {
-                const uint32_t slot = atom_add_shared(cnt_u32 + q * 4u, 1u);
-                if (slot < a.cap) {
-                  sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
-                  pushed = true;
-                } else {
-                  done = false;
-                }
-              }
-              if (done) {
-                if (q < 64u) pend_lo &= ~(1ull << q);
-                else pend_hi &= ~(1ull << (q - 64u));
-              }
+              if (s >= p.z) append(q, s);  // sets the pending bit again when the list is still full
             }
           }
         }
@@ -440,10 +518,9 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     }
 
     // ---- this CTA's best k' per query -> partial[q][cta][k'] (sorted descending, 0 = empty)
-    named_bar_sync(1, 128);
-    for (uint32_t q = ew; q < a.nq; q += 4) {
-      const uint32_t c = lds_u32(cnt_u32 + q * 4u);
-      warp_compact(keys_u32 + q * a.cap * 8u, a.cap, c < a.cap ? c : a.cap, a.kp, cnt_u32 + q * 4u, par_u32 + q * 16u + 8u, lane);
+    named_bar_sync(1, kRowsEpiThreads);
+    for (uint32_t q = ew; q < a.nq; q += kRowsEpiWarps) {
+      compact(q);
       const uint32_t nc = lds_u32(cnt_u32 + q * 4u);
       uint64_t* out = a.partial + ((size_t)q * a.lists + j) * a.kp;
       for (uint32_t jj = lane; jj < a.kp; jj += 32) out[jj] = jj < nc ? lds_u64(keys_u32 + (q * a.cap + jj) * 8u) : 0ull;
@@ -457,7 +534,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
 
 }  // namespace
 
-// Shapes this kernel takes: nq queries whose limb rows (+ candidate lists) fit next to a >= 4-deep ring.
+// Shapes this kernel takes: nq queries whose limb rows (+ candidate lists) fit next to a >= 3-deep ring of 32 KB stages.
 bool scan_rows_plan(int dtype, uint32_t nq, uint32_t kp, uint32_t dim, int max_smem, RowsPlan* out) {
   if (dtype != kDtF16 && dtype != kDtI8) return false;
   if (nq == 0 || nq > 128u) return false;
@@ -469,7 +546,7 @@ bool scan_rows_plan(int dtype, uint32_t nq, uint32_t kp, uint32_t dim, int max_s
   while (cap < 4u * kp) cap <<= 1;  // a list is compacted when half full: at least k' free slots afterwards
   if (cap > 4096u) return false;
   const uint32_t kchunks = (dim * es + 127u) / 128u;
-  for (int st = (int)kRowsMaxStages; st >= 4; --st) {
+  for (int st = (int)kRowsMaxStages; st >= 3; --st) {
     if (rows_layout(nb, bp, cap, kchunks, st).total <= (uint32_t)max_smem) {
       out->bp = bp;
       out->nb = nb;
