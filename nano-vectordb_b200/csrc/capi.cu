@@ -55,13 +55,17 @@ struct nvdb_b200_index {
   const void* tmap_a_ptr = nullptr;
   uint32_t tmap_a_rows = 0;
   // grow-only workspaces
-  void* d_ws[20] = {};
-  size_t d_ws_bytes[20] = {};
+  void* d_ws[24] = {};
+  size_t d_ws_bytes[24] = {};
   void* h_pin[3] = {nullptr, nullptr, nullptr};
   size_t h_pin_bytes[3] = {0, 0, 0};
   // exact tensor-core path (rescore.cu): row-norm maxima of the base (lazy) and certificate statistics
   bool norms_ready = false;
   float max_l2 = 0.f, max_l1 = 0.f;
+  uint32_t rows_launches = 0;          // launches of the row-tile kernel that used the seeding workspace (its counter's epoch)
+  const void* rows_seed_seen = nullptr;  // WS_ROWS_SEED allocation whose counter has been zeroed
+  uint64_t exact_calls = 0;            // candidate-scan + re-score chains enqueued: parity picks the flag counter slot
+  const void* flag_ws_seen = nullptr;  // WS_X_FLAGS allocation whose counter slots have been zeroed
   uint64_t exact_queries = 0, exact_fallbacks = 0;
   uint64_t exact_tier2 = 0, exact_gemv = 0;  // flagged queries re-run with wider lists / on the streaming scan
   // tuning knobs (nvdb_b200_index_set_tuning; defaults may be overridden by environment variables at creation)
@@ -70,7 +74,10 @@ struct nvdb_b200_index {
   int tune_fused_merge = 1;  // final merge inside the streaming scan's last CTA (0: separate merge kernel)
   int tune_gemv_ctas = 1;  // CTAs per SM of the single-query streaming scan (1 | 2)
   int tune_mma_2cta = 1;   // CTA-pair (cta_group::2) tensor-core scan: 0 never, 1 (default) / 2 whenever the shape allows
-  int tune_rows = 1;       // small batches of the exact path on the row-tile tensor kernel (scan_rows.cu): 0 never, 1 when the batch fits
+  int tune_rows = 1;       // small batches of the exact path on the row-tile tensor kernel (scan_rows.cu): 0 never, 1 auto
+                           // (int8 bases: measured faster than the query-tile kernels for every batch that fits, f16: never),
+                           // 2 whenever the batch fits
+  int tune_rows_seed = 1;  // its cross-CTA threshold seeding: 0 off, 1 auto (>= 40 queries, where it pays), 2 always
   int tune_exact_tier2 = 1; // exact path: flagged queries get a second tensor-core pass with wider candidate lists (0: off;
                             // > 1: that many list entries instead of the default width, for A/B measurements)
   std::mutex mu;
@@ -86,7 +93,7 @@ namespace {
 thread_local std::string t_err;
 enum { WS_QUERIES = 0, WS_PARTIAL = 1, WS_OUT_IDS = 2, WS_OUT_SCORES = 3, WS_CAND = 4, WS_OUT_IDS32 = 5, WS_MMA_A = 6,
        WS_MMA_QS = 7, WS_DBG = 8, WS_X_IDS = 9, WS_X_APX = 10, WS_X_FLAGS = 11, WS_X_Q = 12, WS_X_OUT_IDS = 13,
-       WS_X_OUT_SC = 14, WS_SEED = 15, WS_GEMV_CTR = 16, WS_X_LIST = 17, WS_X_Q2 = 18, WS_X_OUT2 = 19 };
+       WS_X_OUT_SC = 14, WS_SEED = 15, WS_GEMV_CTR = 16, WS_X_LIST = 17, WS_X_Q2 = 18, WS_X_OUT2 = 19, WS_ROWS_SEED = 20 };
 
 int fail(const nvdb_b200_index* idx, int code, const std::string& msg) {
   t_err = msg;
@@ -264,6 +271,7 @@ int new_handle(uint32_t dtype, uint64_t n, uint32_t dim, int device, uint64_t ro
   if (const char* ev = getenv("NVDB_B200_FUSED_MERGE")) h->tune_fused_merge = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_EXACT_TIER2")) h->tune_exact_tier2 = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_ROWS")) h->tune_rows = atoi(ev);
+  if (const char* ev = getenv("NVDB_B200_ROWS_SEED")) h->tune_rows_seed = atoi(ev);
   if (const char* ev = getenv("NVDB_B200_XCHG_NO_ALLOC")) h->guard_no_alloc = atoi(ev) != 0;
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_switch, cudaEventDisableTiming);
@@ -920,12 +928,19 @@ int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
 // operand) — one HBM pass, tensor work proportional to the batch. false = the batch / k' does not fit, use scan_mma*.
 bool rows_kernel_fits(const nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t kp, RowsPlan* plan) {
   if (!idx->mma_ok || !idx->tune_rows) return false;
+  // measured (profiles/r2_probe_rows_ab.jsonl, interleaved on one box): int8 0.37-0.42 ms against 0.49-0.57 ms of the
+  // query-tile kernels for 1..32 queries (0.51-0.57 against 0.58-0.59 at 48..64); f16 is the other way round (0.69-0.73
+  // against 0.70-0.80: its one-limb query tile is cheap to re-stream and 256-row tiles need half the MMA issues)
+  if (idx->tune_rows == 1 && idx->dtype != kDtI8) return false;
   if ((reinterpret_cast<uintptr_t>(d_queries) & 15u) || (idx->dim % 4u)) return false;  // float4 reads of the queries
   return scan_rows_plan((int)idx->dtype, nq, kp, idx->dim, idx->max_smem, plan);
 }
 
+// cand_ids == null: no merge launch — the caller's re-score kernel selects the candidates from the per-CTA lists itself
+// (*out_partial / *out_lists describe them).
 int rows_candidate_scan(nvdb_b200_index* idx, const RowsPlan& plan, const float* d_queries, uint32_t nq, uint32_t kp,
-                        uint64_t* cand_ids, float* cand_apx, cudaStream_t stream, uint32_t* launches) {
+                        uint64_t* cand_ids, float* cand_apx, cudaStream_t stream, uint32_t* launches,
+                        const uint64_t** out_partial = nullptr, uint32_t* out_lists = nullptr) {
   const uint32_t tiles = (uint32_t)((idx->n + 127u) / 128u);
   const int grid = (int)(tiles < (uint32_t)idx->num_sms ? tiles : (uint32_t)idx->num_sms);
   int rc;
@@ -937,6 +952,20 @@ int rows_candidate_scan(nvdb_b200_index* idx, const RowsPlan& plan, const float*
   a.scales = idx->scales;
   a.thr_init = nullptr;
   a.partial = (uint64_t*)idx->d_ws[WS_PARTIAL];
+  // cross-CTA threshold seeding workspace: arrival counter (epoch = launch number, so no memset per launch) + one word
+  // per (CTA, query)
+  // (pays from ~40 queries on: below that its publish / poll / select steps cost more than the appends they save)
+  const bool seed = idx->tune_rows_seed == 2 || (idx->tune_rows_seed == 1 && nq >= 40u);
+  if (seed && (uint32_t)grid >= kp && grid <= 256) {  // the kernel's own condition: every CTA publishes or none
+    if ((rc = ensure_ws(idx, WS_ROWS_SEED, 64u + (size_t)idx->num_sms * 2u * 128u * 4u))) return rc;
+    if (idx->rows_seed_seen != idx->d_ws[WS_ROWS_SEED]) {
+      CK(cudaMemsetAsync(idx->d_ws[WS_ROWS_SEED], 0, 64, stream), "memset seeding counter");
+      idx->rows_seed_seen = idx->d_ws[WS_ROWS_SEED];
+      idx->rows_launches = 0;
+    }
+    a.seed_ws = (uint32_t*)idx->d_ws[WS_ROWS_SEED];
+    a.seed_target = ++idx->rows_launches * (uint32_t)grid;
+  }
   a.n_rows = (uint32_t)idx->n;
   a.dim = idx->dim;
   a.kp = kp;
@@ -950,9 +979,14 @@ int rows_candidate_scan(nvdb_b200_index* idx, const RowsPlan& plan, const float*
   a.stages = plan.stages;
   CK(scan_rows_launch((int)idx->dtype, &idx->tmap_mma_b, a, grid, stream), "scan_rows launch");
   if (pev) CK(cudaEventRecord(pev[1], stream), "profile event record");
-  CK(merge_partials_launch(a.partial, a.lists, nq, kp, 0, cand_ids, cand_apx, stream), "merge_partials launch");
+  if (launches) ++*launches;
+  if (cand_ids) {
+    CK(merge_partials_launch(a.partial, a.lists, nq, kp, 0, cand_ids, cand_apx, stream), "merge_partials launch");
+    if (launches) ++*launches;
+  }
   if (pev) CK(cudaEventRecord(pev[2], stream), "profile event record");
-  if (launches) *launches += 2;
+  if (out_partial) *out_partial = a.partial;
+  if (out_lists) *out_lists = a.lists;
   return NVDB_B200_OK;
 }
 
@@ -966,18 +1000,38 @@ int mma_exact_enqueue(nvdb_b200_index* idx, const float* d_queries, uint32_t nq,
   if ((rc = ensure_ws(idx, WS_X_FLAGS, ((size_t)nq + 4) * 4))) return rc;
   uint64_t* cand_ids = (uint64_t*)idx->d_ws[WS_X_IDS];
   float* cand_apx = (float*)idx->d_ws[WS_X_APX];
-  uint32_t* nflag = (uint32_t*)idx->d_ws[WS_X_FLAGS];
-  uint32_t* flags = nflag + 4;
-  CK(cudaMemsetAsync(nflag, 0, 4, stream), "memset flag count");
+  // flag counter: two slots used alternately; the re-score kernel of call i zeroes the slot of call i + 1 (stream order),
+  // so no memset is launched per search. Slots are zeroed here whenever the workspace is new.
+  uint32_t* ws_flags = (uint32_t*)idx->d_ws[WS_X_FLAGS];
+  if (idx->flag_ws_seen != ws_flags) {
+    CK(cudaMemsetAsync(ws_flags, 0, 16, stream), "memset flag counters");
+    idx->flag_ws_seen = ws_flags;
+    idx->exact_calls = 0;
+  }
+  const uint32_t slot = (uint32_t)(idx->exact_calls++ & 1u);
+  uint32_t* nflag = ws_flags + slot;
+  uint32_t* flags = ws_flags + 4;
   const int limbs = idx->dtype == kDtF16 ? 1 : 2;
   RowsPlan rplan;
+  const uint64_t* fused_partial = nullptr;
+  uint32_t fused_lists = 0;
   if (rows_kernel_fits(idx, d_queries, nq, kp, &rplan)) {
-    if ((rc = rows_candidate_scan(idx, rplan, d_queries, nq, kp, cand_ids, cand_apx, stream, launches))) return rc;
+    // few enough keys per query (<= 4096): the re-score kernel selects the candidates from the per-CTA lists itself
+    const uint32_t tiles = (uint32_t)((idx->n + 127u) / 128u);
+    const uint32_t lists = tiles < (uint32_t)idx->num_sms ? tiles : (uint32_t)idx->num_sms;
+    const bool fuse = (size_t)lists * kp <= 4096u;
+    if ((rc = rows_candidate_scan(idx, rplan, d_queries, nq, kp, fuse ? nullptr : cand_ids, cand_apx, stream, launches,
+                                  &fused_partial, &fused_lists)))
+      return rc;
+    if (!fuse) fused_partial = nullptr;
   } else if ((rc = mma_search_impl(idx, d_queries, nq, kp, cand_ids, cand_apx, stream, launches, limbs, nullptr, 0))) {
     return rc;
   }
 
   RescoreArgs r{};
+  r.partial = fused_partial;
+  r.nlists = fused_lists;
+  r.nflag_next = ws_flags + (slot ^ 1u);
   r.base = idx->payload;
   r.scales = idx->scales;
   r.queries = d_queries;
@@ -1060,6 +1114,7 @@ int reserve_exact_ws(nvdb_b200_index* idx, uint32_t nq, uint32_t k, cudaStream_t
   const size_t mpad = (((size_t)(nq < 128u * sms ? nq : 128u * sms) + 127u) / 128u + 1u) * 128u;  // + 1: CTA-pair padding tile
   if ((rc = ensure_ws(idx, WS_MMA_A, (size_t)limbs * mpad * idx->dim * es))) return rc;
   if ((rc = ensure_ws(idx, WS_MMA_QS, 3 * mpad * 4))) return rc;
+  if ((rc = ensure_ws(idx, WS_ROWS_SEED, 64u + (size_t)idx->num_sms * 2u * 128u * 4u))) return rc;
   return ensure_gemv_ctr(idx, stream);
 }
 
@@ -1166,13 +1221,18 @@ int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
 // and is FMA-bound from 4; the tensor-core scan reads the base once per 128 * num_sms queries). Both are bit-identical
 // to the reference, so AUTO never changes results.
 constexpr uint32_t kMmaCrossover = 3;
+// From how many queries AUTO leaves the streaming scan: int8 with the row-tile kernel already at 2 (0.38 ms against the
+// streaming scan's 0.50 ms for two queries: 41 instructions per 16 bytes and query make it issue-bound), else 3.
+static uint32_t auto_crossover(const nvdb_b200_index* idx) {
+  return (idx->dtype == kDtI8 && idx->tune_rows) ? 2u : kMmaCrossover;
+}
 
 int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
                        float* d_out_scores, cudaStream_t stream, uint32_t* launches, uint32_t* path_used,
                        bool* deferred = nullptr) {
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
-    path = (nq >= kMmaCrossover && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
+    path = (nq >= auto_crossover(idx) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
   if (path_used) *path_used = (uint32_t)path;
   if (path == NVDB_B200_PATH_GEMV) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
   if (path == NVDB_B200_PATH_MMA_EXACT)
@@ -1208,7 +1268,7 @@ static int search_exchange_impl(nvdb_b200_index* idx, nvdb_b200_exchange* x, con
   if (idx->device != x->device) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: index and exchange live on different devices");
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
-    path = (nq >= kMmaCrossover && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
+    path = (nq >= auto_crossover(idx) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
   uint64_t* l_ids = reinterpret_cast<uint64_t*>(x->staging);
   float* l_scores = reinterpret_cast<float*>(l_ids + nk);
   int rc;
@@ -1409,6 +1469,7 @@ int nvdb_b200_index_set_tuning(nvdb_b200_index* idx, int knob, int value) {
     case NVDB_B200_TUNE_MMA_RESIDENT: idx->tune_mma_resident = value; break;
     case NVDB_B200_TUNE_EXACT_TIER2: idx->tune_exact_tier2 = value; break;
     case NVDB_B200_TUNE_ROWS: idx->tune_rows = value; break;
+    case NVDB_B200_TUNE_ROWS_SEED: idx->tune_rows_seed = value; break;
     default: return fail(idx, NVDB_B200_ERR_ARG, "unknown tuning knob");
   }
   return NVDB_B200_OK;
@@ -1488,8 +1549,8 @@ int nvdb_b200_search_two_stage(nvdb_b200_index* coarse, nvdb_b200_index* fine, c
   r.cand_approx = capx;
   r.out_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
   r.out_scores = (float*)idx->d_ws[WS_OUT_SCORES];
-  r.nflag = (uint32_t*)idx->d_ws[WS_X_FLAGS];
-  r.flags = r.nflag + 4;
+  r.nflag = (uint32_t*)idx->d_ws[WS_X_FLAGS] + 2;  // scratch word (slots 0 / 1 belong to the exact path's certificate)
+  r.flags = (uint32_t*)idx->d_ws[WS_X_FLAGS] + 4;
   r.row_offset = fine->row_offset;
   r.cand_offset = coarse->row_offset;
   r.n_rows = (uint32_t)fine->n;

@@ -109,23 +109,148 @@ rescore_exact_kernel(const RescoreArgs a) {
   const uint32_t bufn = next_pow2(a.kp);
   const uint32_t sq_u32 = smem_u32(sq);
   const uint32_t row_bytes = a.dim * (uint32_t)Elem<DT>::size;
-  const uint64_t* cid = a.cand_ids + (size_t)q * a.kp;
-  const float* capx = a.cand_approx + (size_t)q * a.kp;
-  float amin = INFINITY;  // smallest approximate score among the valid candidates
-  for (uint32_t c = tid; c < bufn; c += kRescoreThreads) {
-    uint64_t key = 0ull;
-    if (c < a.kp) {
-      const uint64_t raw = cid[c];
-      const uint64_t row64 = raw - a.cand_offset;
-      if (raw != ~0ull && raw >= a.cand_offset && row64 < (uint64_t)a.n_rows) {
-        const uint32_t row = (uint32_t)row64;
-        float s = exact_dot_row<DT>(reinterpret_cast<const uint8_t*>(a.base) + (size_t)row * row_bytes, row_bytes, sq_u32);
-        if constexpr (DT == kDtI8) s = __fmul_rn(s, __ldg(a.scales + row));  // src/simd_dot.cpp:198
-        key = make_key(s, row);
-        amin = fminf(amin, capx[c]);
+  const uint64_t* cid = a.cand_ids ? a.cand_ids + (size_t)q * a.kp : nullptr;
+  const float* capx = a.cand_approx ? a.cand_approx + (size_t)q * a.kp : nullptr;
+  // Fused merge (a.partial): the candidates are the kp best keys of this query's per-CTA lists [nlists][kp] (each sorted
+  // descending, 0 = empty) — selected here instead of by a separate merge launch. Every list's last entry is a lower
+  // bound of the final kp-th best key, so only keys >= the largest of them can matter: those few survivors are sorted.
+  uint64_t* sel = nullptr;
+  if (a.partial) {
+    __shared__ unsigned long long s_floor;
+    __shared__ uint32_t s_nsel;
+    sel = reinterpret_cast<uint64_t*>(rs_smem + a.sel_off);
+    const uint64_t* part = a.partial + (size_t)q * a.nlists * a.kp;
+    const uint32_t total = a.nlists * a.kp;
+    if (tid == 0) {
+      s_floor = 0ull;
+      s_nsel = 0u;
+    }
+    __syncthreads();
+    // two lower bounds of the final kp-th best key: the largest of the lists' LAST entries (that list alone holds kp keys
+    // at least as good), and — much tighter when there are many lists — the kp-th largest of the lists' FIRST entries
+    // (kp distinct keys at least as good); with 148 lists of 16 the first leaves ~1200 survivors, the second ~2 kp.
+    uint64_t fl = 0ull;
+    for (uint32_t l = tid; l < a.nlists; l += kRescoreThreads) {
+      const uint64_t v = part[(size_t)l * a.kp + (a.kp - 1u)];
+      fl = v > fl ? v : fl;
+      sel[l] = part[(size_t)l * a.kp];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const uint64_t o = __shfl_xor_sync(0xffffffffu, fl, off);
+      fl = o > fl ? o : fl;
+    }
+    if ((tid & 31u) == 0u && fl) atomicMax(&s_floor, (unsigned long long)fl);
+    __syncthreads();
+    if (a.nlists >= a.kp) {
+      for (uint32_t l = tid; l < a.nlists; l += kRescoreThreads) {
+        const uint64_t h = sel[l];
+        if (h == 0ull) continue;
+        uint32_t rank = 0;
+        for (uint32_t m = 0; m < a.nlists; ++m) rank += sel[m] > h ? 1u : 0u;
+        if (rank == a.kp - 1u) atomicMax(&s_floor, (unsigned long long)h);   // keys are unique: at most one thread
       }
     }
+    __syncthreads();
+    const uint64_t floor_key = s_floor;
+    for (uint32_t i = tid; i < total; i += kRescoreThreads) {
+      const uint64_t v = part[i];
+      if (v != 0ull && v >= floor_key) sel[atomicAdd(&s_nsel, 1u)] = v;   // <= total entries: the buffer holds them all
+    }
+    __syncthreads();
+    const uint32_t nsel = s_nsel, seln = next_pow2(nsel < 2u ? 2u : nsel);
+    for (uint32_t i = nsel + tid; i < seln; i += kRescoreThreads) sel[i] = 0ull;
+    __syncthreads();
+    auto ssync = [] { __syncthreads(); };
+    bitonic_sort_desc(sel, seln, tid, kRescoreThreads, ssync);
+    for (uint32_t i = seln + tid; i < bufn; i += kRescoreThreads) sel[i] = 0ull;   // sel[c] is read for c < bufn
+    __syncthreads();
+  }
+  // candidate c of this query: local row (0xFFFFFFFF = none) and approximate score
+  auto candidate = [&](uint32_t c, float* apx) -> uint32_t {
+    if (c >= a.kp) return 0xFFFFFFFFu;
+    if (sel) {
+      const uint64_t key = sel[c];
+      if (key == 0ull) return 0xFFFFFFFFu;
+      *apx = key_score(key);
+      return key_row(key);
+    }
+    const uint64_t raw = cid[c];
+    const uint64_t row64 = raw - a.cand_offset;
+    if (raw == ~0ull || raw < a.cand_offset || row64 >= (uint64_t)a.n_rows) return 0xFFFFFFFFu;
+    *apx = capx[c];
+    return (uint32_t)row64;
+  };
+  float amin = INFINITY;  // smallest approximate score among the valid candidates
+  if (a.stage_rows) {
+    // Candidate rows are scattered over the base: a thread walking one row alone pays a DRAM round trip per 128-byte
+    // line, twelve in a row for 1536 bytes. Instead the CTA first stages 16 candidate rows in shared memory with every
+    // thread's loads in flight at once, then 8 lanes share a candidate, lane j running chain j of the reference (elements
+    // j, j + 8, ... ascending: src/simd_dot.cpp:26-49,102-124,160-199) and the fixed horizontal sum runs over shuffles.
+    uint8_t* rows = rs_smem + ((a.dim * 4u + 15u) & ~15u) + ((bufn * 8u + 15u) & ~15u);  // [16][row_bytes + 16]
+    __shared__ uint32_t s_row[16];
+    __shared__ float s_apx[16];
+    const uint32_t rstride = row_bytes + 16u, ppr = row_bytes >> 4;
+    const uint32_t grp = tid >> 3, jl = tid & 7u;
+    for (uint32_t c0 = 0; c0 < bufn; c0 += 16u) {
+      if (tid < 16u) {
+        float apx = 0.f;
+        s_row[tid] = candidate(c0 + tid, &apx);
+        s_apx[tid] = apx;
+      }
+      __syncthreads();
+      for (uint32_t pc = tid; pc < 16u * ppr; pc += kRescoreThreads) {
+        const uint32_t c = pc / ppr, p16 = pc - c * ppr;
+        const uint32_t row = s_row[c];
+        if (row != 0xFFFFFFFFu) {
+          const uint4 v = ldg128_stream(reinterpret_cast<const uint8_t*>(a.base) + (size_t)row * row_bytes + (size_t)p16 * 16u);
+          *reinterpret_cast<uint4*>(rows + c * rstride + p16 * 16u) = v;
+        }
+      }
+      __syncthreads();
+      {
+        const uint32_t row = s_row[grp];
+        float acc = 0.f;
+        if (row != 0xFFFFFFFFu) {
+          const uint8_t* rp = rows + grp * rstride;
+          for (uint32_t i = jl; i < a.dim; i += 8u) {
+            float x;
+            if constexpr (DT == kDtF16) x = __half2float(reinterpret_cast<const __half*>(rp)[i]);
+            else if constexpr (DT == kDtI8) x = (float)reinterpret_cast<const int8_t*>(rp)[i];
+            else x = reinterpret_cast<const float*>(rp)[i];
+            acc = __fmaf_rn(sq[i], x, acc);
+          }
+        }
+        // ((a0+a4)+(a1+a5))+((a2+a6)+(a3+a7)): lanes j and j^4, then j^1, then j^2 (FP32 addition commutes exactly)
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 4));
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 1));
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 2));
+        if (jl == 0) {
+          uint64_t key = 0ull;
+          if (row != 0xFFFFFFFFu) {
+            float sc = acc;
+            if constexpr (DT == kDtI8) sc = __fmul_rn(sc, __ldg(a.scales + row));  // src/simd_dot.cpp:198
+            key = make_key(sc, row);
+            amin = fminf(amin, s_apx[grp]);
+          }
+          if (c0 + grp < bufn) keys[c0 + grp] = key;
+        }
+      }
+      __syncthreads();
+    }
+  } else {
+  for (uint32_t c = tid; c < bufn; c += kRescoreThreads) {
+    uint64_t key = 0ull;
+    float apx = 0.f;
+    const uint32_t row = candidate(c, &apx);
+    if (row != 0xFFFFFFFFu) {
+      float s = exact_dot_row<DT>(reinterpret_cast<const uint8_t*>(a.base) + (size_t)row * row_bytes, row_bytes, sq_u32);
+      if constexpr (DT == kDtI8) s = __fmul_rn(s, __ldg(a.scales + row));  // src/simd_dot.cpp:198
+      key = make_key(s, row);
+      amin = fminf(amin, apx);
+    }
     keys[c] = key;
+  }
   }
   __syncthreads();
   auto sync = [] { __syncthreads(); };
@@ -168,6 +293,7 @@ rescore_exact_kernel(const RescoreArgs a) {
     }
     a.flags[q] = pass ? 0u : 1u;
     if (!pass) atomicAdd(a.nflag, 1u);
+    if (q == 0 && a.nflag_next) *a.nflag_next = 0u;  // the counter of the NEXT call on this stream (no memset launch)
   }
 }
 
@@ -262,14 +388,27 @@ cudaError_t scatter_topk_launch(const uint64_t* src_ids, const float* src_scores
 
 cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, cudaStream_t stream) {
   if (nq == 0 || a.k == 0) return cudaSuccess;
-  const size_t smem = ((a.dim * 4u + 15u) & ~15u) + (size_t)next_pow2(a.kp) * 8u;
+  size_t smem = ((a.dim * 4u + 15u) & ~15u) + (((size_t)next_pow2(a.kp) * 8u + 15u) & ~(size_t)15u);
   if (smem > 200u * 1024u) return cudaErrorInvalidValue;
+  // staged form: whole 8-chains only (the shapes the tensor-core scans take), 16 rows of the base next to the query
+  RescoreArgs b = a;
+  const uint32_t es = dtype == kDtF32 ? 4u : dtype == kDtF16 ? 2u : 1u;
+  const size_t stage = 16u * ((size_t)a.dim * es + 16u);
+  b.stage_rows = (a.dim % 8u == 0u) && ((a.dim * es) % 16u == 0u) && (smem + stage <= 160u * 1024u) ? 1 : 0;
+  if (b.stage_rows) smem += stage;
+  if (a.partial) {  // selection buffer of the fused merge: every key of the lists in the worst case
+    const size_t seln = next_pow2(a.nlists * a.kp < 2u ? 2u : a.nlists * a.kp);
+    const size_t need = seln > next_pow2(a.kp) ? seln : next_pow2(a.kp);
+    b.sel_off = (uint32_t)smem;
+    smem += need * 8u;
+    if (smem > 200u * 1024u) return cudaErrorInvalidValue;
+  }
   auto launch = [&](auto kern) -> cudaError_t {
     if (smem > 48u * 1024u) {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
     }
-    kern<<<nq, kRescoreThreads, smem, stream>>>(a);
+    kern<<<nq, kRescoreThreads, smem, stream>>>(b);
     count_launch();
     return cudaGetLastError();
   };

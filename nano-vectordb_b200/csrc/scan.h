@@ -116,6 +116,9 @@ struct RowsArgs {
   const float* scales;    // [n_rows] row scales (i8) or null
   const float* thr_init;  // [nq] admission threshold seeds or null
   uint64_t* partial;      // [nq][lists][kp] ordered keys (0 = empty); CTA j writes list j
+  uint32_t* seed_ws;      // cross-CTA threshold seeding: [0] arrival counter, [16 + cta * bp + q] best ordered score of
+                          // CTA cta for query q after its first tile; null = off
+  uint32_t seed_target;   // counter value that means "every CTA of THIS launch has published" (launch number * grid)
   uint32_t n_rows, dim, kp, nq;
   uint32_t num_tiles;     // ceil(n_rows / 128)
   uint32_t kchunks;       // ceil(dim * elem_size / 128)
@@ -143,6 +146,13 @@ struct RescoreArgs {
   uint32_t n_rows, dim, kp, k;
   float max_l2, max_l1;      // max over rows of |row|_2, |row|_1 (times the row scale for i8), rounded up
   float rel_err;             // bound on |approx - exact| / (|q|_2 * max_l2) excluding the i8 limb residual term
+  // fused merge: when `partial` is set the candidates are selected here from the scan's per-CTA lists [nq][nlists][kp]
+  // (each sorted descending, 0 = empty) and cand_ids / cand_approx are not read
+  const uint64_t* partial;
+  uint32_t nlists;
+  uint32_t* nflag_next;      // optional: zeroed by the kernel (the flag counter of the next call on the stream)
+  uint32_t sel_off;          // set by rescore_exact_launch
+  int stage_rows;            // set by rescore_exact_launch: candidate rows staged in shared memory, 8 lanes per candidate
 };
 cudaError_t rescore_exact_launch(int dtype, const RescoreArgs& a, uint32_t nq, cudaStream_t stream);
 cudaError_t row_norm_max_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim, uint32_t* out2,

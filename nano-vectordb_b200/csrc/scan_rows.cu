@@ -391,6 +391,9 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     const uint32_t ngroups = a.bp >> 4;          // groups of 16 queries
     const uint32_t half_cap = a.cap >> 1;
     uint32_t rp = 0;                             // parity of the compaction work list appends go to
+    // cross-CTA threshold seeding (see below): off when there is no workspace or fewer CTAs than list entries
+    bool seeded = a.seed_ws == nullptr || P < a.kp || P > 256u;
+    uint32_t next_poll = 1;                      // tile count after which the arrival counter is looked at next
 
     // score of (this row, query q) from the raw accumulators, in scan_mma.cu's fixed FP32 order
     auto score_of = [&](const float4& p, uint32_t v, uint32_t w, float rs) -> float {
@@ -515,6 +518,65 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       tc::fence_before_thread_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[buf]);
+
+      // ---- threshold seeding across the CTAs. A CTA sees 1/P of the rows, so its own k'-th best stays far below the
+      // final one and (k' ln) rows per query keep passing it. After its FIRST tile every CTA publishes, per query, the best
+      // score it has seen; the k'-th largest of the P published values is a lower bound of the final k'-th best (k'
+      // distinct rows reach it) that is as tight as if one CTA had seen all P first tiles (~rank 17 of 128 P rows).
+      // Nobody waits: the arrival counter is polled at a few tile boundaries and the bound is adopted once all P CTAs
+      // have published; until then the local thresholds apply. Epochs make the counter reusable without a memset.
+      if (!seeded) {
+        if (it == 0) {
+          for (uint32_t q = ew; q < a.nq; q += kRowsEpiWarps) {
+            const uint32_t c0 = lds_u32(cnt_u32 + q * 4u), c = c0 < a.cap ? c0 : a.cap;
+            uint32_t best = 0u;
+            for (uint32_t i = lane; i < c; i += 32) {
+              const uint32_t h = (uint32_t)(lds_u64(keys_u32 + (q * a.cap + i) * 8u) >> 32);
+              best = h > best ? h : best;
+            }
+            best = __reduce_max_sync(0xffffffffu, best);
+            if (lane == 0) a.seed_ws[16u + j * a.bp + q] = best;
+          }
+          __threadfence();
+          named_bar_sync(1, kRowsEpiThreads);
+          if (tid == 64u) atomicAdd(a.seed_ws, 1u);
+        } else if (it == next_poll) {
+          next_poll += next_poll < 4u ? 1u : next_poll >> 1;
+          if (tid == 64u) {
+            uint32_t cur;
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(cur) : "l"(a.seed_ws) : "memory");
+            sts_u32(wl_u32 + 8u, (int32_t)(cur - a.seed_target) >= 0 ? 1u : 0u);
+          }
+          named_bar_sync(1, kRowsEpiThreads);
+          if (lds_u32(wl_u32 + 8u)) {
+            for (uint32_t q = ew; q < a.nq; q += kRowsEpiWarps) {
+              uint32_t h[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const uint32_t l = lane + 32u * (uint32_t)i;
+                h[i] = l < P ? __ldcg(a.seed_ws + 16u + l * a.bp + q) : 0u;
+              }
+              uint32_t ans = 0u;  // the largest v with at least kp published values >= v: the kp-th largest of them
+#pragma unroll 1
+              for (int bit = 31; bit >= 0; --bit) {
+                const uint32_t cand = ans | (1u << bit);
+                uint32_t n = 0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) n += h[i] >= cand ? 1u : 0u;
+                if (__reduce_add_sync(0xffffffffu, n) >= a.kp) ans = cand;
+              }
+              if (lane == 0 && ans != 0u) {
+                const float t = ordered_to_float(ans);
+                float cur;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(cur) : "r"(par_u32 + q * 16u + 8u));
+                if (t > cur) sts_f32(par_u32 + q * 16u + 8u, t);
+              }
+            }
+            seeded = true;
+            named_bar_sync(1, kRowsEpiThreads);  // the raised thresholds are visible before the next tile's offers
+          }
+        }
+      }
     }
 
     // ---- this CTA's best k' per query -> partial[q][cta][k'] (sorted descending, 0 = empty)

@@ -43,6 +43,8 @@ def small():
 
 
 def perf():
+    """interleaved A/B per batch size: rows kernel with seeding (1), without (2), query-tile kernels (0), streaming scan"""
+    import time
     st = torch.cuda.Stream(device=dev)
     n = 2_903_054
     for dt, name in ((nv.F16, "f16"), (nv.I8, "i8")):
@@ -51,31 +53,44 @@ def perf():
             qh = q.cpu().numpy()
             out_ids = torch.empty((128, 10), dtype=torch.int64, device=dev)
             out_sc = torch.empty((128, 10), dtype=torch.float32, device=dev)
-            for rows in (1, 0):
-                idx.set_tuning(7, rows)
-                for b in (2, 3, 8, 16, 32, 64, 80, 128):
-                    idx.set_path(nv.PATH_MMA_EXACT)
-                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    with torch.cuda.stream(st):
-                        for _ in range(3):
-                            idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
-                        st.synchronize()
-                        idx.profile(True)
-                        e0.record(st)
-                        for _ in range(20):
-                            idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
-                        e1.record(st)
-                        st.synchronize()
-                    scan_ms, merge_ms, calls = idx.profile_read()
-                    idx.profile(False)
-                    import time
-                    t0 = time.perf_counter()
-                    for _ in range(10):
-                        idx.search_topk_dot_batch(qh[:b], 10)
-                    e2e = (time.perf_counter() - t0) * 100
-                    print(json.dumps({"dtype": name, "rows_kernel": rows, "batch": b, "ms": e0.elapsed_time(e1) / 20,
-                                      "scan_ms": scan_ms / max(calls, 1), "merge_ms": merge_ms / max(calls, 1), "e2e_ms": e2e,
-                                      "fallbacks": idx.exact_stats(reset=True)[1]}), flush=True)
+
+            def run(b, iters=20):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                with torch.cuda.stream(st):
+                    for _ in range(3):
+                        idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                    st.synchronize()
+                    idx.profile(True)
+                    e0.record(st)
+                    for _ in range(iters):
+                        idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                    e1.record(st)
+                    st.synchronize()
+                scan_ms, merge_ms, calls = idx.profile_read()
+                idx.profile(False)
+                return e0.elapsed_time(e1) / iters, scan_ms / max(calls, 1)
+
+            for b in (1, 2, 3, 4, 8, 16, 32, 48, 64, 128):
+                rec = {"dtype": name, "batch": b}
+                for rep in range(2):
+                    for label, path, rows in (("rows", nv.PATH_MMA_EXACT, 1), ("rows_noseed", nv.PATH_MMA_EXACT, 2),
+                                              ("tile", nv.PATH_MMA_EXACT, 0), ("gemv", nv.PATH_GEMV, 1)):
+                        if label == "gemv" and b > 8:
+                            continue
+                        idx.set_tuning(7, rows)
+                        idx.set_path(path)
+                        ms, kms = run(b)
+                        key = f"{label}_ms"
+                        if key not in rec or ms < rec[key]:
+                            rec[key], rec[f"{label}_scan"] = round(ms, 4), round(kms, 4)
+                idx.set_tuning(7, 1)
+                idx.set_path(nv.PATH_MMA_EXACT)
+                t0 = time.perf_counter()
+                for _ in range(10):
+                    idx.search_topk_dot_batch(qh[:b], 10)
+                rec["rows_e2e_ms"] = round((time.perf_counter() - t0) * 100, 4)
+                rec["fallbacks"] = idx.exact_stats(reset=True)[1]
+                print(json.dumps(rec), flush=True)
 
 
 if __name__ == "__main__":

@@ -125,6 +125,13 @@ def test_auto_path_crossover_and_timing_path(nv, oracle):
         assert t.path == nv.PATH_GEMV
         idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 3, rng), 10, t)
         assert t.path == nv.PATH_MMA_EXACT
+    b8, s8 = oracle.synth(I8, 2, 0, n, d)
+    with nv.FlatIndexCuda.from_host(b8, s8, I8) as idx:       # int8: the row-tile kernel already wins at two queries
+        t = nv.Timing()
+        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 1, rng), 10, t)
+        assert t.path == nv.PATH_GEMV
+        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 2, rng), 10, t)
+        assert t.path == nv.PATH_MMA_EXACT
     f32 = oracle.synth_f32(2, 0, n, d)
     with nv.FlatIndexCuda.from_host(f32, None, F32) as idx:   # FP32 base: no tensor path (tf32 excluded), GEMV always
         t = nv.Timing()

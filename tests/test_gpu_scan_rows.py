@@ -12,12 +12,14 @@ import pytest
 from _oracle import F16, I8, assert_topk_equal
 
 pytestmark = pytest.mark.gpu
-TUNE_ROWS = 7
+TUNE_ROWS, TUNE_ROWS_SEED = 7, 8
+ROWS_ALWAYS = 2            # "whenever the batch fits" (auto = int8 only)
 
 
-def _search(nv, dtype, base, scales, queries, k, rows):
+def _search(nv, dtype, base, scales, queries, k, rows, seed=1):
     with nv.FlatIndexCuda.from_host(base, scales, dtype) as idx:
         idx.set_tuning(TUNE_ROWS, rows)
+        idx.set_tuning(TUNE_ROWS_SEED, seed)
         idx.set_path(nv.PATH_MMA_EXACT)
         l0 = nv.launch_count()
         ids, sc = idx.search_topk_dot_batch(queries, k)
@@ -37,7 +39,7 @@ def test_rows_kernel_bit_exact_vs_oracle_and_streaming_scan(nv, oracle, dt, n, d
     rng = np.random.default_rng(nq * 131 + k)
     f = oracle.synth_f32(21, 0, n, d)
     queries = np.ascontiguousarray(f[rng.integers(0, n, nq)] + (0.02 * rng.standard_normal((nq, d))).astype(np.float32))
-    ids, sc, gids, gsc, stats, _ = _search(nv, dtype, base, scales, queries, k, rows=1)
+    ids, sc, gids, gsc, stats, _ = _search(nv, dtype, base, scales, queries, k, rows=ROWS_ALWAYS, seed=2)
     assert np.array_equal(ids, gids) and np.array_equal(sc.view(np.uint32), gsc.view(np.uint32)), "rows kernel != streaming scan"
     oids, osc = oracle.search_batch(dtype, base, scales, queries, k)
     kk = min(k, n)
@@ -46,6 +48,8 @@ def test_rows_kernel_bit_exact_vs_oracle_and_streaming_scan(nv, oracle, dt, n, d
     assert stats[0] == nq
     ids0, sc0, _, _, _, _ = _search(nv, dtype, base, scales, queries, k, rows=0)   # the query-tile kernels (scan_mma*.cu)
     assert np.array_equal(ids, ids0) and np.array_equal(sc.view(np.uint32), sc0.view(np.uint32))
+    ids1, sc1, _, _, _, _ = _search(nv, dtype, base, scales, queries, k, rows=ROWS_ALWAYS, seed=0)   # no threshold seeding
+    assert np.array_equal(ids, ids1) and np.array_equal(sc.view(np.uint32), sc1.view(np.uint32))
 
 
 @pytest.mark.parametrize("dt", ["f16", "i8"])
@@ -66,7 +70,7 @@ def test_rows_kernel_every_row_beats_the_threshold(nv, oracle, dt, nq):
     else:
         base, scales = oracle.quantize_i8(rows)
     queries = np.ascontiguousarray(u[None, :] + 0.05 * rng.standard_normal((nq, d)).astype(np.float32))
-    ids, sc, gids, gsc, _, _ = _search(nv, dtype, base, scales, queries, k, rows=1)
+    ids, sc, gids, gsc, _, _ = _search(nv, dtype, base, scales, queries, k, rows=ROWS_ALWAYS, seed=2)
     assert np.array_equal(ids, gids) and np.array_equal(sc.view(np.uint32), gsc.view(np.uint32))
     assert int(ids.min()) > n - 400      # the best rows are the last ones
 
@@ -87,7 +91,7 @@ def test_rows_kernel_exact_ties_and_duplicates(nv, oracle, dt):
         scales[2900:2940] = scales[2900]
     f = oracle.synth_f32(8, 0, n, d)
     queries = np.ascontiguousarray(f[[7, 500, 2900, 1234, 2999, 0, 500]])
-    ids, sc, gids, gsc, stats, _ = _search(nv, dtype, base, scales, queries, k, rows=1)
+    ids, sc, gids, gsc, stats, _ = _search(nv, dtype, base, scales, queries, k, rows=ROWS_ALWAYS, seed=2)
     assert np.array_equal(ids, gids) and np.array_equal(sc.view(np.uint32), gsc.view(np.uint32))
     oids, osc = oracle.search_batch(dtype, base, scales, queries, k)
     assert np.array_equal(ids, oids) and np.array_equal(sc.view(np.uint32), osc.view(np.uint32))
@@ -95,16 +99,17 @@ def test_rows_kernel_exact_ties_and_duplicates(nv, oracle, dt):
 
 
 def test_rows_kernel_is_what_auto_runs_for_small_batches(nv, oracle):
-    """AUTO, 8 queries: prep-free candidate scan (scan_rows_kernel) + merge + re-score = 3 launches; with the knob off
-    the query-tile kernel needs its prep launch as well."""
+    """AUTO, int8, 8 queries: candidate scan (scan_rows_kernel converts the queries itself) + re-score (which selects the
+    candidates from the per-CTA lists itself) = 2 launches; with the knob off the query-tile kernel needs its prep and
+    merge launches as well."""
     n, d, k, nq = 30000, 128, 10, 8
-    base, _ = oracle.synth(F16, 3, 0, n, d)
+    base, scales = oracle.synth(I8, 3, 0, n, d)
     queries = np.ascontiguousarray(oracle.synth_f32(3, 0, n, d)[:nq])
-    with nv.FlatIndexCuda.from_host(base, None, F16) as idx:
+    with nv.FlatIndexCuda.from_host(base, scales, I8) as idx:
         idx.search_topk_dot_batch(queries, k)          # row norms (once per index) + workspaces
         l0 = nv.launch_count()
         idx.search_topk_dot_batch(queries, k)
-        assert nv.launch_count() - l0 == 3
+        assert nv.launch_count() - l0 == 2
         idx.set_tuning(TUNE_ROWS, 0)
         idx.search_topk_dot_batch(queries, k)
         l0 = nv.launch_count()
