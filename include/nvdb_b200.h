@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NVDB_B200_VERSION 100
+#define NVDB_B200_VERSION 101
 
 enum {
   NVDB_B200_OK = 0,
@@ -57,7 +57,11 @@ enum {
 
 typedef struct nvdb_b200_index nvdb_b200_index;
 
-/* mirrors nvdb::CudaRefineTiming's first four fields (include/nvdb/cuda_refine.h:7-8) */
+/* mirrors nvdb::CudaRefineTiming (include/nvdb/cuda_refine.h:7-22): the four event times, the launch shape and the
+ * optional in-kernel phase sampling of the refine kernel (clock64 at the phase boundaries of the first dbg_q queries:
+ * enabled by the reference's own switches, environment CUDA_DBG_TIMING=1 and CUDA_DBG_Q=<n, default 32>, when a timing
+ * struct is passed to nvdb_b200_refine_l2; src/cuda_refine.cu:863-872,1116-1144). Phases here: "write" = the query into
+ * shared memory, "dist" = gather + distances + key writes, "merge" = selection + output. */
 typedef struct nvdb_b200_timing {
   float h2d_ms;
   float kernel_ms;
@@ -65,6 +69,10 @@ typedef struct nvdb_b200_timing {
   float total_ms;
   uint32_t kernel_launches; /* kernels of this library launched by the call */
   uint32_t path;            /* NVDB_B200_PATH_* actually used */
+  uint32_t threads;         /* refine: threads per CTA */
+  uint32_t shmem_bytes;     /* refine: dynamic shared memory per CTA */
+  uint32_t dbg_q;           /* queries sampled (0 = sampling off) */
+  float dbg_dist_cycles_avg, dbg_write_cycles_avg, dbg_merge_cycles_avg;
 } nvdb_b200_timing;
 
 int nvdb_b200_version(void);
@@ -213,6 +221,12 @@ int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const u
 int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, const uint32_t* cand_ids_dev,
                                uint32_t Q, uint32_t R, uint32_t K, uint32_t* out_ids_dev, float* out_dist_dev,
                                void* stream);
+
+/* Page-lock caller memory (cudaHostRegister / cudaHostUnregister behind the C ABI, so that host code needs no CUDA
+ * headers): host-buffer calls copy straight from / to registered or pinned buffers instead of staging them through the
+ * library's own pinned buffers — the analogue of the reference's CUDA_PINNED=1 (src/cuda_refine.cu:875,903-916). */
+int nvdb_b200_host_register(void* ptr, size_t bytes);
+int nvdb_b200_host_unregister(void* ptr);
 
 /* ---- IVF-PQ candidate generation ---------------------------------------------------------
  * The stage in front of the refine: replaces the FAISS calls of the reference's apps — build:

@@ -27,7 +27,9 @@ lib = C.CDLL(str(lib_path))
 
 class Timing(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("kernel_ms", C.c_float), ("d2h_ms", C.c_float), ("total_ms", C.c_float),
-                ("kernel_launches", C.c_uint32), ("path", C.c_uint32)]
+                ("kernel_launches", C.c_uint32), ("path", C.c_uint32), ("threads", C.c_uint32), ("shmem_bytes", C.c_uint32),
+                ("dbg_q", C.c_uint32), ("dbg_dist_cycles_avg", C.c_float), ("dbg_write_cycles_avg", C.c_float),
+                ("dbg_merge_cycles_avg", C.c_float)]
 
 
 class NvdbError(RuntimeError):
@@ -62,6 +64,8 @@ _sig = {
     "nvdb_b200_merge_topk_packed_device": (_i, [_i, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_refine_l2": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_refine_l2_device": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_host_register": (_i, [_vp, C.c_size_t]),
+    "nvdb_b200_host_unregister": (_i, [_vp]),
     "nvdb_b200_synth_fill_device": (_i, [_i, _u32, _u64, _u32, _u64, _u64, _vp, _vp, _vp]),
     "nvdb_b200_convert": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp]),
     "nvdb_b200_convert_device": (_i, [_i, _u32, _vp, _u32, _u64, _u32, _vp, _vp, _vp]),

@@ -1666,6 +1666,40 @@ int nvdb_b200_refine_l2_device(nvdb_b200_index* idx, const float* queries_dev, c
   return NVDB_B200_OK;
 }
 
+// true when the driver can DMA from / to `p` directly (cudaMallocHost / cudaHostRegister memory)
+static bool host_is_pinned(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
+int nvdb_b200_host_register(void* ptr, size_t bytes) {
+  const nvdb_b200_index* idx = nullptr;
+  if (!ptr || bytes == 0) return fail(nullptr, NVDB_B200_ERR_ARG, "host_register: NULL / empty buffer");
+  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();
+    return NVDB_B200_OK;
+  }
+  CK(e, "cudaHostRegister");
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_host_unregister(void* ptr) {
+  const nvdb_b200_index* idx = nullptr;
+  if (!ptr) return NVDB_B200_OK;
+  cudaError_t e = cudaHostUnregister(ptr);
+  if (e == cudaErrorHostMemoryNotRegistered) {
+    cudaGetLastError();
+    return NVDB_B200_OK;
+  }
+  CK(e, "cudaHostUnregister");
+  return NVDB_B200_OK;
+}
+
 int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const uint32_t* cand_ids_host, uint32_t Q,
                         uint32_t R, uint32_t K, uint32_t* out_ids, float* out_dist, nvdb_b200_timing* timing) {
   if (timing) *timing = nvdb_b200_timing{};
@@ -1677,60 +1711,104 @@ int nvdb_b200_refine_l2(nvdb_b200_index* idx, const float* queries_host, const u
   std::lock_guard<std::mutex> g(idx->mu);
   CK(cudaSetDevice(idx->device), "cudaSetDevice");
   const size_t qb = (size_t)Q * idx->dim * 4, cb = (size_t)Q * R * 4, ob = (size_t)Q * K * 4;
+  // Registered / pinned caller buffers are used in place (no staging copy: 41 MB at the K5 shape, which was 3 of the
+  // call's 3.7 ms); pageable ones go through the library's pinned staging buffers in chunks.
+  const bool in_pinned = host_is_pinned(queries_host) && host_is_pinned(cand_ids_host);
+  const bool out_pinned = host_is_pinned(out_ids) && (!out_dist || host_is_pinned(out_dist));
   if ((rc = ensure_ws(idx, WS_QUERIES, qb))) return rc;
   if ((rc = ensure_ws(idx, WS_CAND, cb))) return rc;
   if ((rc = ensure_ws(idx, WS_OUT_IDS32, ob))) return rc;
   if ((rc = ensure_ws(idx, WS_OUT_SCORES, ob))) return rc;
-  if ((rc = ensure_pin(idx, 0, qb + cb))) return rc;
-  if ((rc = ensure_pin(idx, 1, 2 * ob))) return rc;
+  if (!in_pinned && (rc = ensure_pin(idx, 0, qb + cb))) return rc;
+  if (!out_pinned && (rc = ensure_pin(idx, 1, 2 * ob))) return rc;
+  // in-kernel phase sampling (the reference's CUDA_DBG_TIMING / CUDA_DBG_Q switches; only with a timing struct)
+  uint32_t dbg_q = 0;
+  if (timing) {
+    const char* on = getenv("CUDA_DBG_TIMING");
+    if (on && atoi(on) != 0) {
+      const char* dq = getenv("CUDA_DBG_Q");
+      dbg_q = dq ? (uint32_t)atoi(dq) : 32u;
+      if (dbg_q > Q) dbg_q = Q;
+    }
+  }
+  unsigned long long* dbg_dev = nullptr;
+  if (dbg_q) {
+    if ((rc = ensure_ws(idx, WS_DBG, (size_t)dbg_q * 24))) return rc;
+    if ((rc = ensure_pin(idx, 2, (size_t)dbg_q * 24 + 64))) return rc;
+    dbg_dev = (unsigned long long*)idx->d_ws[WS_DBG];
+  }
   cudaStream_t s = idx->stream;
   if ((rc = adopt_stream(idx, s))) return rc;
-  char* hin = (char*)idx->h_pin[0];
-  char* hout = (char*)idx->h_pin[1];
-  // Chunks of queries flow through staging copy -> H2D -> kernel -> D2H, so the host's copy of chunk c+1 into pinned
+  if (dbg_dev) CK(cudaMemsetAsync(dbg_dev, 0, (size_t)dbg_q * 24, s), "memset dbg");
+  const char* hin_q = in_pinned ? (const char*)queries_host : (const char*)idx->h_pin[0];
+  const char* hin_c = in_pinned ? (const char*)cand_ids_host : (const char*)idx->h_pin[0] + qb;
+  char* hout_i = out_pinned ? (char*)out_ids : (char*)idx->h_pin[1];
+  char* hout_d = out_pinned ? (char*)out_dist : (char*)idx->h_pin[1] + ob;
+  // Chunks of queries flow through (staging copy ->) H2D -> kernel -> D2H, so the host's copy of chunk c+1 into pinned
   // memory overlaps the device work on chunk c (the reference moves everything, then computes: src/cuda_refine.cu:
-  // 926-1115). With `timing` the call is one chunk, so that the four events still bracket H2D / kernel / D2H.
+  // 926-1115). With `timing`, or with pinned caller buffers, the call is one chunk: the four events then bracket H2D /
+  // kernel / D2H.
   const size_t per_q = (size_t)idx->dim * 4 + (size_t)R * 4;
-  uint32_t qc = timing ? Q : (uint32_t)(((size_t)8 << 20) / per_q);
+  uint32_t qc = (timing || in_pinned) ? Q : (uint32_t)(((size_t)8 << 20) / per_q);
   if (qc == 0) qc = 1;
   if (qc > Q) qc = Q;
-  if (timing) {  // staged up front: ev[0] -> ev[1] is the H2D copy alone, as in the reference's timing
-    par_memcpy(hin, queries_host, qb);
-    par_memcpy(hin + qb, cand_ids_host, cb);
+  if (timing && !in_pinned) {  // staged up front: ev[0] -> ev[1] is the H2D copy alone, as in the reference's timing
+    par_memcpy(idx->h_pin[0], queries_host, qb);
+    par_memcpy((char*)idx->h_pin[0] + qb, cand_ids_host, cb);
   }
+  uint32_t smem_bytes = 0;
   CK(cudaEventRecord(idx->ev[0], s), "event");
   for (uint32_t q0 = 0; q0 < Q; q0 += qc) {
     const uint32_t nqc = Q - q0 < qc ? Q - q0 : qc;
     const size_t qoff = (size_t)q0 * idx->dim * 4, qlen = (size_t)nqc * idx->dim * 4;
     const size_t coff = (size_t)q0 * R * 4, clen = (size_t)nqc * R * 4;
     const size_t ooff = (size_t)q0 * K * 4, olen = (size_t)nqc * K * 4;
-    if (!timing) {
-      par_memcpy(hin + qoff, (const char*)queries_host + qoff, qlen);
-      par_memcpy(hin + qb + coff, (const char*)cand_ids_host + coff, clen);
+    if (!timing && !in_pinned) {
+      par_memcpy((char*)idx->h_pin[0] + qoff, (const char*)queries_host + qoff, qlen);
+      par_memcpy((char*)idx->h_pin[0] + qb + coff, (const char*)cand_ids_host + coff, clen);
     }
-    CK(cudaMemcpyAsync((char*)idx->d_ws[WS_QUERIES] + qoff, hin + qoff, qlen, cudaMemcpyHostToDevice, s), "H2D queries");
-    CK(cudaMemcpyAsync((char*)idx->d_ws[WS_CAND] + coff, hin + qb + coff, clen, cudaMemcpyHostToDevice, s), "H2D candidates");
+    CK(cudaMemcpyAsync((char*)idx->d_ws[WS_QUERIES] + qoff, hin_q + qoff, qlen, cudaMemcpyHostToDevice, s), "H2D queries");
+    CK(cudaMemcpyAsync((char*)idx->d_ws[WS_CAND] + coff, hin_c + coff, clen, cudaMemcpyHostToDevice, s), "H2D candidates");
     if (timing) CK(cudaEventRecord(idx->ev[1], s), "event");
     CK(refine_l2_launch((int)idx->dtype, idx->payload, idx->scales, idx->n, idx->dim,
                         (const float*)((char*)idx->d_ws[WS_QUERIES] + qoff),
                         (const uint32_t*)((char*)idx->d_ws[WS_CAND] + coff), nqc, R, K,
-                        (uint32_t*)((char*)idx->d_ws[WS_OUT_IDS32] + ooff), (float*)((char*)idx->d_ws[WS_OUT_SCORES] + ooff), s),
+                        (uint32_t*)((char*)idx->d_ws[WS_OUT_IDS32] + ooff), (float*)((char*)idx->d_ws[WS_OUT_SCORES] + ooff), s,
+                        q0 == 0 ? dbg_dev : nullptr, dbg_q, &smem_bytes),
        "refine launch");
     if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
-    CK(cudaMemcpyAsync(hout + ooff, (char*)idx->d_ws[WS_OUT_IDS32] + ooff, olen, cudaMemcpyDeviceToHost, s), "D2H ids");
+    CK(cudaMemcpyAsync(hout_i + ooff, (char*)idx->d_ws[WS_OUT_IDS32] + ooff, olen, cudaMemcpyDeviceToHost, s), "D2H ids");
     if (out_dist)
-      CK(cudaMemcpyAsync(hout + ob + ooff, (char*)idx->d_ws[WS_OUT_SCORES] + ooff, olen, cudaMemcpyDeviceToHost, s), "D2H dist");
+      CK(cudaMemcpyAsync(hout_d + ooff, (char*)idx->d_ws[WS_OUT_SCORES] + ooff, olen, cudaMemcpyDeviceToHost, s), "D2H dist");
   }
   CK(cudaEventRecord(idx->ev[3], s), "event");
-  CK(cudaEventSynchronize(idx->ev[3]), "refine sync");
-  std::memcpy(out_ids, hout, ob);
-  if (out_dist) std::memcpy(out_dist, hout + ob, ob);
+  if (dbg_dev) CK(cudaMemcpyAsync(idx->h_pin[2], dbg_dev, (size_t)dbg_q * 24, cudaMemcpyDeviceToHost, s), "D2H dbg");
+  CK(cudaStreamSynchronize(s), "refine sync");
+  if (!out_pinned) {
+    std::memcpy(out_ids, hout_i, ob);
+    if (out_dist) std::memcpy(out_dist, hout_d, ob);
+  }
   if (timing) {
     cudaEventElapsedTime(&timing->h2d_ms, idx->ev[0], idx->ev[1]);
     cudaEventElapsedTime(&timing->kernel_ms, idx->ev[1], idx->ev[2]);
     cudaEventElapsedTime(&timing->d2h_ms, idx->ev[2], idx->ev[3]);
     cudaEventElapsedTime(&timing->total_ms, idx->ev[0], idx->ev[3]);
     timing->kernel_launches = 1;
+    timing->threads = (uint32_t)kRefineThreadsPerCta;
+    timing->shmem_bytes = smem_bytes;
+    if (dbg_q) {
+      const unsigned long long* h = (const unsigned long long*)idx->h_pin[2];
+      double w = 0, d = 0, m = 0;
+      for (uint32_t i = 0; i < dbg_q; ++i) {
+        w += (double)h[(size_t)i * 3 + 0];
+        d += (double)h[(size_t)i * 3 + 1];
+        m += (double)h[(size_t)i * 3 + 2];
+      }
+      timing->dbg_q = dbg_q;
+      timing->dbg_write_cycles_avg = (float)(w / dbg_q);
+      timing->dbg_dist_cycles_avg = (float)(d / dbg_q);
+      timing->dbg_merge_cycles_avg = (float)(m / dbg_q);
+    }
   }
   return NVDB_B200_OK;
 }

@@ -3,13 +3,13 @@
 // Replaces nvdb::cuda_l2_topk_batch's kernels (reference src/cuda_refine.cu:405-838). The reference gives one
 // THREAD a whole candidate row (32 lanes -> 32 different rows, uncoalesced) and merges K-lists on thread 0
 // (58 % of its kernel time, Performance_CUDA.md:267). Here:
-//   * one CTA per query, one WARP per candidate row: a row is read as consecutive 16-byte pieces by
-//     consecutive lanes (every request is a fully used 512-byte span), two rows in flight per warp;
+//   * one CTA per query, 8 / 16 / 32 LANES per candidate row (whichever keeps every lane busy for the row length): a row
+//     is read as consecutive 16-byte pieces by consecutive lanes, four rows in flight per lane group;
 //   * the query lives in shared memory; per-lane partial sums use 4 independent chains, then a fixed
 //     shuffle tree — deterministic, and closer to the double-precision CPU refine
 //     (apps/nvdb_ivf_eval.cpp:232-240) than the reference kernel's 4 x 192-long chains;
-//   * selection = block bitonic sort of R (distance, id) keys in shared memory; K smallest written in
-//     ascending order (ties: id ascending). No serial merge.
+//   * selection = rank counting over the R (distance, id) keys in shared memory (R <= 512; a block bitonic sort above):
+//     K smallest written in ascending order (ties: id ascending). No serial merge.
 // Semantics kept: ids >= N (incl. 0xFFFFFFFF) are skipped; unfilled output slots are 0xFFFFFFFF / 1e30f
 // (src/cuda_refine.cu:435-437, 891-894).
 #include "common.cuh"
@@ -61,59 +61,106 @@ __device__ __forceinline__ void l2_piece(const uint4 v, const float* __restrict_
   }
 }
 
-template <int DT>
+// LPR lanes share a candidate row (8, 16 or 32: the host picks the one that keeps every lane busy for the row length:
+// a 768-byte row is 48 pieces = 16 lanes x 3, a 1536-byte row 32 lanes x 3, a 128-byte row 8 lanes x 1), and every group
+// keeps kRowsInFlight rows in flight, so the bytes a CTA has outstanding do not depend on the shape.
+constexpr int kRowsInFlight = 4;
+
+template <int DT, int LPR>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ scales, uint64_t n, uint32_t dim,
                  const float* __restrict__ queries, const uint32_t* __restrict__ cand, uint32_t R, uint32_t K,
-                 uint32_t sortn, uint32_t* __restrict__ out_ids, float* __restrict__ out_dist) {
+                 uint32_t sortn, uint32_t* __restrict__ out_ids, float* __restrict__ out_dist,
+                 unsigned long long* __restrict__ dbg, uint32_t dbg_q) {
   extern __shared__ uint64_t smem64[];
+  // optional in-kernel phase sampling (the reference's CUDA_DBG_TIMING, src/cuda_refine.cu:863-872,1116-1144): thread 0
+  // of the first dbg_q queries records clock64 at the phase boundaries -> dbg[q*3 + {0: query staging, 1: gather +
+  // distances, 2: selection + output}] cycles
+  const bool sample = dbg != nullptr && blockIdx.x < dbg_q && threadIdx.x == 0;
+  long long tq0 = 0, tq1 = 0, tq2 = 0;
+  if (sample) tq0 = clock64();
   uint64_t* skeys = smem64;                                  // [sortn]
   float* sq = reinterpret_cast<float*>(smem64 + sortn);      // [dim]
   constexpr int ES = (DT == kDtF32) ? 4 : (DT == kDtF16 ? 2 : 1);
   constexpr int P16 = 16 / ES;
-  const uint32_t q = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  constexpr uint32_t kGroups = kRefineThreads / LPR;
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  const uint32_t grp = tid / LPR, gl = tid % LPR;
   const size_t row_bytes = (size_t)dim * ES;
   const uint32_t npieces = (uint32_t)(row_bytes >> 4);       // dim * ES is a multiple of 16 (checked by the host)
 
   for (uint32_t i = tid; i < dim; i += kRefineThreads) sq[i] = queries[(size_t)q * dim + i];
   for (uint32_t i = R + tid; i < sortn; i += kRefineThreads) skeys[i] = 0ull;
   __syncthreads();
+  if (sample) tq1 = clock64();
 
   const uint32_t* cq = cand + (size_t)q * R;
-  for (uint32_t r0 = warp * 2; r0 < R; r0 += kRefineWarps * 2) {
-    const uint32_t idA = cq[r0];
-    const uint32_t idB = (r0 + 1 < R) ? cq[r0 + 1] : 0xFFFFFFFFu;
-    const bool okA = (uint64_t)idA < n, okB = (uint64_t)idB < n;
-    const uint8_t* rowA = base + (size_t)(okA ? idA : 0) * row_bytes;
-    const uint8_t* rowB = base + (size_t)(okB ? idB : 0) * row_bytes;
-    float scA = 1.f, scB = 1.f;
-    if constexpr (DT == kDtI8) {
-      scA = okA ? __ldg(scales + idA) : 0.f;
-      scB = okB ? __ldg(scales + idB) : 0.f;
-    }
-    float accA[4] = {0.f, 0.f, 0.f, 0.f}, accB[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 3
-    for (uint32_t c = lane; c < npieces; c += 32) {
-      uint4 va = make_uint4(0, 0, 0, 0), vb = make_uint4(0, 0, 0, 0);
-      if (okA) va = ldg128_stream(rowA + (size_t)c * 16);
-      if (okB) vb = ldg128_stream(rowB + (size_t)c * 16);
-      l2_piece<DT>(va, sq + c * P16, scA, accA);
-      l2_piece<DT>(vb, sq + c * P16, scB, accB);
-    }
-    float dA = __fadd_rn(__fadd_rn(accA[0], accA[1]), __fadd_rn(accA[2], accA[3]));
-    float dB = __fadd_rn(__fadd_rn(accB[0], accB[1]), __fadd_rn(accB[2], accB[3]));
+  for (uint32_t r0 = grp * kRowsInFlight; r0 < R; r0 += kGroups * kRowsInFlight) {
+    uint32_t id[kRowsInFlight];
+    bool ok[kRowsInFlight];
+    const uint8_t* row[kRowsInFlight];
+    float sc[kRowsInFlight], acc[kRowsInFlight][4];
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-      dA = __fadd_rn(dA, __shfl_xor_sync(0xffffffffu, dA, off));
-      dB = __fadd_rn(dB, __shfl_xor_sync(0xffffffffu, dB, off));
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      id[u] = (r0 + u < R) ? cq[r0 + u] : 0xFFFFFFFFu;
+      ok[u] = (uint64_t)id[u] < n;
+      row[u] = base + (size_t)(ok[u] ? id[u] : 0) * row_bytes;
+      sc[u] = 1.f;
+      if constexpr (DT == kDtI8) sc[u] = ok[u] ? __ldg(scales + id[u]) : 0.f;
+#pragma unroll
+      for (int a4 = 0; a4 < 4; ++a4) acc[u][a4] = 0.f;
     }
-    if (lane == 0) {
+    for (uint32_t c = gl; c < npieces; c += LPR) {
+      uint4 v[kRowsInFlight];
+#pragma unroll
+      for (int u = 0; u < kRowsInFlight; ++u) v[u] = ok[u] ? ldg128_stream(row[u] + (size_t)c * 16) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int u = 0; u < kRowsInFlight; ++u) l2_piece<DT>(v[u], sq + c * P16, sc[u], acc[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      float d = __fadd_rn(__fadd_rn(acc[u][0], acc[u][1]), __fadd_rn(acc[u][2], acc[u][3]));
+#pragma unroll
+      for (int off = LPR / 2; off > 0; off >>= 1) d = __fadd_rn(d, __shfl_xor_sync(0xffffffffu, d, off));
       // distance >= +0, so its bit pattern orders like the value; smaller (dist, id) -> larger stored key
-      skeys[r0] = okA ? ~(((uint64_t)__float_as_uint(dA) << 32) | idA) : 0ull;
-      if (r0 + 1 < R) skeys[r0 + 1] = okB ? ~(((uint64_t)__float_as_uint(dB) << 32) | idB) : 0ull;
+      if (gl == 0 && r0 + u < R) skeys[r0 + u] = ok[u] ? ~(((uint64_t)__float_as_uint(d) << 32) | id[u]) : 0ull;
     }
   }
   __syncthreads();
+  if (sample) {
+    tq2 = clock64();
+    dbg[(size_t)q * 3 + 0] = (unsigned long long)(tq1 - tq0);
+    dbg[(size_t)q * 3 + 1] = (unsigned long long)(tq2 - tq1);
+  }
+  if (sortn <= 512u) {
+    // selection by rank counting (keys are unique per (distance, id); duplicates of one id get consecutive ranks by
+    // position): a thread's key goes to output slot `rank` when rank < K. R^2 / 256 broadcast compares per thread and
+    // no barrier, against the 36+ barrier-separated stages of a full sort of 256 keys.
+    for (uint32_t j = tid; j < K; j += kRefineThreads) {
+      out_ids[(size_t)q * K + j] = 0xFFFFFFFFu;
+      if (out_dist) out_dist[(size_t)q * K + j] = 1e30f;
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < R; i += kRefineThreads) {
+      const uint64_t mine = skeys[i];
+      if (mine == 0ull) continue;
+      uint32_t rank = 0;
+      for (uint32_t m = 0; m < R; ++m) {
+        const uint64_t o = skeys[m];
+        rank += (o > mine || (o == mine && m < i)) ? 1u : 0u;
+      }
+      if (rank < K) {
+        const uint64_t key = ~mine;
+        out_ids[(size_t)q * K + rank] = (uint32_t)key;
+        if (out_dist) out_dist[(size_t)q * K + rank] = __uint_as_float((uint32_t)(key >> 32));
+      }
+    }
+    if (dbg != nullptr && blockIdx.x < dbg_q) {  // the selection phase ends when the slowest thread is done
+      __syncthreads();
+      if (sample) dbg[(size_t)q * 3 + 2] = (unsigned long long)(clock64() - tq2);
+    }
+    return;
+  }
   auto sync = [] { __syncthreads(); };
   bitonic_sort_desc(skeys, sortn, tid, kRefineThreads, sync);
   for (uint32_t j = tid; j < K; j += kRefineThreads) {
@@ -123,31 +170,39 @@ refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ sca
     out_ids[(size_t)q * K + j] = ok ? (uint32_t)key : 0xFFFFFFFFu;
     if (out_dist) out_dist[(size_t)q * K + j] = ok ? __uint_as_float((uint32_t)(key >> 32)) : 1e30f;
   }
+  if (sample) dbg[(size_t)q * 3 + 2] = (unsigned long long)(clock64() - tq2);
 }
 
 }  // namespace
 
 cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim,
                              const float* queries, const uint32_t* cand, uint32_t Q, uint32_t R, uint32_t K,
-                             uint32_t* out_ids, float* out_dist, cudaStream_t stream) {
+                             uint32_t* out_ids, float* out_dist, cudaStream_t stream, unsigned long long* dbg,
+                             uint32_t dbg_q, uint32_t* smem_bytes_out) {
   if (Q == 0 || K == 0) return cudaSuccess;
   const uint32_t sortn = next_pow2(R < 2 ? 2 : R);
   const size_t smem = (size_t)sortn * 8u + (size_t)dim * 4u;
   if (smem > 220u * 1024u) return cudaErrorInvalidValue;
+  if (smem_bytes_out) *smem_bytes_out = (uint32_t)smem;
   auto go = [&](auto kern) -> cudaError_t {
     if (smem > 48u * 1024u) {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
     }
     kern<<<Q, kRefineThreads, smem, stream>>>(reinterpret_cast<const uint8_t*>(base), scales, n, dim, queries, cand, R,
-                                              K, sortn, out_ids, out_dist);
+                                              K, sortn, out_ids, out_dist, dbg, dbg_q);
     count_launch();
     return cudaGetLastError();
   };
+  // lanes per row: the largest of 32 / 16 / 8 that leaves no lane without a piece in the last pass over the row
+  const uint32_t es = dtype == kDtF32 ? 4u : dtype == kDtF16 ? 2u : 1u;
+  const uint32_t npieces = (uint32_t)(((size_t)dim * es) >> 4);
+  const int lpr = (npieces % 32u == 0u) ? 32 : (npieces % 16u == 0u) ? 16 : (npieces % 8u == 0u || npieces < 16u) ? 8 : (npieces < 48u ? 16 : 32);
+  auto pick = [&](auto k32, auto k16, auto k8) -> cudaError_t { return lpr == 32 ? go(k32) : lpr == 16 ? go(k16) : go(k8); };
   switch (dtype) {
-    case kDtF32: return go(refine_l2_kernel<kDtF32>);
-    case kDtF16: return go(refine_l2_kernel<kDtF16>);
-    case kDtI8: return go(refine_l2_kernel<kDtI8>);
+    case kDtF32: return pick(refine_l2_kernel<kDtF32, 32>, refine_l2_kernel<kDtF32, 16>, refine_l2_kernel<kDtF32, 8>);
+    case kDtF16: return pick(refine_l2_kernel<kDtF16, 32>, refine_l2_kernel<kDtF16, 16>, refine_l2_kernel<kDtF16, 8>);
+    case kDtI8: return pick(refine_l2_kernel<kDtI8, 32>, refine_l2_kernel<kDtI8, 16>, refine_l2_kernel<kDtI8, 8>);
     default: return cudaErrorInvalidValue;
   }
 }

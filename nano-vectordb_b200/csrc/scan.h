@@ -70,7 +70,9 @@ cudaError_t merge_lists_launch(const uint64_t* ids, const float* scores, size_t 
 
 cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, uint64_t n, uint32_t dim,
                              const float* queries, const uint32_t* cand, uint32_t Q, uint32_t R, uint32_t K,
-                             uint32_t* out_ids, float* out_dist, cudaStream_t stream);
+                             uint32_t* out_ids, float* out_dist, cudaStream_t stream, unsigned long long* dbg = nullptr,
+                             uint32_t dbg_q = 0, uint32_t* smem_bytes_out = nullptr);
+constexpr int kRefineThreadsPerCta = 256;
 
 cudaError_t synth_fill_launch(int dtype, uint64_t n, uint32_t dim, uint64_t seed, uint64_t first_row, void* payload,
                               float* scales, cudaStream_t stream);

@@ -14,6 +14,7 @@
 // No compute happens here: every call lands in libnvdb_b200.so.
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <memory>
 #include <mutex>
 #include <stdexcept>
@@ -30,8 +31,22 @@ struct SearchResult {  // include/nvdb/topK.h:9-12
   float score;
 };
 
-struct CudaRefineTiming {  // include/nvdb/cuda_refine.h:7-22 (first four fields; the clock64 debug block is dropped)
+struct CudaRefineTiming {  // include/nvdb/cuda_refine.h:7-22, field for field
   float h2d_ms = 0, kernel_ms = 0, d2h_ms = 0, total_ms = 0;
+  uint32_t threads = 0;
+  uint32_t nwarps = 0;
+  uint32_t K = 0;
+  uint32_t R = 0;
+  size_t shmem_bytes = 0;
+  // debug timing (clock64 sample; CUDA_DBG_TIMING=1, CUDA_DBG_Q=<n>). Phases of this kernel: "write" = the query into
+  // shared memory, "dist" = gather + distances, "merge" = selection + output (include/nvdb_b200.h).
+  uint32_t dbg_q = 0;
+  double dbg_dist_cycles_avg = 0.0;
+  double dbg_write_cycles_avg = 0.0;
+  double dbg_merge_cycles_avg = 0.0;
+  double dbg_dist_pct = 0.0;
+  double dbg_write_pct = 0.0;
+  double dbg_merge_pct = 0.0;
 };
 
 namespace detail {
@@ -109,7 +124,10 @@ class FlatIndexCuda {
 };
 
 // Same signature as the reference's refine entry point. base_dtype: 1 = f32, 2 = f16 (3 = i8 is not expressible through
-// this signature because it carries no scales; use FlatIndexCuda::refine_l2).
+// this signature because it carries no scales; use FlatIndexCuda::refine_l2). The reference's environment switches are
+// honoured (src/cuda_refine.cu:863-876): CUDA_RETURN_DIST=0 -> ids only (out_dist is cleared), CUDA_PINNED=1 -> the
+// caller's query / candidate buffers are page-locked (once per buffer) and read by the copy engine in place,
+// CUDA_DBG_TIMING=1 (+ CUDA_DBG_Q) -> in-kernel phase sampling into the timing struct.
 inline void cuda_l2_topk_batch(const void* base_ptr, uint32_t base_dtype, uint64_t N, uint32_t D,
                                const float* queries_f32, const uint32_t* cand_ids, uint32_t Q, uint32_t R, uint32_t K,
                                std::vector<uint32_t>& out_ids, std::vector<float>& out_dist,
@@ -120,10 +138,28 @@ inline void cuda_l2_topk_batch(const void* base_ptr, uint32_t base_dtype, uint64
     uint32_t dtype = 0, dim = 0;
     uint64_t n = 0;
     std::unique_ptr<FlatIndexCuda> idx;
+    const void *reg_q = nullptr, *reg_c = nullptr;  // buffers registered for CUDA_PINNED=1
+    size_t reg_q_bytes = 0, reg_c_bytes = 0;
+    ~Cache() {
+      if (reg_q) nvdb_b200_host_unregister(const_cast<void*>(reg_q));
+      if (reg_c) nvdb_b200_host_unregister(const_cast<void*>(reg_c));
+    }
   };
   static Cache c;
+  if (timing) *timing = CudaRefineTiming{};
   if (base_dtype != 1 && base_dtype != 2) throw std::runtime_error("Unsupported base dtype (Float32/Float16 only)");
+  auto env_int = [](const char* k, int defv) {
+    const char* v = std::getenv(k);
+    return v ? std::atoi(v) : defv;
+  };
+  const bool want_dist = env_int("CUDA_RETURN_DIST", 1) != 0;
+  const bool pinned = env_int("CUDA_PINNED", 0) != 0;
   std::lock_guard<std::mutex> g(c.mu);
+  if (K == 0 || Q == 0 || R == 0) {  // src/cuda_refine.cu:853-857
+    out_ids.clear();
+    out_dist.clear();
+    return;
+  }
   if (!c.idx || c.ptr != base_ptr || c.dtype != base_dtype || c.n != N || c.dim != D) {
     c.idx.reset();
     c.idx = std::make_unique<FlatIndexCuda>(base_ptr, nullptr, base_dtype, N, D, 0);
@@ -132,13 +168,42 @@ inline void cuda_l2_topk_batch(const void* base_ptr, uint32_t base_dtype, uint64
     c.n = N;
     c.dim = D;
   }
+  if (pinned) {
+    auto pin = [](const void*& have, size_t& have_bytes, const void* want, size_t bytes) {
+      if (have == want && have_bytes >= bytes) return;
+      if (have) nvdb_b200_host_unregister(const_cast<void*>(have));
+      have = nullptr;
+      if (nvdb_b200_host_register(const_cast<void*>(want), bytes) == NVDB_B200_OK) {
+        have = want;
+        have_bytes = bytes;
+      }
+    };
+    pin(c.reg_q, c.reg_q_bytes, queries_f32, (size_t)Q * D * sizeof(float));
+    pin(c.reg_c, c.reg_c_bytes, cand_ids, (size_t)Q * R * sizeof(uint32_t));
+  }
   nvdb_b200_timing t{};
-  c.idx->refine_l2(queries_f32, cand_ids, Q, R, K, out_ids, out_dist, &t);
+  c.idx->refine_l2(queries_f32, cand_ids, Q, R, K, out_ids, out_dist, &t, want_dist);
+  if (!want_dist) out_dist.clear();  // src/cuda_refine.cu:893-894
   if (timing) {
     timing->h2d_ms = t.h2d_ms;
     timing->kernel_ms = t.kernel_ms;
     timing->d2h_ms = t.d2h_ms;
     timing->total_ms = t.total_ms;
+    timing->threads = t.threads;
+    timing->nwarps = t.threads / 32;
+    timing->K = K;
+    timing->R = R;
+    timing->shmem_bytes = t.shmem_bytes;
+    timing->dbg_q = t.dbg_q;
+    timing->dbg_dist_cycles_avg = t.dbg_dist_cycles_avg;
+    timing->dbg_write_cycles_avg = t.dbg_write_cycles_avg;
+    timing->dbg_merge_cycles_avg = t.dbg_merge_cycles_avg;
+    const double tot = timing->dbg_dist_cycles_avg + timing->dbg_write_cycles_avg + timing->dbg_merge_cycles_avg;
+    if (tot > 0.0) {
+      timing->dbg_dist_pct = timing->dbg_dist_cycles_avg / tot;
+      timing->dbg_write_pct = timing->dbg_write_cycles_avg / tot;
+      timing->dbg_merge_pct = timing->dbg_merge_cycles_avg / tot;
+    }
   }
 }
 

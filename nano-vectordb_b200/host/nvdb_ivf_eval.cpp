@@ -1,7 +1,8 @@
 // nvdb_ivf_eval (B200) — ANN evaluation harness with the reference tool's command line and report, both stages on the GPU.
 //
 //   nvdb_ivf_eval <base.vecbin> <ivf.nvdbivf> <query.vecbin> <k>
-//   Env: IVF_NPROBE=16  WARMUP=5  REFINE_K=0  EVAL_MODE=full|ann_only  GT_PATH=<gtbin>  (+ IVF_GPU=0)
+//   Env: IVF_NPROBE=16  WARMUP=5  REFINE_K=0  EVAL_MODE=full|ann_only  GT_PATH=<gtbin>  PIPELINE=staged|interleaved
+//        EXACT_METRIC=L2|DOT  CUDA_DBG_TIMING=1 CUDA_DBG_Q=<n> CUDA_DBG_DIR=<dir>  (+ IVF_GPU=0)
 //
 // Follows apps/nvdb_ivf_eval.cpp: argv / exit codes 1-3, 7-10 (:309-380), the staged protocol (:470-662: stage A one
 // query per call with its own wall-clock latency, stage B ONE batched refine whose per-query share is added to every
@@ -9,13 +10,17 @@
 // (:708-779: Recall@k, ANN / TOTAL Avg p50 p95 p99, one RESULT line of key=value pairs). Differences: the index file is
 // this repo's container (ivfpq_file.h), stage A is nvdb_b200_ivfpq_search instead of faiss::Index::search, stage B is
 // nvdb_b200_refine_l2 (always the CUDA refine; CUDA_REFINE=0's host loop does not exist here). Without GT_PATH the
-// reference computes exact L2 neighbours on the host cores; here they come from the exact flat scan on the GPU
-// (dot-product ranking, identical to L2 ranking for the L2-normalised embeddings the tool chain assumes,
-// apps/nvdb_gt_build.cpp:33-35).
+// reference computes exact neighbours on the host cores (EXACT_METRIC=L2: exact_topk_l2_ids, DOT: FlatIndexOMP,
+// apps/nvdb_ivf_eval.cpp:353,384-385,431-435); here EXACT_METRIC=DOT is the exact flat scan on the GPU and EXACT_METRIC=L2
+// (the default, as in the reference) re-ranks the flat scan's top max(4k, 64) by exact L2 with the refine kernel — the L2
+// ranking itself whenever the true L2 top-k lies inside that dot-product shortlist, which holds for the L2-normalised
+// embeddings the tool chain assumes (apps/nvdb_gt_build.cpp:33-35), where the two rankings coincide.
+// PIPELINE=interleaved (apps/nvdb_ivf_eval.cpp:465,664-693): ANN + refine per query, one latency sample for both.
 #include <algorithm>
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <filesystem>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
@@ -61,6 +66,35 @@ struct GtBinHeader {  // include/nvdb/gtbin_format.h:18-35
 };
 #pragma pack(pop)
 constexpr uint64_t kGtMagic = 0x4E56444247543031ULL;
+
+// the reference's clock64 phase dump (apps/nvdb_ivf_eval.cpp:47-126): same file name pattern, columns and DBG_TSV line
+void write_dbg_tsv_if_enabled(const nvdb_b200_timing& t, int k, uint64_t Q, uint32_t R, int nprobe, int refine_k) {
+  if (getenv_int("CUDA_DBG_TIMING", 0) == 0 || t.dbg_q == 0) return;
+  const std::string outdir = getenv_str("CUDA_DBG_DIR", "./results_dbg");
+  std::filesystem::create_directories(outdir);
+  const int pinned = getenv_int("CUDA_PINNED", 0), ret = getenv_int("CUDA_RETURN_DIST", 1);
+  const std::string git = getenv_str("GIT_SHA", "NA");
+  const std::string path = outdir + "/dbg_K" + std::to_string(k) + "_Q" + std::to_string(Q) + "_R" + std::to_string(R) + "_th" +
+                           std::to_string(t.threads) + "_mode=b200_optin=1_pinned=" + std::to_string(pinned) +
+                           "_ret=" + std::to_string(ret) + "_git=" + git + ".tsv";
+  std::ofstream ofs(path, std::ios::out | std::ios::trunc);
+  if (!ofs) {
+    std::cerr << "[WARN] cannot write DBG TSV: " << path << "\n";
+    return;
+  }
+  const double tot = (double)t.dbg_dist_cycles_avg + t.dbg_write_cycles_avg + t.dbg_merge_cycles_avg;
+  const double pd = tot > 0 ? t.dbg_dist_cycles_avg / tot : 0, pw = tot > 0 ? t.dbg_write_cycles_avg / tot : 0,
+               pm = tot > 0 ? t.dbg_merge_cycles_avg / tot : 0;
+  ofs << "k\tQ\tR\tnprobe\trefine_k\tkernel_mode\tcuda_threads\tcuda_nwarps\tcuda_shmem_bytes\tcuda_shmem_optin\t"
+         "cuda_pinned\tcuda_return_dist\tgit_rev\tdbg_q\tdbg_dist_cycles_avg\tdbg_write_cycles_avg\tdbg_merge_cycles_avg\t"
+         "dbg_dist_pct\tdbg_write_pct\tdbg_merge_pct\n";
+  ofs << k << "\t" << Q << "\t" << R << "\t" << nprobe << "\t" << refine_k << "\tb200\t" << t.threads << "\t" << t.threads / 32 << "\t"
+      << t.shmem_bytes << "\t1\t" << pinned << "\t" << ret << "\t" << git << "\t" << t.dbg_q << "\t" << std::fixed
+      << std::setprecision(3) << t.dbg_dist_cycles_avg << "\t" << t.dbg_write_cycles_avg << "\t" << t.dbg_merge_cycles_avg << "\t"
+      << std::setprecision(6) << pd << "\t" << pw << "\t" << pm << "\n";
+  std::cout << "DBG_TSV=" << path << " dbg_q=" << t.dbg_q << " dist%=" << std::setprecision(3) << pd * 100.0
+            << " write%=" << pw * 100.0 << " merge%=" << pm * 100.0 << "\n";
+}
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -71,7 +105,9 @@ int main(int argc, char** argv) {
               << "  WARMUP=5\n"
               << "  REFINE_K=0\n"
               << "  GT_PATH=<query.gtbin>\n"
-              << "  EVAL_MODE=full|ann_only   (default: full)\n";
+              << "  EVAL_MODE=full|ann_only   (default: full)\n"
+              << "  PIPELINE=staged|interleaved   (default: staged)\n"
+              << "  EXACT_METRIC=L2|DOT   (default: L2)\n";
     return 1;
   }
   const std::string base_path = argv[1], index_path = argv[2], query_path = argv[3];
@@ -99,6 +135,18 @@ int main(int argc, char** argv) {
     const uint32_t d = base.dim();
     const uint64_t Q = query.count();
     const bool ann_only = getenv_str("EVAL_MODE", "full") == "ann_only";
+    const std::string pipeline = getenv_str("PIPELINE", "staged");
+    const bool interleaved = pipeline == "interleaved";
+    if (!interleaved && pipeline != "staged") {
+      std::cerr << "PIPELINE must be staged or interleaved\n";
+      return 6;
+    }
+    const std::string exact_metric = getenv_str("EXACT_METRIC", "L2");
+    if (exact_metric != "L2" && exact_metric != "DOT") {
+      std::cerr << "EXACT_METRIC must be L2 or DOT\n";
+      return 6;
+    }
+    std::cout << "PIPELINE=" << pipeline << " EXACT_METRIC=" << exact_metric << "\n";
     const std::string gt_path = getenv_str("GT_PATH", "");
     std::vector<uint32_t> gt;  // [Q * k]
     if (!gt_path.empty() && !ann_only) {
@@ -146,11 +194,23 @@ int main(int argc, char** argv) {
 
     if (gt.empty() && !ann_only) {  // exact neighbours from the flat scan (see the header comment)
       gt.resize((size_t)Q * k);
+      const bool l2 = exact_metric == "L2";
+      const uint32_t ks = l2 ? (uint32_t)std::min<uint64_t>(base.count(), (uint64_t)std::max(4 * k, 64)) : (uint32_t)k;
+      std::vector<uint32_t> shortlist, l2_ids;
+      std::vector<float> l2_dist;
       for (uint64_t q0 = 0; q0 < Q; q0 += 1024) {
         const uint32_t nq = (uint32_t)std::min<uint64_t>(1024, Q - q0);
-        auto res = flat.search_topk_dot_batch(query.vector_ptr_f32(q0), nq, (uint32_t)k);
+        auto res = flat.search_topk_dot_batch(query.vector_ptr_f32(q0), nq, ks);
+        if (!l2) {
+          for (uint32_t i = 0; i < nq; ++i)
+            for (int j = 0; j < k; ++j) gt[(q0 + i) * k + j] = j < (int)res[i].size() ? (uint32_t)res[i][j].id : 0xFFFFFFFFu;
+          continue;
+        }
+        shortlist.assign((size_t)nq * ks, 0xFFFFFFFFu);
         for (uint32_t i = 0; i < nq; ++i)
-          for (int j = 0; j < k; ++j) gt[(q0 + i) * k + j] = j < (int)res[i].size() ? (uint32_t)res[i][j].id : 0xFFFFFFFFu;
+          for (uint32_t j = 0; j < ks && j < res[i].size(); ++j) shortlist[(size_t)i * ks + j] = (uint32_t)res[i][j].id;
+        flat.refine_l2(query.vector_ptr_f32(q0), shortlist.data(), nq, ks, (uint32_t)k, l2_ids, l2_dist);
+        std::memcpy(gt.data() + q0 * k, l2_ids.data(), (size_t)nq * k * 4);
       }
     }
 
@@ -161,10 +221,35 @@ int main(int argc, char** argv) {
     for (int i = 0; i < warmup && Q > 0; ++i)
       nvdb_b200_ivfpq_search(ivf, query.vector_ptr_f32(0), 1, (uint32_t)nprobe, (uint32_t)k_search, I.data(), nullptr);
 
-    // ---- stage A: ANN only, one query per call
     std::vector<double> ann_lat_ms, total_lat_ms;
     ann_lat_ms.reserve(Q);
-    for (uint64_t qi = 0; qi < Q; ++qi) {
+    std::vector<uint32_t> pred_il;  // interleaved pipeline: per-query refine results
+    if (interleaved) {
+      // ---- interleaved: ANN then refine of the same query, one call each, one latency sample for the pair
+      // (apps/nvdb_ivf_eval.cpp:664-693); the candidates never leave the device (nvdb_b200_ivfpq_search_refine)
+      const bool refine_il = !ann_only && refine_k > 0;
+      pred_il.assign((size_t)Q * k, 0xFFFFFFFFu);
+      std::vector<uint32_t> one((size_t)k);
+      for (uint64_t qi = 0; qi < Q; ++qi) {
+        const auto t0 = std::chrono::steady_clock::now();
+        int st;
+        if (refine_il)
+          st = nvdb_b200_ivfpq_search_refine(ivf, flat.handle(), query.vector_ptr_f32(qi), 1, (uint32_t)nprobe, (uint32_t)k_search,
+                                             (uint32_t)k, one.data(), nullptr);
+        else
+          st = nvdb_b200_ivfpq_search(ivf, query.vector_ptr_f32(qi), 1, (uint32_t)nprobe, (uint32_t)k_search, I.data(), nullptr);
+        if (st != NVDB_B200_OK) {
+          std::cerr << "Error: " << nvdb_b200_ivfpq_last_error(ivf) << "\n";
+          return 11;
+        }
+        const double ms = ms_since(t0, std::chrono::steady_clock::now());
+        ann_lat_ms.push_back(ms);
+        total_lat_ms.push_back(ms);
+        for (int j = 0; j < k; ++j) pred_il[qi * k + j] = refine_il ? one[j] : I[j];
+      }
+    }
+    // ---- stage A: ANN only, one query per call
+    for (uint64_t qi = 0; qi < Q && !interleaved; ++qi) {
       const auto t0 = std::chrono::steady_clock::now();
       if (nvdb_b200_ivfpq_search(ivf, query.vector_ptr_f32(qi), 1, (uint32_t)nprobe, (uint32_t)k_search, I.data(), nullptr) !=
           NVDB_B200_OK) {
@@ -179,7 +264,9 @@ int main(int argc, char** argv) {
     nvdb_b200_timing t{};
     std::vector<uint32_t> pred((size_t)Q * k, 0xFFFFFFFFu);
     const bool refine = !ann_only && refine_k > 0;
-    if (refine) {
+    if (interleaved) {
+      pred = pred_il;
+    } else if (refine) {
       std::vector<uint32_t> out_ids;
       std::vector<float> out_dist;
       if (getenv_int("CUDA_REFINE_WARMUP", 1) != 0)
@@ -192,11 +279,13 @@ int main(int argc, char** argv) {
       pred = out_ids;
       std::cout << "CUDA_REFINE=1 refine_ms_total=" << refine_ms_total << " refine_ms_per_q=" << refine_ms_per_q
                 << " | h2d_ms=" << t.h2d_ms << " kernel_ms=" << t.kernel_ms << " d2h_ms=" << t.d2h_ms << "\n";
+      write_dbg_tsv_if_enabled(t, k, Q, (uint32_t)k_search, nprobe, refine_k);
     } else {
       for (uint64_t qi = 0; qi < Q; ++qi)
         for (int j = 0; j < k; ++j) pred[qi * k + j] = I_all[qi * k_search + j];
     }
-    for (double a : ann_lat_ms) total_lat_ms.push_back(a + (refine ? refine_ms_per_q : 0.0));
+    if (!interleaved)
+      for (double a : ann_lat_ms) total_lat_ms.push_back(a + (refine ? refine_ms_per_q : 0.0));
 
     double recall_sum = 0;
     if (!ann_only)
@@ -230,7 +319,8 @@ int main(int argc, char** argv) {
     std::cout << "TOTAL p99:   " << totalS.p99_ms << " ms\n";
     std::cout.setf(std::ios::fixed);
     std::cout << std::setprecision(6) << "RESULT"
-              << " refine_k=" << refine_k << " k_search=" << k_search << " nprobe=" << nprobe << " Q=" << Q << " k=" << k
+              << " pipeline=" << pipeline << " exact_metric=" << exact_metric << " refine_k=" << refine_k << " k_search=" << k_search
+              << " nprobe=" << nprobe << " Q=" << Q << " k=" << k
               << " cuda_refine=" << (refine ? 1 : 0) << " refine_enabled=" << (refine ? 1 : 0)
               << " refine_backend=" << (refine ? "cuda" : "none") << " recall=" << (ann_only || !Q ? 0.0 : recall_sum / (double)Q)
               << " ann_avg_ms=" << annS.avg_ms << " ann_p99_ms=" << annS.p99_ms << " total_avg_ms=" << totalS.avg_ms

@@ -50,12 +50,25 @@ for D, R, Q, K in ((768, 256, 10_000, 10), (768, 256, 1_000, 10), (384, 500, 10_
             if rep:
                 ours.append((t.kernel_ms, t.total_ms, (w1 - w0) * 1e3))
                 theirs.append((float(t4[1]), float(t4[3]), (w2 - w1) * 1e3))
+        # the same call with page-locked caller buffers (nvdb_b200_host_register: the CUDA_PINNED=1 analogue): no staging copy
+        for a in (queries, cand):
+            nv.lib.nvdb_b200_host_register(a.ctypes.data, a.nbytes)
+        pinned = []
+        for rep in range(REPS + 1):
+            w0 = time.perf_counter()
+            pids, pdist = idx.refine_l2(queries, cand, K)
+            if rep:
+                pinned.append((time.perf_counter() - w0) * 1e3)
+        for a in (queries, cand):
+            nv.lib.nvdb_b200_host_unregister(a.ctypes.data)
+        assert np.array_equal(pids, ids)
         same = float(np.mean(ids == rids))
         o, r = np.median(np.array(ours), axis=0), np.median(np.array(theirs), axis=0)
         print(json.dumps({
             "shape": f"FP16 {N} x {D}, Q={Q}, R={R}, K={K}", "ids_equal_fraction": same,
             "max_rel_dist_diff": float(np.max(np.abs(dist - rdist) / np.maximum(np.abs(rdist), 1e-6))),
             "ours": {"kernel_ms": float(o[0]), "h2d_kernel_d2h_ms": float(o[1]), "wall_ms": float(o[2]),
+                     "wall_ms_registered_caller_buffers": float(np.median(pinned)),
                      "us_per_query_kernel": float(o[0]) * 1e3 / Q,
                      "gather_GBps": Q * R * D * 2 / (float(o[0]) * 1e-3) / 1e9},
             "reference_cuda_refine_sm100a": {"kernel_ms": float(r[0]), "h2d_kernel_d2h_ms": float(r[1]), "wall_ms": float(r[2]),

@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol(nv):
 
 
 def test_version_and_status_strings(nv):
-    assert nv.lib.nvdb_b200_version() == 100
+    assert nv.lib.nvdb_b200_version() == 101
     assert nv.lib.nvdb_b200_status_string(2) == b"Empty base"
     assert nv.lib.nvdb_b200_status_string(0) == b"ok"
 

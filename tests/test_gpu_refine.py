@@ -1,4 +1,7 @@
 """GPU parity for the refine kernel vs the CPU oracle (double-accumulated L2, reference apps/nvdb_ivf_eval.cpp:232-307)."""
+import ctypes as C
+from pathlib import Path
+
 import numpy as np
 import pytest
 
@@ -93,3 +96,58 @@ def test_refine_matches_compiled_reference_cuda_kernel(nv, oracle, d, R, K):
     assert got == Q * K
     compare(ids, dist, rids, rdist)
     assert np.all(ids[5] == 0xFFFFFFFF) and np.all(rids[5] == 0xFFFFFFFF)
+
+
+@pytest.fixture(scope="module")
+def shim_binary(tmp_path_factory):
+    """tests/cpp/shim_refine_main.cpp: includes host/flat_index_cuda.h and calls nvdb::cuda_l2_topk_batch(...)"""
+    import subprocess
+    root = Path(__file__).resolve().parent.parent
+    out = tmp_path_factory.mktemp("shim") / "shim_refine_main"
+    pkg = root / "nano-vectordb_b200"
+    subprocess.run(["/usr/bin/g++", "-std=c++17", "-O2", f"-I{root / 'include'}", f"-I{pkg / 'host'}", "-o", str(out),
+                    str(root / "tests" / "cpp" / "shim_refine_main.cpp"), f"-L{pkg / 'lib'}", "-lnvdb_b200",
+                    f"-Wl,-rpath,{pkg / 'lib'}", "-lpthread"], check=True, capture_output=True)
+    return out
+
+
+@pytest.mark.parametrize("env", [{}, {"CUDA_RETURN_DIST": "0"}, {"CUDA_PINNED": "1"},
+                                 {"CUDA_DBG_TIMING": "1", "CUDA_DBG_Q": "7", "CUDA_PINNED": "1"}])
+def test_drop_in_symbol_cuda_l2_topk_batch(nv, oracle, shim_binary, tmp_path, env):
+    """The one symbol apps/nvdb_ivf_eval.cpp:542 binds, through a compiled C++ caller with the reference's argument list
+    and environment switches (src/cuda_refine.cu:863-876), against the reference's own kernel on the same GPU."""
+    import os
+    import subprocess
+    lib = _refcuda()
+    n, d, Q, R, K = 20000, 384, 300, 500, 10
+    base, _ = oracle.synth(F16, 17, 0, n, d)
+    rng = np.random.default_rng(4)
+    queries = np.ascontiguousarray(oracle.synth_f32(17, 0, n, d)[rng.integers(0, n, Q)] +
+                                   0.05 * rng.standard_normal((Q, d)).astype(np.float32))
+    cand = rng.integers(0, n, (Q, R)).astype(np.uint32)
+    cand[:, 3] = 0xFFFFFFFF
+    paths = {k: tmp_path / k for k in ("base", "q", "cand", "ids", "dist")}
+    base.tofile(paths["base"])
+    queries.tofile(paths["q"])
+    cand.tofile(paths["cand"])
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([str(shim_binary), str(paths["base"]), str(paths["q"]), str(paths["cand"]), str(n), str(d), str(Q), str(R),
+                        str(K), str(paths["ids"]), str(paths["dist"])], capture_output=True, text=True, env=e, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ids = np.fromfile(paths["ids"], np.uint32).reshape(Q, K)
+    dist = np.fromfile(paths["dist"], np.float32)
+    rid = np.empty((Q, K), np.uint32)
+    rdist = np.empty((Q, K), np.float32)
+    t4 = (C.c_float * 4)()
+    got = lib.refcuda_l2_topk_batch(base.ctypes.data, F16, n, d, queries.ctypes.data, cand.ctypes.data, Q, R, K,
+                                    rid.ctypes.data, rdist.ctypes.data, t4)
+    assert got == Q * K
+    if env.get("CUDA_RETURN_DIST") == "0":
+        assert dist.size == 0                      # ids only: the distance vector is cleared (src/cuda_refine.cu:893-894)
+    else:
+        np.testing.assert_allclose(dist.reshape(Q, K), rdist, rtol=1e-5)
+    assert (ids == rid).mean() > 0.999             # FP32 near-ties aside
+    if "CUDA_DBG_TIMING" in env:
+        assert "dbg_q=7" in r.stdout and "dbg_dist=0.0" not in r.stdout
+    assert "threads=256 nwarps=8 K=10 R=500" in r.stdout

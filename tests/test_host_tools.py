@@ -159,3 +159,27 @@ def test_ivfpq_build_then_eval_reports_recall_and_latencies(tools, oracle, tmp_p
     assert r.returncode == 0 and "| pretransform=OPQ" in r.stdout, r.stderr
     res = dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:])
     assert float(res["recall"]) > 0.8
+    # the reference's protocol knobs (apps/nvdb_ivf_eval.cpp:353,465,664-693): PIPELINE=interleaved answers each query with
+    # ANN + refine in one latency sample and reaches the staged pipeline's recall; EXACT_METRIC picks the ground truth;
+    # CUDA_DBG_TIMING dumps the refine kernel's clock64 phase split as a TSV (apps/nvdb_ivf_eval.cpp:47-126)
+    out, il = evaluate(IVF_NPROBE=16, REFINE_K=50, PIPELINE="interleaved")
+    assert "PIPELINE=interleaved EXACT_METRIC=L2" in out and il["pipeline"] == "interleaved"
+    assert abs(float(il["recall"]) - float(ref50["recall"])) < 1e-9 and float(il["total_avg_ms"]) == float(il["ann_avg_ms"]) > 0
+    recalls = {}
+    for metric in ("L2", "DOT"):
+        r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
+                env={"IVF_NPROBE": "16", "REFINE_K": "50", "EXACT_METRIC": metric})
+        assert r.returncode == 0 and f"EXACT_METRIC={metric}" in r.stdout, r.stderr
+        recalls[metric] = float(dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0]
+                                     .split()[1:])["recall"])
+    assert abs(recalls["L2"] - recalls["DOT"]) < 2e-3          # normalised rows: the two rankings coincide (ties aside)
+    assert run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
+               env={"PIPELINE": "sideways"}).returncode == 6
+    out, _ = evaluate(IVF_NPROBE=16, REFINE_K=50, CUDA_DBG_TIMING=1, CUDA_DBG_Q=16, CUDA_DBG_DIR=str(tmp_path / "dbg"))
+    assert "DBG_TSV=" in out and "dbg_q=16" in out
+    tsv = list((tmp_path / "dbg").glob("dbg_K10_Q200_R50_th256_mode=b200_*.tsv"))
+    assert len(tsv) == 1
+    head, row = tsv[0].read_text().strip().split("\n")
+    cols = dict(zip(head.split("\t"), row.split("\t")))
+    assert cols["dbg_q"] == "16" and float(cols["dbg_dist_cycles_avg"]) > 0 and float(cols["dbg_merge_cycles_avg"]) > 0
+    assert abs(float(cols["dbg_dist_pct"]) + float(cols["dbg_write_pct"]) + float(cols["dbg_merge_pct"]) - 1.0) < 1e-3
