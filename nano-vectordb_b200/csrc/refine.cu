@@ -8,7 +8,8 @@
 //   * the query lives in shared memory; per-lane partial sums use 4 independent chains, then a fixed
 //     shuffle tree — deterministic, and closer to the double-precision CPU refine
 //     (apps/nvdb_ivf_eval.cpp:232-240) than the reference kernel's 4 x 192-long chains;
-//   * selection = rank counting over the R (distance, id) keys in shared memory (R <= 512; a block bitonic sort above):
+//   * selection = warp-local register sorts of 32-key chunks, then rank counting over each chunk's best K (K <= 32; a
+//     block bitonic sort of all R keys above that):
 //     K smallest written in ascending order (ties: id ascending). No serial merge.
 // Semantics kept: ids >= N (incl. 0xFFFFFFFF) are skipped; unfilled output slots are 0xFFFFFFFF / 1e30f
 // (src/cuda_refine.cu:435-437, 891-894).
@@ -63,10 +64,11 @@ __device__ __forceinline__ void l2_piece(const uint4 v, const float* __restrict_
 
 // LPR lanes share a candidate row (8, 16 or 32: the host picks the one that keeps every lane busy for the row length:
 // a 768-byte row is 48 pieces = 16 lanes x 3, a 1536-byte row 32 lanes x 3, a 128-byte row 8 lanes x 1), and every group
-// keeps kRowsInFlight rows in flight, so the bytes a CTA has outstanding do not depend on the shape.
-constexpr int kRowsInFlight = 4;
-
-template <int DT, int LPR>
+// keeps 2 or 4 rows in flight, so the bytes a CTA has outstanding depend little on the shape.
+// Loads in flight per thread = rows in flight (U) x pieces per lane (unrolled up to 4): U = 2 for long rows (3+ pieces per
+// lane), 4 for short ones — enough to cover the HBM latency at 5-6 resident CTAs per SM without the register count
+// cutting the occupancy (4 rows x 3 pieces measured 0.73 of the copy peak at D = 768, 2 x 3 0.89).
+template <int DT, int LPR, int kRowsInFlight, int PPL>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ scales, uint64_t n, uint32_t dim,
                  const float* __restrict__ queries, const uint32_t* __restrict__ cand, uint32_t R, uint32_t K,
@@ -95,7 +97,10 @@ refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ sca
   if (sample) tq1 = clock64();
 
   const uint32_t* cq = cand + (size_t)q * R;
-  for (uint32_t r0 = grp * kRowsInFlight; r0 < R; r0 += kGroups * kRowsInFlight) {
+  // the loop bound is the same for every thread (rows past R are skipped inside): the lane groups of one warp must
+  // reach the full-mask shuffles below together
+  for (uint32_t rb = 0; rb < R; rb += kGroups * kRowsInFlight) {
+    const uint32_t r0 = rb + grp * kRowsInFlight;
     uint32_t id[kRowsInFlight];
     bool ok[kRowsInFlight];
     const uint8_t* row[kRowsInFlight];
@@ -110,12 +115,28 @@ refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ sca
 #pragma unroll
       for (int a4 = 0; a4 < 4; ++a4) acc[u][a4] = 0.f;
     }
-    for (uint32_t c = gl; c < npieces; c += LPR) {
-      uint4 v[kRowsInFlight];
+    if constexpr (PPL > 0) {
+      // exactly PPL pieces per lane (npieces == PPL * LPR): every load of the kRowsInFlight rows is issued before the
+      // first use — PPL * kRowsInFlight 16-byte loads in flight per thread
+      uint4 v[PPL][kRowsInFlight];
 #pragma unroll
-      for (int u = 0; u < kRowsInFlight; ++u) v[u] = ok[u] ? ldg128_stream(row[u] + (size_t)c * 16) : make_uint4(0, 0, 0, 0);
+      for (int i = 0; i < PPL; ++i)
 #pragma unroll
-      for (int u = 0; u < kRowsInFlight; ++u) l2_piece<DT>(v[u], sq + c * P16, sc[u], acc[u]);
+        for (int u = 0; u < kRowsInFlight; ++u)
+          v[i][u] = ok[u] ? ldg128_stream(row[u] + (size_t)(gl + i * LPR) * 16) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int i = 0; i < PPL; ++i)
+#pragma unroll
+        for (int u = 0; u < kRowsInFlight; ++u) l2_piece<DT>(v[i][u], sq + (gl + i * LPR) * P16, sc[u], acc[u]);
+    } else {
+#pragma unroll 2
+      for (uint32_t c = gl; c < npieces; c += LPR) {
+        uint4 v[kRowsInFlight];
+#pragma unroll
+        for (int u = 0; u < kRowsInFlight; ++u) v[u] = ok[u] ? ldg128_stream(row[u] + (size_t)c * 16) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < kRowsInFlight; ++u) l2_piece<DT>(v[u], sq + c * P16, sc[u], acc[u]);
+      }
     }
 #pragma unroll
     for (int u = 0; u < kRowsInFlight; ++u) {
@@ -132,22 +153,45 @@ refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ sca
     dbg[(size_t)q * 3 + 0] = (unsigned long long)(tq1 - tq0);
     dbg[(size_t)q * 3 + 1] = (unsigned long long)(tq2 - tq1);
   }
-  if (sortn <= 512u) {
-    // selection by rank counting (keys are unique per (distance, id); duplicates of one id get consecutive ranks by
-    // position): a thread's key goes to output slot `rank` when rank < K. R^2 / 256 broadcast compares per thread and
-    // no barrier, against the 36+ barrier-separated stages of a full sort of 256 keys.
+  if (K <= 32u) {
+    // Selection in two barrier-light steps instead of a full block sort (36+ barrier-separated stages for 256 keys):
+    //   1. every warp sorts chunks of 32 keys in registers (bitonic over shuffles) and leaves each chunk's best
+    //      min(K, 32) at the front of the chunk — the final K best are among them;
+    //   2. those few keys are ranked by counting (keys are unique per (distance, id); equal keys — the same id listed
+    //      twice — take consecutive ranks by position) and a key of rank < K goes straight to its output slot.
+    const uint32_t lane = tid & 31u, warp = tid >> 5;
+    const uint32_t nchunks = (R + 31u) >> 5;
+    for (uint32_t ch = warp; ch < nchunks; ch += kRefineThreads / 32) {
+      const uint32_t pos = ch * 32u + lane;
+      uint64_t key = pos < R ? skeys[pos] : 0ull;
+#pragma unroll
+      for (uint32_t size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+          const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)key, stride);
+          const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(key >> 32), stride);
+          const uint64_t o = ((uint64_t)hi << 32) | lo;
+          const bool lower = (lane & stride) == 0, desc = (lane & size) == 0 || size == 32;
+          key = (lower == desc) ? (key > o ? key : o) : (key < o ? key : o);
+        }
+      }
+      skeys[pos] = key;   // sortn >= 32 * nchunks (the host rounds it up to a power of two >= 32)
+    }
     for (uint32_t j = tid; j < K; j += kRefineThreads) {
       out_ids[(size_t)q * K + j] = 0xFFFFFFFFu;
       if (out_dist) out_dist[(size_t)q * K + j] = 1e30f;
     }
     __syncthreads();
-    for (uint32_t i = tid; i < R; i += kRefineThreads) {
-      const uint64_t mine = skeys[i];
+    const uint32_t ncand = nchunks * K;
+    for (uint32_t i = tid; i < ncand; i += kRefineThreads) {
+      const uint32_t pi = (i / K) * 32u + (i % K);
+      const uint64_t mine = skeys[pi];
       if (mine == 0ull) continue;
       uint32_t rank = 0;
-      for (uint32_t m = 0; m < R; ++m) {
-        const uint64_t o = skeys[m];
-        rank += (o > mine || (o == mine && m < i)) ? 1u : 0u;
+      for (uint32_t m = 0; m < ncand; ++m) {
+        const uint32_t pm = (m / K) * 32u + (m % K);
+        const uint64_t o = skeys[pm];
+        rank += (o > mine || (o == mine && pm < pi)) ? 1u : 0u;
       }
       if (rank < K) {
         const uint64_t key = ~mine;
@@ -180,7 +224,7 @@ cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, u
                              uint32_t* out_ids, float* out_dist, cudaStream_t stream, unsigned long long* dbg,
                              uint32_t dbg_q, uint32_t* smem_bytes_out) {
   if (Q == 0 || K == 0) return cudaSuccess;
-  const uint32_t sortn = next_pow2(R < 2 ? 2 : R);
+  const uint32_t sortn = next_pow2(R < 32 ? 32 : R);
   const size_t smem = (size_t)sortn * 8u + (size_t)dim * 4u;
   if (smem > 220u * 1024u) return cudaErrorInvalidValue;
   if (smem_bytes_out) *smem_bytes_out = (uint32_t)smem;
@@ -198,13 +242,29 @@ cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, u
   const uint32_t es = dtype == kDtF32 ? 4u : dtype == kDtF16 ? 2u : 1u;
   const uint32_t npieces = (uint32_t)(((size_t)dim * es) >> 4);
   const int lpr = (npieces % 32u == 0u) ? 32 : (npieces % 16u == 0u) ? 16 : (npieces % 8u == 0u || npieces < 16u) ? 8 : (npieces < 48u ? 16 : 32);
-  auto pick = [&](auto k32, auto k16, auto k8) -> cudaError_t { return lpr == 32 ? go(k32) : lpr == 16 ? go(k16) : go(k8); };
+  // pieces per lane: exactly 3 (768-byte rows on 16 lanes, 1536-byte rows on 32: the shapes of the reference's tables
+  // and of BASELINE.json) gets the fully unrolled form; otherwise a loop, 2 rows in flight for long rows and 4 for short
+  const uint32_t ppl = npieces / (uint32_t)lpr;
+  const int variant = (npieces == 3u * (uint32_t)lpr) ? 0 : (ppl >= 3u ? 1 : 2);
+#define NVDB_REFINE_PICK(DT)                                                                                         \
+  switch (variant * 100 + lpr) {                                                                                     \
+    case 32: return go(refine_l2_kernel<DT, 32, 2, 3>);                                                              \
+    case 16: return go(refine_l2_kernel<DT, 16, 2, 3>);                                                              \
+    case 8: return go(refine_l2_kernel<DT, 8, 2, 3>);                                                                \
+    case 132: return go(refine_l2_kernel<DT, 32, 2, 0>);                                                             \
+    case 116: return go(refine_l2_kernel<DT, 16, 2, 0>);                                                             \
+    case 108: return go(refine_l2_kernel<DT, 8, 2, 0>);                                                              \
+    case 232: return go(refine_l2_kernel<DT, 32, 4, 0>);                                                             \
+    case 216: return go(refine_l2_kernel<DT, 16, 4, 0>);                                                             \
+    default: return go(refine_l2_kernel<DT, 8, 4, 0>);                                                               \
+  }
   switch (dtype) {
-    case kDtF32: return pick(refine_l2_kernel<kDtF32, 32>, refine_l2_kernel<kDtF32, 16>, refine_l2_kernel<kDtF32, 8>);
-    case kDtF16: return pick(refine_l2_kernel<kDtF16, 32>, refine_l2_kernel<kDtF16, 16>, refine_l2_kernel<kDtF16, 8>);
-    case kDtI8: return pick(refine_l2_kernel<kDtI8, 32>, refine_l2_kernel<kDtI8, 16>, refine_l2_kernel<kDtI8, 8>);
+    case kDtF32: NVDB_REFINE_PICK(kDtF32)
+    case kDtF16: NVDB_REFINE_PICK(kDtF16)
+    case kDtI8: NVDB_REFINE_PICK(kDtI8)
     default: return cudaErrorInvalidValue;
   }
+#undef NVDB_REFINE_PICK
 }
 
 }  // namespace nvdb_b200

@@ -40,7 +40,10 @@ for D, R, Q, K in ((768, 256, 10_000, 10), (768, 256, 1_000, 10), (384, 500, 10_
         rdist = np.empty((Q, K), np.float32)
         t4 = np.zeros(4, np.float32)
         for rep in range(REPS + 1):              # first round warms both (the reference uploads its base copy once)
+            os.environ["CUDA_DBG_TIMING"] = "1"              # in-kernel phase sampling of the first 32 queries
             idx.refine_l2(queries, cand, K, timing=t)      # one chunk, four events: H2D / kernel / D2H
+            os.environ.pop("CUDA_DBG_TIMING")
+            phases = (t.dbg_write_cycles_avg, t.dbg_dist_cycles_avg, t.dbg_merge_cycles_avg)
             w0 = time.perf_counter()
             ids, dist = idx.refine_l2(queries, cand, K)     # the call a user makes: chunks pipelined through staging
             w1 = time.perf_counter()
@@ -69,6 +72,7 @@ for D, R, Q, K in ((768, 256, 10_000, 10), (768, 256, 1_000, 10), (384, 500, 10_
             "max_rel_dist_diff": float(np.max(np.abs(dist - rdist) / np.maximum(np.abs(rdist), 1e-6))),
             "ours": {"kernel_ms": float(o[0]), "h2d_kernel_d2h_ms": float(o[1]), "wall_ms": float(o[2]),
                      "wall_ms_registered_caller_buffers": float(np.median(pinned)),
+                     "phase_cycles_query_dist_select": [float(x) for x in phases],
                      "us_per_query_kernel": float(o[0]) * 1e3 / Q,
                      "gather_GBps": Q * R * D * 2 / (float(o[0]) * 1e-3) / 1e9},
             "reference_cuda_refine_sm100a": {"kernel_ms": float(r[0]), "h2d_kernel_d2h_ms": float(r[1]), "wall_ms": float(r[2]),
