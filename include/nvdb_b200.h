@@ -100,6 +100,10 @@ int nvdb_b200_index_create_synthetic(uint32_t dtype, uint64_t n, uint32_t dim, u
 int nvdb_b200_index_destroy(nvdb_b200_index* idx);
 int nvdb_b200_index_info(const nvdb_b200_index* idx, uint64_t* n, uint32_t* dim, uint32_t* dtype, int* device,
                          uint64_t* row_offset, const void** payload_dev, const float** scales_dev);
+/* Loader fast path: wall time and bytes of the host -> device upload done by nvdb_b200_index_create
+ * (chunked, multi-threaded staging into two pinned buffers overlapping the DMA; the reference does one synchronous
+ * pageable cudaMemcpy of the whole base, src/cuda_refine.cu:179-204). 0 / 0 for device-resident and synthetic indexes. */
+int nvdb_b200_index_upload_info(const nvdb_b200_index* idx, double* seconds, uint64_t* bytes);
 int nvdb_b200_index_set_path(nvdb_b200_index* idx, int path);
 /* Copy rows [row0,row0+nrows) of the device-resident payload (and scales) back to the host. */
 int nvdb_b200_index_read_rows(const nvdb_b200_index* idx, uint64_t row0, uint64_t nrows, void* payload_host,

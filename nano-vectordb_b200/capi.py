@@ -51,6 +51,7 @@ _sig = {
     "nvdb_b200_index_destroy": (_i, [_vp]),
     "nvdb_b200_index_info": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_i),
                                   C.POINTER(_u64), C.POINTER(_vp), C.POINTER(_vp)]),
+    "nvdb_b200_index_upload_info": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(_u64)]),
     "nvdb_b200_index_set_path": (_i, [_vp, _i]),
     "nvdb_b200_index_read_rows": (_i, [_vp, _u64, _u64, _vp, _vp]),
     "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
@@ -259,6 +260,12 @@ class FlatIndexCuda:
 
     def __exit__(self, *a):
         self.close()
+
+    def upload_info(self):
+        """(seconds, bytes) of the host -> device upload done at creation (0, 0 for device-resident / synthetic bases)"""
+        sec, nb = C.c_double(), _u64()
+        _check(lib.nvdb_b200_index_upload_info(self._h, C.byref(sec), C.byref(nb)), self._h)
+        return sec.value, nb.value
 
     def set_path(self, path):
         _check(lib.nvdb_b200_index_set_path(self._h, path), self._h)

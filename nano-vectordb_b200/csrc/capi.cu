@@ -2,6 +2,7 @@
 // No CPU compute path lives here: every result is produced by the kernels in this directory.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cmath>
 #include <cstring>
@@ -45,6 +46,8 @@ struct nvdb_b200_index {
   // sharing one device would dead-lock behind a spinning peer kernel
   bool guard_no_alloc = false, in_exchange = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  double upload_s = 0;         // host -> device time of the base (index_create), and the bytes moved
+  uint64_t upload_bytes = 0;
   bool tma_ok = false;
   CUtensorMap tmap;
   // tensor-core scan: base tensor map with box rows = scan_mma_block_n(dtype); query (A operand) tensor map cache
@@ -112,11 +115,11 @@ int fail_cuda(const nvdb_b200_index* idx, cudaError_t e, const char* what) {
 
 // Staging copies into pinned memory: one core moves ~10 GB/s, which is slower than the H2D copy that follows; large
 // blocks are split over a few short-lived threads (>= 2 MB per thread).
-void par_memcpy(void* dst, const void* src, size_t bytes) {
+void par_memcpy(void* dst, const void* src, size_t bytes, size_t max_threads = 6) {
   const size_t per_thread = (size_t)2 << 20;
   unsigned hw = std::thread::hardware_concurrency();
   size_t T = bytes / per_thread;
-  if (T > 6) T = 6;
+  if (T > max_threads) T = max_threads;
   if (hw && T > hw) T = hw;
   if (T <= 1) {
     std::memcpy(dst, src, bytes);
@@ -352,6 +355,7 @@ static int alloc_base(nvdb_b200_index* idx) {
 // cudaMemcpy of the whole base (src/cuda_refine.cu:198).
 static int upload(nvdb_b200_index* idx, void* dst, const void* src, size_t bytes) {
   const size_t chunk = (size_t)64 << 20;
+  const auto t0 = std::chrono::steady_clock::now();
   int rc;
   if ((rc = ensure_pin(idx, 0, bytes < chunk ? bytes : chunk))) return rc;
   if (bytes > chunk && (rc = ensure_pin(idx, 1, chunk))) return rc;
@@ -362,7 +366,9 @@ static int upload(nvdb_b200_index* idx, void* dst, const void* src, size_t bytes
   while (off < bytes) {
     const size_t take = bytes - off < chunk ? bytes - off : chunk;
     if (used[b]) CK(cudaEventSynchronize(done[b]), "upload event sync");
-    std::memcpy(idx->h_pin[b], (const char*)src + off, take);
+    // the staging copy (page faults of a cold mmap included) is the slow side: one core moves ~10 GB/s, the copy engine
+    // ~50 GB/s, so each chunk is split over up to 16 threads
+    par_memcpy(idx->h_pin[b], (const char*)src + off, take, 16);
     CK(cudaMemcpyAsync((char*)dst + off, idx->h_pin[b], take, cudaMemcpyHostToDevice, idx->stream), "H2D base chunk");
     CK(cudaEventRecord(done[b], idx->stream), "upload event record");
     used[b] = true;
@@ -370,6 +376,8 @@ static int upload(nvdb_b200_index* idx, void* dst, const void* src, size_t bytes
     b ^= 1;
   }
   CK(cudaStreamSynchronize(idx->stream), "upload sync");
+  idx->upload_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  idx->upload_bytes += bytes;
   return NVDB_B200_OK;
 }
 
@@ -553,6 +561,13 @@ int nvdb_b200_index_info(const nvdb_b200_index* idx, uint64_t* n, uint32_t* dim,
   if (row_offset) *row_offset = idx->row_offset;
   if (payload_dev) *payload_dev = idx->payload;
   if (scales_dev) *scales_dev = idx->scales;
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_index_upload_info(const nvdb_b200_index* idx, double* seconds, uint64_t* bytes) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (seconds) *seconds = idx->upload_s;
+  if (bytes) *bytes = idx->upload_bytes;
   return NVDB_B200_OK;
 }
 
@@ -1418,8 +1433,13 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   if ((rc = ensure_pin(idx, 1, ibytes + sbytes))) return rc;
   cudaStream_t s = idx->stream;
   if ((rc = adopt_stream(idx, s))) return rc;
-  uint64_t* d_ids = (uint64_t*)idx->d_ws[WS_OUT_IDS];
-  float* d_scores = (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
+  // Small results (a handful of queries) are written by the kernels straight into the pinned host buffer, which the
+  // device addresses directly (unified addressing): no device-to-host copy is enqueued, the stream synchronisation
+  // below makes the stores visible. Larger results go through device memory and one copy.
+  char* hp = (char*)idx->h_pin[1];
+  const bool direct_out = ibytes + sbytes <= 4096u;
+  uint64_t* d_ids = direct_out ? (uint64_t*)hp : (uint64_t*)idx->d_ws[WS_OUT_IDS];
+  float* d_scores = direct_out ? (float*)(hp + ibytes) : (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
   par_memcpy(idx->h_pin[0], queries_host, qbytes);
   if (timing) CK(cudaEventRecord(idx->ev[0], s), "event");
   CK(cudaMemcpyAsync(idx->d_ws[WS_QUERIES], idx->h_pin[0], qbytes, cudaMemcpyHostToDevice, s), "H2D queries");
@@ -1430,8 +1450,7 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
                           &deferred);
   if (rc) return rc;
   if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
-  char* hp = (char*)idx->h_pin[1];
-  CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
+  if (!direct_out) CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
   if (timing) CK(cudaEventRecord(idx->ev[3], s), "event");
   CK(cudaStreamSynchronize(s), "search sync");
   if (deferred) {  // exact tensor-core path: the certificate verdict arrived with the results
@@ -1440,7 +1459,7 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
     if (rc) return rc;
     if (nfall) {  // flagged queries were re-run on the streaming scan: fetch the corrected results
       if (timing) CK(cudaEventRecord(idx->ev[2], s), "event");
-      CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
+      if (!direct_out) CK(cudaMemcpyAsync(hp, d_ids, ibytes + sbytes, cudaMemcpyDeviceToHost, s), "D2H results");
       if (timing) CK(cudaEventRecord(idx->ev[3], s), "event");
       CK(cudaStreamSynchronize(s), "search sync");
     }

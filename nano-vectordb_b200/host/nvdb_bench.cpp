@@ -257,7 +257,8 @@ int main(int argc, char** argv) {
     std::cout << "payload_equiv_bandwidth_GBps=" << (avg_query > 0 ? bytes_per_query * 1e-6 / avg_query : 0.0) << "\n";
     if (batch_q > 1) std::cout << "(note) payload_equiv_bandwidth_GBps may exceed DRAM peak due to cache reuse\n";
     std::cout << "batch_q=" << batch_q << " path=" << path_s << " path_used=" << path_used << " shards=" << index.shards() << "\n";
-    std::cout << "kernel_ms_avg=" << kernel_ms_sum / (double)lat_ms.size() << " upload_ms=" << upload_ms << "\n";
+    std::cout << "kernel_ms_avg=" << kernel_ms_sum / (double)lat_ms.size() << " upload_ms=" << upload_ms
+              << " upload_GBps=" << (double)nvdb::bytes_for_payload_and_aux(base.count(), base.dim(), base.dtype()) * 1e-6 / upload_ms << "\n";
 
     if (const char* gt = std::getenv("GT_PATH")) {
       uint32_t gk = 0;
