@@ -499,7 +499,8 @@ ivfpq_merge_kernel(const uint64_t* __restrict__ partial, uint32_t total, uint32_
     const ulonglong2 o = mk2[i];
 #pragma unroll
     for (int u = 0; u < 2; ++u) rank[u] += (o.x > key[u] ? 1u : 0u) + (o.y > key[u] ? 1u : 0u);
-    if (key[0] == 0ull) break;  // (key[1] is then empty too: slots fill from the front) nothing to rank
+    if ((key[0] | key[1]) == 0ull) break;  // nothing to rank (a group's list is zero-padded at ITS end, so key[1] may be
+                                           // real while key[0] is padding)
   }
 #pragma unroll
   for (int u = 0; u < 2; ++u)

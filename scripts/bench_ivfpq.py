@@ -11,7 +11,8 @@ numbers therefore describe THIS data, only their shape (monotone in nprobe, thre
 comparable with the reference's table.
 
   NVDB_IVF_ROWS (1,000,000)  NVDB_IVF_DIM (768)  NVDB_IVF_NLIST (4096)  NVDB_IVF_M (64)  NVDB_IVF_TRAIN (200000)
-  NVDB_IVF_NITER (25)  NVDB_IVF_Q (1000)  NVDB_IVF_LATENT (24)  NVDB_IVF_OPQ (0)
+  NVDB_IVF_NITER (25)  NVDB_IVF_Q (1000)  NVDB_IVF_LATENT (24)  NVDB_IVF_OPQ (0)  NVDB_IVF_DATA (manifold | clustered)
+  NVDB_IVF_CLUSTERS (2048)  NVDB_IVF_REFINE (0,20,50,256)
 """
 import importlib
 import json
@@ -44,11 +45,25 @@ g.manual_seed(20240229)
 # low intrinsic dimension (like text embeddings, unlike isotropic noise): points = normalize(z W + small noise), z in R^LAT
 LAT = int(os.environ.get("NVDB_IVF_LATENT", 24))
 W = torch.randn(LAT, D, device=dev, generator=g)
+DATA = os.environ.get("NVDB_IVF_DATA", "manifold")
 base = torch.empty(N, D, device=dev, dtype=torch.float16)
+if DATA == "clustered":
+    # the shape of the reference's data (L2-normalised 384-d text embeddings, Performance.md:15): topical clusters whose
+    # centres lie on a low-dimensional manifold, members spread along a few local directions plus isotropic noise
+    NC = int(os.environ.get("NVDB_IVF_CLUSTERS", 2048))
+    SPREAD = float(os.environ.get("NVDB_IVF_SPREAD", 0.9))   # in-cluster spread along the local directions (centres: norm 1)
+    NOISE = float(os.environ.get("NVDB_IVF_NOISE", 0.5))     # isotropic part
+    centres = torch.nn.functional.normalize(torch.randn(NC, LAT, device=dev, generator=g) @ W, dim=1)
+    W2 = torch.randn(LAT, D, device=dev, generator=g)
 for r0 in range(0, N, 100_000):
     r1 = min(N, r0 + 100_000)
     z = torch.randn(r1 - r0, LAT, device=dev, generator=g)
-    x = z @ W + 0.3 * torch.randn(r1 - r0, D, device=dev, generator=g)
+    if DATA == "clustered":
+        owner = torch.randint(0, NC, (r1 - r0,), device=dev, generator=g)
+        x = centres[owner] + SPREAD * torch.nn.functional.normalize(z @ W2, dim=1) + \
+            (NOISE / D ** 0.5) * torch.randn(r1 - r0, D, device=dev, generator=g)
+    else:
+        x = z @ W + 0.3 * torch.randn(r1 - r0, D, device=dev, generator=g)
     base[r0:r1] = torch.nn.functional.normalize(x, dim=1).half()
 qrows = torch.randint(0, N, (Q,), device=dev, generator=g)
 queries = torch.nn.functional.normalize(base[qrows].float() + 0.03 * torch.randn(Q, D, device=dev, generator=g), dim=1)
@@ -72,7 +87,7 @@ idx = nv.FlatIndexCuda.from_device(base.data_ptr(), None, nv.F16, N, D, keepaliv
 t0 = time.perf_counter()
 ivf = nv.IvfPqIndex(idx, nlist=NLIST, pq_m=M, ntrain=NTRAIN, niter=NITER, seed=1234, opq_niter=OPQ)
 build_s = time.perf_counter() - t0
-print(json.dumps({"what": "build", "rows": N, "dim": D, "nlist": NLIST, "pq_m": M, "ntrain": NTRAIN, "niter": NITER, "opq_niter": OPQ,
+print(json.dumps({"what": "build", "rows": N, "dim": D, "nlist": NLIST, "pq_m": M, "ntrain": NTRAIN, "niter": NITER, "opq_niter": OPQ, "data": DATA,
                   "build_s": round(build_s, 2), "index_MB": round(ivf.index_bytes / 1e6, 1),
                   "base_MB": round(N * D * 2 / 1e6, 1)}), flush=True)
 
@@ -87,7 +102,7 @@ def pct(v, p):
 
 
 for nprobe in (8, 16, 32, 64, 128):
-    for R in (0, 20, 50, 256):
+    for R in tuple(int(x) for x in os.environ.get("NVDB_IVF_REFINE", "0,20,50,256").split(",")):
         lat = []
         found = np.empty((Q, K), np.uint32)
         for w in range(5):  # warm-up (workspaces)

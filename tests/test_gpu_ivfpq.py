@@ -107,7 +107,9 @@ def test_training_is_deterministic_and_as_good_as_lloyd(nv):
     assert np.allclose(c1, w1, rtol=1e-4, atol=1e-5)
 
 
-@pytest.mark.parametrize("M,nprobe,R", [(8, 1, 10), (8, 8, 50), (16, 64, 256), (12, 5, 1000)])
+# (8, 8, 100) / (16, 8, 128): a single query's 8 probe groups x R keys = 800 / 1024 keys in the rank-counting merge, with
+# groups that hold fewer than R candidates (zero padding in the middle of the key array)
+@pytest.mark.parametrize("M,nprobe,R", [(8, 1, 10), (8, 8, 50), (8, 8, 100), (16, 8, 128), (16, 64, 256), (12, 5, 1000)])
 def test_search_matches_oracle_adc(nv, M, nprobe, R):
     n, d, nlist = 30_000, 48, 64
     x = clustered(n, d, 60, 4)
