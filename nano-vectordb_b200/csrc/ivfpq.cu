@@ -370,7 +370,7 @@ struct RankTopR {
 // The table T (ivfpq_lut_kernel) is copied into shared memory once and serves all the lists of the group
 // (p = g, g + G, ...); |y|^2 is stored per vector at build time, q.c is one block reduction per list.
 // (A table of squared residual sub-distances would have to be rebuilt for every probed list: measured 14 ms for
-// 1000 queries x 64 probes, profiles/r1_ivfpq_1M_v1.jsonl.)
+// 1000 queries x 64 probes, profiles/r1_ivfpq_1M_v3.jsonl.)
 __global__ void __launch_bounds__(kScanThreads) ivfpq_scan_kernel(const IvfScanArgs a) {
   extern __shared__ __align__(16) uint8_t sm[];
   float* lut = reinterpret_cast<float*>(sm);                    // [M x 256]
