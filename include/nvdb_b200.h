@@ -51,7 +51,7 @@ enum {
   NVDB_B200_PATH_MMA_EXACT = 4 /* tensor-core candidate scan (f16: one limb, i8: two limbs) keeping k' > k rows per
                                   query, exact FP32 re-score of the candidates in the reference's summation order, and a
                                   per-query error-bound certificate; queries that fail it are re-run on PATH_GEMV. Ids and
-                                  scores are bit-identical to PATH_GEMV. AUTO uses this for batches of >= 3 queries.
+                                  scores are bit-identical to PATH_GEMV. AUTO uses this for batches of >= 2 queries (k <= 12; >= 3 otherwise).
                                   Synchronises the stream once per call. */
 };
 
@@ -118,7 +118,7 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
 /* Same, all buffers in device memory, asynchronous on `stream` (a cudaStream_t; NULL = the index's stream).
  * One search of an index is in flight at a time: its workspaces are per index, so a call that arrives on another stream
  * than the previous one is ordered behind it with an event, never overlapped. NVDB_B200_PATH_MMA_EXACT (what AUTO picks
- * for >= 3 queries) synchronises `stream` once per call (the certificate verdict comes back to the host). */
+ * for batches) synchronises `stream` once per call (the certificate verdict comes back to the host). */
 int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
                             uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
 /* Merge `nlists` per-shard results (each [nq][k], laid out list-major: [nlists][nq][k]) into one [nq][k]

@@ -67,6 +67,12 @@ struct nvdb_b200_index {
   float max_l2 = 0.f, max_l1 = 0.f;
   uint32_t rows_launches = 0;          // launches of the row-tile kernel that used the seeding workspace (its counter's epoch)
   const void* rows_seed_seen = nullptr;  // WS_ROWS_SEED allocation whose counter has been zeroed
+  // adaptive first tier: running rate of first-certificate failures (per k); when most queries of large batches fail the
+  // narrow lists anyway (clustered bases at k = 100: 61 %), the wide lists are scanned FIRST and the narrow pass is only
+  // probed every 8th call
+  float exact_fail_ewma = 0.f;
+  uint32_t exact_ewma_k = 0, exact_batches = 0;
+  bool exact_wide_first = false;
   uint64_t exact_calls = 0;            // candidate-scan + re-score chains enqueued: parity picks the flag counter slot
   const void* flag_ws_seen = nullptr;  // WS_X_FLAGS allocation whose counter slots have been zeroed
   uint64_t exact_queries = 0, exact_fallbacks = 0;
@@ -1145,7 +1151,16 @@ int mma_exact_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t
   // pinned words: [0] flag count, [4, 4 + nq) flags, then two index lists of up to nq entries (mma_exact_finish)
   if ((rc = ensure_pin(idx, 2, (3 * (size_t)nq + 8) * 4))) return rc;
   if ((rc = reserve_exact_ws(idx, nq, k, stream))) return rc;
-  if ((rc = mma_exact_enqueue(idx, d_queries, nq, k, exact_kprime(k), d_out_ids, d_out_scores, stream, launches))) return rc;
+  if (idx->exact_ewma_k != k) {
+    idx->exact_ewma_k = k;
+    idx->exact_fail_ewma = 0.f;
+    idx->exact_batches = 0;
+  }
+  const uint32_t kp2 = exact_kprime2(idx, k);
+  idx->exact_wide_first = kp2 != 0 && nq >= 64u && idx->exact_fail_ewma > 0.35f && (++idx->exact_batches & 7u) != 0u;
+  if ((rc = mma_exact_enqueue(idx, d_queries, nq, k, idx->exact_wide_first ? kp2 : exact_kprime(k), d_out_ids, d_out_scores,
+                              stream, launches)))
+    return rc;
   if (deferred) {
     *deferred = true;
     return NVDB_B200_OK;
@@ -1165,9 +1180,11 @@ int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   idx->exact_queries += nq;
   idx->exact_fallbacks += nf;
   if (fallbacks) *fallbacks = nf;
+  if (!idx->exact_wide_first && nq >= 64u) idx->exact_fail_ewma = 0.5f * idx->exact_fail_ewma + 0.5f * (float)nf / (float)nq;
   if (nf == 0) return NVDB_B200_OK;
 
-  const uint32_t kp2 = exact_kprime2(idx, k);
+  // the wide lists were scanned first (adaptive first tier): what they could not certify goes to the streaming scan
+  const uint32_t kp2 = idx->exact_wide_first ? 0u : exact_kprime2(idx, k);
   if (nf == nq && !kp2) {
     idx->exact_gemv += nf;
     return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
@@ -1238,8 +1255,13 @@ int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
 constexpr uint32_t kMmaCrossover = 3;
 // From how many queries AUTO leaves the streaming scan: int8 with the row-tile kernel already at 2 (0.38 ms against the
 // streaming scan's 0.50 ms for two queries: 41 instructions per 16 bytes and query make it issue-bound), else 3.
-static uint32_t auto_crossover(const nvdb_b200_index* idx) {
-  return (idx->dtype == kDtI8 && idx->tune_rows) ? 2u : kMmaCrossover;
+static uint32_t auto_crossover(const nvdb_b200_index* idx, uint32_t k, bool exchange) {
+  if (idx->dtype == kDtI8 && idx->tune_rows) return 2u;
+  // f16, two queries, small k: the one-limb query-tile kernel streams the base at 6.9 TB/s, the streaming scan with two
+  // queries per pass at 6.2 (0.692 against 0.726 ms per step, profiles/r2_probe_rows_ab.jsonl). Row-sharded searches keep
+  // the streaming scan there: its last CTA runs the exchange in the same launch.
+  if (idx->dtype == kDtF16 && k <= 12u && !exchange) return 2u;
+  return kMmaCrossover;
 }
 
 int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t k, uint64_t* d_out_ids,
@@ -1247,7 +1269,7 @@ int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq
                        bool* deferred = nullptr) {
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
-    path = (nq >= auto_crossover(idx) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
+    path = (nq >= auto_crossover(idx, k, false) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
   if (path_used) *path_used = (uint32_t)path;
   if (path == NVDB_B200_PATH_GEMV) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
   if (path == NVDB_B200_PATH_MMA_EXACT)
@@ -1283,7 +1305,7 @@ static int search_exchange_impl(nvdb_b200_index* idx, nvdb_b200_exchange* x, con
   if (idx->device != x->device) return fail(idx, NVDB_B200_ERR_ARG, "search_exchange: index and exchange live on different devices");
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
-    path = (nq >= auto_crossover(idx) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
+    path = (nq >= auto_crossover(idx, k, true) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
   uint64_t* l_ids = reinterpret_cast<uint64_t*>(x->staging);
   float* l_scores = reinterpret_cast<float*>(l_ids + nk);
   int rc;

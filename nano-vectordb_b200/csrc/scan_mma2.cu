@@ -17,6 +17,8 @@
 //   empty[s]  count 1, arrived by the leader's tcgen05.commit multicast (slot consumed by the pair's MMA)
 //   tfull[b]  count 1, arrived by the commit multicast (accumulator buffer b complete)
 //   tempty[b] leader only, count 8: the four epilogue warps of both CTAs (the peer's arrive remotely)
+#include <cstdlib>
+
 #include "common.cuh"
 #include "scan.h"
 #include "scan_mma_common.cuh"
@@ -351,7 +353,15 @@ uint32_t scan_mma2_half_n(int dtype) { return dtype == kDtI8 ? PairGeom<kDtI8>::
 
 // ring depth next to the k-entry lists (k <= 16: lists in registers); false when not even 3 stages fit
 bool scan_mma2_plan(int dtype, int limbs, uint32_t k, int max_smem, int* stages) {
-  *stages = mma2_fit_stages(scan_mma2_half_n(dtype), limbs, k, 0, 0u, max_smem, 3);
+  // smallest ring accepted: 2 stages — only reached when 3 do not fit, i.e. by the wide shared-memory lists of the second
+  // certificate tier (150+ entries): the pair kernel with a 2-stage ring still beats the single-CTA kernel there
+  // (clustered base, k = 100, batch 1024: 11.32 -> 10.07 ms). NVDB_B200_PAIR_MIN_STAGES=3 restores the old rule (A/B).
+  static const int min_stages = [] {
+    const char* e = getenv("NVDB_B200_PAIR_MIN_STAGES");
+    const int v = e ? atoi(e) : 2;
+    return v < 2 ? 2 : v;
+  }();
+  *stages = mma2_fit_stages(scan_mma2_half_n(dtype), limbs, k, 0, 0u, max_smem, min_stages);
   return *stages != 0;
 }
 
