@@ -359,29 +359,51 @@ static int alloc_base(nvdb_b200_index* idx) {
 // Upload path: host (typically the mmap of a vecbin file) -> two pinned staging buffers -> cudaMemcpyAsync,
 // the memcpy of chunk i+1 overlapping the DMA of chunk i. The reference does one synchronous pageable
 // cudaMemcpy of the whole base (src/cuda_refine.cu:198).
+// Process-wide staging buffers of the loader: three 64 MB pinned chunks, allocated on the first large upload and kept
+// (page-locking 128 MB cost ~45 ms of a 160 ms upload when every index allocated its own). Uploads serialise on them.
+namespace {
+constexpr size_t kStageChunk = (size_t)64 << 20;
+constexpr int kStageBufs = 3;
+std::mutex g_stage_mu;
+void* g_stage[kStageBufs] = {nullptr, nullptr, nullptr};
+}  // namespace
+
 static int upload(nvdb_b200_index* idx, void* dst, const void* src, size_t bytes) {
-  const size_t chunk = (size_t)64 << 20;
+  const size_t chunk = kStageChunk;
   const auto t0 = std::chrono::steady_clock::now();
   int rc;
-  if ((rc = ensure_pin(idx, 0, bytes < chunk ? bytes : chunk))) return rc;
-  if (bytes > chunk && (rc = ensure_pin(idx, 1, chunk))) return rc;
-  cudaEvent_t done[2] = {idx->ev[0], idx->ev[1]};
-  bool used[2] = {false, false};
-  size_t off = 0;
-  int b = 0;
-  while (off < bytes) {
-    const size_t take = bytes - off < chunk ? bytes - off : chunk;
-    if (used[b]) CK(cudaEventSynchronize(done[b]), "upload event sync");
-    // the staging copy (page faults of a cold mmap included) is the slow side: one core moves ~10 GB/s, the copy engine
-    // ~50 GB/s, so each chunk is split over up to 16 threads
-    par_memcpy(idx->h_pin[b], (const char*)src + off, take, 16);
-    CK(cudaMemcpyAsync((char*)dst + off, idx->h_pin[b], take, cudaMemcpyHostToDevice, idx->stream), "H2D base chunk");
-    CK(cudaEventRecord(done[b], idx->stream), "upload event record");
-    used[b] = true;
-    off += take;
-    b ^= 1;
+  if (bytes <= chunk) {  // small payloads (tests, scales of small bases): the index's own pinned buffer
+    if ((rc = ensure_pin(idx, 0, bytes))) return rc;
+    par_memcpy(idx->h_pin[0], src, bytes, 16);
+    CK(cudaMemcpyAsync(dst, idx->h_pin[0], bytes, cudaMemcpyHostToDevice, idx->stream), "H2D base");
+    CK(cudaStreamSynchronize(idx->stream), "upload sync");
+  } else {
+    std::lock_guard<std::mutex> g(g_stage_mu);
+    for (auto& p : g_stage)
+      if (!p) CK(cudaHostAlloc(&p, chunk, cudaHostAllocPortable), "cudaHostAlloc staging");
+    cudaEvent_t done[kStageBufs];
+    bool used[kStageBufs] = {false, false, false};
+    for (auto& e : done) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "upload event");
+    size_t off = 0;
+    int b = 0;
+    cudaError_t err = cudaSuccess;
+    while (off < bytes && err == cudaSuccess) {
+      const size_t take = bytes - off < chunk ? bytes - off : chunk;
+      if (used[b]) err = cudaEventSynchronize(done[b]);
+      // the staging copy (page faults of a cold mmap included) is the slow side: one core moves ~10 GB/s, the copy
+      // engine ~50 GB/s, so each chunk is split over up to 16 threads; with three buffers two copies can be queued
+      // behind the one in flight
+      par_memcpy(g_stage[b], (const char*)src + off, take, 16);
+      if (err == cudaSuccess) err = cudaMemcpyAsync((char*)dst + off, g_stage[b], take, cudaMemcpyHostToDevice, idx->stream);
+      if (err == cudaSuccess) err = cudaEventRecord(done[b], idx->stream);
+      used[b] = true;
+      off += take;
+      b = (b + 1) % kStageBufs;
+    }
+    if (err == cudaSuccess) err = cudaStreamSynchronize(idx->stream);
+    for (auto& e : done) cudaEventDestroy(e);
+    CK(err, "H2D base chunks");
   }
-  CK(cudaStreamSynchronize(idx->stream), "upload sync");
   idx->upload_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   idx->upload_bytes += bytes;
   return NVDB_B200_OK;
