@@ -141,11 +141,14 @@ def test_ivfpq_build_then_eval_reports_recall_and_latencies(tools, oracle, tmp_p
     _, all_lists = evaluate(IVF_NPROBE=64, REFINE_K=500)
     assert float(ref50["recall"]) > float(raw["recall"]) and float(all_lists["recall"]) > 0.99
     assert float(ref50["total_avg_ms"]) >= float(ref50["ann_avg_ms"]) > 0
-    # without GT_PATH the neighbours come from the exact flat scan: same recall on normalised data
-    r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
-            env={"IVF_NPROBE": "16", "REFINE_K": "50"})
-    res = dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:])
-    assert abs(float(res["recall"]) - float(ref50["recall"])) < 1e-9
+    # without GT_PATH the neighbours come from the exact flat scan. EXACT_METRIC=DOT ranks as nvdb_gt_build does: the same
+    # recall to the digit. The default (L2, the reference's refine metric) ranks by distance: on rows that are unit length
+    # only up to their FP16 rounding the two orders differ on a near-tie here and there (1 neighbour of 2000 on this data)
+    for metric, tol in (("DOT", 1e-9), ("L2", 2.5 / (200 * k))):
+        r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
+                env={"IVF_NPROBE": "16", "REFINE_K": "50", "EXACT_METRIC": metric})
+        res = dict(kv.split("=", 1) for kv in [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:])
+        assert abs(float(res["recall"]) - float(ref50["recall"])) < tol, metric
     r = run(tools / "nvdb_ivf_eval", tmp_path / "base.vecbin", tmp_path / "idx.nvdbivf", tmp_path / "q.raw12", k,
             env={"EVAL_MODE": "ann_only"})
     assert r.returncode == 0 and f"Recall@{k}: N/A (EVAL_MODE=ann_only)" in r.stdout
