@@ -121,6 +121,19 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
  * for batches) synchronises `stream` once per call (the certificate verdict comes back to the host). */
 int nvdb_b200_search_device(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
                             uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
+/* Allocation-free variant of nvdb_b200_search_device. It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). Same arguments, same result (bit for bit: the streaming scan and its merge kernel), but
+ * the scan's scratch - the per-CTA partial lists, nq * lists * k * 8 bytes with lists = 148 or 296 on a B200 - lives in
+ * a file-scope static __device__ array of NVDB_B200_STATIC_SCRATCH_BYTES that every GPU which loads the library holds
+ * until the process exits. The call does no cudaMalloc / cudaFree / allocating library call, never touches the index's
+ * workspaces and always takes the streaming scan (the PATH setting is ignored; meant for 1-8 queries).
+ * A request whose scratch exceeds the maximum returns NVDB_B200_ERR_UNSUPPORTED with the sizes in last_error.
+ * ALL calls in the process on one GPU share the array (whatever the index or stream): calls that overlap on the GPU race.
+ * The array keeps the previous call's contents; every launch rewrites the part it reads, nothing is assumed zero. */
+#define NVDB_B200_STATIC_SCRATCH_BYTES (4u << 20)
+int nvdb_b200_search_device_static(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
+                                   uint64_t* out_ids_dev, float* out_scores_dev, void* stream);
 /* Merge `nlists` per-shard results (each [nq][k], laid out list-major: [nlists][nq][k]) into one [nq][k]
  * under (score desc, id asc). Device buffers; asynchronous on `stream`. This is the step after the all-gather
  * of a row-sharded index. */

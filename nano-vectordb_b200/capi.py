@@ -56,6 +56,7 @@ _sig = {
     "nvdb_b200_index_read_rows": (_i, [_vp, _u64, _u64, _vp, _vp]),
     "nvdb_b200_search": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_search_device": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
+    "nvdb_b200_search_device_static": (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "nvdb_b200_search_two_stage": (_i, [_vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, C.POINTER(Timing)]),
     "nvdb_b200_debug_mma_accumulators": (_i, [_vp, _vp, _u32, _i, _vp]),
     "nvdb_b200_index_set_tuning": (_i, [_vp, _i, _i]),
@@ -329,6 +330,10 @@ class FlatIndexCuda:
 
     def search_device(self, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
         _check(lib.nvdb_b200_search_device(self._h, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream), self._h)
+
+    def search_device_static(self, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream=None):
+        """Allocation-free streaming scan over the library's static device scratch (include/nvdb_b200.h)."""
+        _check(lib.nvdb_b200_search_device_static(self._h, queries_ptr, nq, k, out_ids_ptr, out_scores_ptr, stream), self._h)
 
     # ---- refine (mirrors nvdb::cuda_l2_topk_batch)
     def refine_l2(self, queries, cand_ids, K, want_dist=True, timing: Timing | None = None):

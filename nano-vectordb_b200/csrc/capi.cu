@@ -1911,4 +1911,89 @@ int nvdb_b200_index_profile_read(nvdb_b200_index* idx, double* scan_ms_sum, doub
   return NVDB_B200_OK;
 }
 
+// =====================================================================================================
+// allocation-free streaming scan (no counterpart in the reference; see include/nvdb_b200.h)
+// =====================================================================================================
+// Scratch of nvdb_b200_search_device_static: the per-CTA partial top-k lists [nq][grid][k] of the streaming scan, which
+// the ordinary entry points keep in a grow-only cudaMalloc workspace of the index. Lives in every GPU that loads the
+// library until the process exits. In host code `g_static_scratch` is only a stand-in for the symbol: the device address
+// comes from cudaGetSymbolAddress (static_scratch_ptr), once per device, with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch[NVDB_B200_STATIC_SCRATCH_BYTES];
+
+static std::mutex g_static_mu;
+static void* g_static_ptr[64] = {};
+
+// device address of g_static_scratch on `device` (the caller has made it current); no allocation
+static int static_scratch_ptr(const nvdb_b200_index* idx, int device, void** out) {
+  if (device < 0 || device >= 64) return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "search_device_static: device ordinal >= 64");
+  std::lock_guard<std::mutex> g(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_static_scratch), "cudaGetSymbolAddress (static scratch)");
+    if (!p) return fail(idx, NVDB_B200_ERR_CUDA, "cudaGetSymbolAddress returned NULL for the static scratch");
+    g_static_ptr[device] = p;
+  }
+  *out = g_static_ptr[device];
+  return NVDB_B200_OK;
+}
+
+int nvdb_b200_search_device_static(nvdb_b200_index* idx, const float* queries_dev, uint32_t nq, uint32_t k,
+                                   uint64_t* out_ids_dev, float* out_scores_dev, void* stream) {
+  if (!idx) return fail(nullptr, NVDB_B200_ERR_ARG, "index is NULL");
+  if (nq == 0 || k == 0) return NVDB_B200_OK;
+  if (!queries_dev) return fail(idx, NVDB_B200_ERR_ARG, "Null query");
+  if (!out_ids_dev || !out_scores_dev) return fail(idx, NVDB_B200_ERR_ARG, "output buffer is NULL");
+  std::lock_guard<std::mutex> g(idx->mu);
+  CK(cudaSetDevice(idx->device), "cudaSetDevice");
+  ScanPlan plan;
+  int rc = plan_scan(idx, nq, k, &plan);
+  if (rc) return rc;
+  const size_t need = (size_t)nq * (size_t)plan.grid * k * 8u;
+  if (need > (size_t)NVDB_B200_STATIC_SCRATCH_BYTES)
+    return fail(idx, NVDB_B200_ERR_UNSUPPORTED,
+                "search_device_static: nq * " + std::to_string(plan.grid) + " lists * k * 8 = " + std::to_string(need) +
+                    " bytes of scratch exceed the static maximum of " + std::to_string((size_t)NVDB_B200_STATIC_SCRATCH_BYTES) +
+                    " (use nvdb_b200_search_device, or fewer queries / a smaller k per call)");
+  void* scratch = nullptr;
+  if ((rc = static_scratch_ptr(idx, idx->device, &scratch))) return rc;
+  uint64_t* partial = (uint64_t*)scratch;
+  cudaStream_t s = stream ? (cudaStream_t)stream : idx->stream;
+
+  ScanLaunch L;
+  L.dtype = (int)idx->dtype;
+  L.use_tma = idx->tma_ok;
+  L.tmap = &idx->tmap;
+  L.grid = plan.grid;
+  L.stream = s;
+  ScanArgs a;
+  a.scales = idx->scales;
+  a.base = idx->payload;
+  a.n_rows = (uint32_t)idx->n;
+  a.dim = idx->dim;
+  a.k = k;
+  a.cap = plan.cap;
+  a.num_tiles = (uint32_t)((idx->n + kScanRowsPerTile - 1) / kScanRowsPerTile);
+  a.kchunks = (uint32_t)(((size_t)idx->dim * elem_size(idx->dtype) + 127) / 128);
+  a.stages = plan.stages;
+  a.done_counter = nullptr;  // unfused: every CTA rewrites its k slots of every query, so nothing has to start at zero
+  a.out_ids = nullptr;
+  a.out_scores = nullptr;
+  a.row_offset = idx->row_offset;
+  a.xchg = ScanXchg{};
+  for (uint32_t q0 = 0; q0 < nq; q0 += (uint32_t)plan.nq_template) {
+    const uint32_t left = nq - q0;
+    int t = plan.nq_template;
+    while (t > 1 && (uint32_t)(t / 2) >= left) t >>= 1;
+    a.nq = left < (uint32_t)t ? left : (uint32_t)t;
+    a.queries = queries_dev + (size_t)q0 * idx->dim;
+    a.partial = partial + (size_t)q0 * plan.grid * k;
+    const cudaError_t le = scan_gemv_launch(L, a, t);
+    if (le != cudaSuccess) return fail_cuda(idx, le, "scan_gemv launch (static scratch)");
+    count_launch();
+  }
+  CK(merge_partials_launch(partial, (uint32_t)plan.grid, nq, k, idx->row_offset, out_ids_dev, out_scores_dev, s),
+     "merge_partials launch (static scratch)");
+  return NVDB_B200_OK;
+}
+
 }  // extern "C"
