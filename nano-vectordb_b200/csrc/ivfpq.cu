@@ -51,6 +51,19 @@ struct nvdb_b200_ivfpq {
   size_t ws_bytes[10] = {};
   void* h_pin = nullptr;
   size_t h_pin_bytes = 0;
+  // Small host-API searches (<= kGraphMaxQ queries) replay a captured graph of the call's copies and kernels: one
+  // launch instead of 7-9 API calls. A shape is captured the second time it is seen in a row (its workspaces exist by
+  // then); a workspace regrow (ws_gen) drops the graphs that baked the old pointers in.
+  struct Graph {
+    uint64_t key[8] = {};
+    uint64_t ws_gen = 0;
+    cudaGraphExec_t exec = nullptr;
+    uint32_t launches = 0;
+  } graphs[4];
+  uint32_t graph_next = 0;
+  uint64_t ws_gen = 1, last_key[8] = {};
+  int graph_mode = -1;  // -1 = read NVDB_B200_IVF_GRAPH on first use (default on)
+  uint64_t graph_replays = 0;
   std::mutex mu;
   mutable std::string err;
 };
@@ -79,6 +92,7 @@ int iws(nvdb_b200_ivfpq* h, int which, size_t bytes) {
   if (h->ws[which]) cudaFree(h->ws[which]);
   h->ws[which] = nullptr;
   h->ws_bytes[which] = 0;
+  h->ws_gen++;
   ICK(cudaMalloc(&h->ws[which], bytes), "cudaMalloc (ivfpq workspace)");
   h->ws_bytes[which] = bytes;
   return NVDB_B200_OK;
@@ -576,6 +590,8 @@ void ivf_free(nvdb_b200_ivfpq* h) {
   cudaFree(h->list_off);
   cudaFree(h->rot_t);
   cudaFree(h->zeros);
+  for (auto& g : h->graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
   for (void* w : h->ws) cudaFree(w);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -843,9 +859,63 @@ int pin(nvdb_b200_ivfpq* h, size_t bytes) {
   if (h->h_pin) cudaFreeHost(h->h_pin);
   h->h_pin = nullptr;
   h->h_pin_bytes = 0;
+  h->ws_gen++;
   ICK(cudaMallocHost(&h->h_pin, bytes), "cudaMallocHost");
   h->h_pin_bytes = bytes;
   return NVDB_B200_OK;
+}
+
+constexpr uint32_t kGraphMaxQ = 8;
+
+// Runs `enqueue` (the asynchronous copies and kernels of one host call on h->stream, no synchronisation inside) either
+// directly or, for a small shape seen twice in a row, as a captured graph that later calls replay with one launch.
+template <class F>
+int run_or_replay(nvdb_b200_ivfpq* h, const uint64_t (&key)[8], uint32_t nq, F&& enqueue) {
+  if (h->graph_mode < 0) {
+    const char* e = getenv("NVDB_B200_IVF_GRAPH");
+    h->graph_mode = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (!h->graph_mode || nq > kGraphMaxQ) return enqueue();
+  for (auto& g : h->graphs)
+    if (g.exec && g.ws_gen == h->ws_gen && !memcmp(g.key, key, sizeof key)) {
+      ICK(cudaGraphLaunch(g.exec, h->stream), "ivfpq graph launch");
+      count_launch(g.launches);
+      h->graph_replays++;
+      return NVDB_B200_OK;
+    }
+  if (memcmp(h->last_key, key, sizeof key)) {  // first sighting: plain run (grows and warms every workspace)
+    memcpy(h->last_key, key, sizeof key);
+    return enqueue();
+  }
+  const uint64_t gen0 = h->ws_gen;
+  const uint64_t l0 = nvdb_b200_launch_count();
+  if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
+    cudaGetLastError();
+    h->graph_mode = 0;
+    return enqueue();
+  }
+  const int rc = enqueue();
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ee = cudaStreamEndCapture(h->stream, &graph);
+  const uint32_t nl = (uint32_t)(nvdb_b200_launch_count() - l0);
+  cudaGraphExec_t exec = nullptr;
+  if (rc == NVDB_B200_OK && ee == cudaSuccess && graph && h->ws_gen == gen0 &&
+      cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess) {
+    cudaGraphDestroy(graph);
+    auto& g = h->graphs[h->graph_next++ % 4u];
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    memcpy(g.key, key, sizeof key);
+    g.ws_gen = h->ws_gen;
+    g.exec = exec;
+    g.launches = nl;
+    ICK(cudaGraphLaunch(g.exec, h->stream), "ivfpq graph launch");  // the captured work has not run yet
+    return NVDB_B200_OK;
+  }
+  if (graph) cudaGraphDestroy(graph);
+  cudaGetLastError();
+  h->graph_mode = 0;  // not capturable here: stay on the plain path from now on
+  if (rc != NVDB_B200_OK) return rc;
+  return enqueue();
 }
 
 }  // namespace
@@ -1065,13 +1135,18 @@ int nvdb_b200_ivfpq_search(nvdb_b200_ivfpq* h, const float* queries_host, uint32
   if ((rc = iws(h, IWS_OUT, ob))) return rc;
   if ((rc = pin(h, qb + 2 * ob))) return rc;
   memcpy(h->h_pin, queries_host, qb);  // pinned staging: asynchronous copies, one sync per call
-  ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
-  if ((rc = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND],
-                               out_dist ? (float*)h->ws[IWS_OUT] : nullptr, h->stream)))
-    return rc;
   uint8_t* hp = (uint8_t*)h->h_pin + qb;
-  ICK(cudaMemcpyAsync(hp, h->ws[IWS_CAND], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate ids");
-  if (out_dist) ICK(cudaMemcpyAsync(hp + ob, h->ws[IWS_OUT], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate distances");
+  auto enqueue = [&]() -> int {
+    ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
+    if (int rc2 = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND],
+                                     out_dist ? (float*)h->ws[IWS_OUT] : nullptr, h->stream))
+      return rc2;
+    ICK(cudaMemcpyAsync(hp, h->ws[IWS_CAND], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate ids");
+    if (out_dist) ICK(cudaMemcpyAsync(hp + ob, h->ws[IWS_OUT], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate distances");
+    return NVDB_B200_OK;
+  };
+  const uint64_t key[8] = {out_dist ? 3u : 1u, nq, nprobe, R, 0, 0, 0, 0};
+  if ((rc = run_or_replay(h, key, nq, enqueue))) return rc;
   ICK(cudaStreamSynchronize(h->stream), "ivfpq search");
   memcpy(out_ids, hp, ob);
   if (out_dist) memcpy(out_dist, hp + ob, ob);
@@ -1083,11 +1158,14 @@ int nvdb_b200_ivfpq_search_refine(nvdb_b200_ivfpq* h, nvdb_b200_index* base, con
   if (!h || !base || !queries_host || !out_ids) return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search_refine: NULL argument");
   if (nq == 0) return NVDB_B200_OK;
   if (k == 0 || k > R) return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search_refine: need 1 <= k <= R");
+  const void* b_payload = nullptr;
+  const float* b_scales = nullptr;
+  uint32_t b_dtype = 0;
   {  // `base` must be the rows this index was built over, on this index's device (its stream and workspaces are used)
     uint64_t bn = 0;
     uint32_t bd = 0;
     int bdev = -1;
-    if (nvdb_b200_index_info(base, &bn, &bd, nullptr, &bdev, nullptr, nullptr, nullptr) != NVDB_B200_OK || bdev != h->device ||
+    if (nvdb_b200_index_info(base, &bn, &bd, &b_dtype, &bdev, nullptr, &b_payload, &b_scales) != NVDB_B200_OK || bdev != h->device ||
         bd != h->d || bn != h->n)
       return ifail(h, NVDB_B200_ERR_ARG, "ivfpq search_refine: base does not match the index (device, dim or row count)");
   }
@@ -1101,17 +1179,23 @@ int nvdb_b200_ivfpq_search_refine(nvdb_b200_ivfpq* h, nvdb_b200_index* base, con
   if ((rc = pin(h, qb + 2 * ob))) return rc;
   // staged through pinned memory so that the copies are truly asynchronous and the call costs one sync
   memcpy(h->h_pin, queries_host, qb);
-  ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
-  if ((rc = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND], nullptr, h->stream)))
-    return rc;
-  uint32_t* o_ids = (uint32_t*)h->ws[IWS_OUT];
-  float* o_dist = (float*)((uint8_t*)h->ws[IWS_OUT] + ob);
-  // candidates never leave the device (the reference copies them to the host and back: src/cuda_refine.cu:926-929)
-  if (nvdb_b200_refine_l2_device(base, (const float*)h->ws[IWS_Q], (const uint32_t*)h->ws[IWS_CAND], nq, R, k, o_ids, o_dist,
-                                 h->stream) != NVDB_B200_OK)
-    return ifail(h, NVDB_B200_ERR_CUDA, std::string("refine: ") + nvdb_b200_last_error(base));
   uint8_t* hp = (uint8_t*)h->h_pin + qb;
-  ICK(cudaMemcpyAsync(hp, h->ws[IWS_OUT], 2 * ob, cudaMemcpyDeviceToHost, h->stream), "D2H results");
+  auto enqueue = [&]() -> int {
+    ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
+    if (int rc2 = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND], nullptr, h->stream))
+      return rc2;
+    uint32_t* o_ids = (uint32_t*)h->ws[IWS_OUT];
+    float* o_dist = (float*)((uint8_t*)h->ws[IWS_OUT] + ob);
+    // candidates never leave the device (the reference copies them to the host and back: src/cuda_refine.cu:926-929)
+    if (nvdb_b200_refine_l2_device(base, (const float*)h->ws[IWS_Q], (const uint32_t*)h->ws[IWS_CAND], nq, R, k, o_ids, o_dist,
+                                   h->stream) != NVDB_B200_OK)
+      return ifail(h, NVDB_B200_ERR_CUDA, std::string("refine: ") + nvdb_b200_last_error(base));
+    ICK(cudaMemcpyAsync(hp, h->ws[IWS_OUT], 2 * ob, cudaMemcpyDeviceToHost, h->stream), "D2H results");
+    return NVDB_B200_OK;
+  };
+  // the graph bakes the base's device pointers in: they are part of the key
+  const uint64_t key[8] = {2, nq, nprobe, R, k, (uint64_t)(uintptr_t)b_payload, (uint64_t)(uintptr_t)b_scales, b_dtype};
+  if ((rc = run_or_replay(h, key, nq, enqueue))) return rc;
   ICK(cudaStreamSynchronize(h->stream), "ivfpq search_refine");
   memcpy(out_ids, hp, ob);
   if (out_dist) memcpy(out_dist, hp + ob, ob);

@@ -172,6 +172,50 @@ def test_recall_grows_with_nprobe_and_refine_recovers_exact_neighbours(nv):
     assert ref.recall_at_k(full_i, truth) > 0.995
 
 
+def test_small_host_searches_replayed_from_a_graph_equal_the_batch(nv):
+    """Host-API searches of <= 8 queries are captured the second time a shape is seen and replayed afterwards
+    (ivfpq.cu: run_or_replay). Plain, capturing and replayed calls must all return the batch's answer, also when shapes
+    alternate (several cached graphs), when a workspace regrows in between (graphs dropped) and with the knob off."""
+    import os
+    n, d, nlist, M, k = 30_000, 64, 64, 16, 10
+    x = clustered(n, d, 80, 12)
+    rng = np.random.default_rng(3)
+    queries = np.ascontiguousarray(x[rng.integers(0, n, 40)] + 0.1 * rng.standard_normal((40, d)).astype(np.float32))
+    base, rows, ivf = build(nv, x, F16, nlist=nlist, pq_m=M, ntrain=10_000, niter=6, seed=5)
+    with base, ivf:
+        bi, bd = ivf.search(queries, 8, 50)               # 40 queries: never a graph
+        ri, rd = ivf.search_refine(queries, 8, 50, k)
+        l0 = nv.launch_count()
+        for i in range(12):                               # plain, capture, then replays
+            gi, gd = ivf.search(queries[i:i + 1], 8, 50)
+            assert np.array_equal(gi[0], bi[i]) and np.array_equal(gd[0], bd[i]), i
+        per_call = (nv.launch_count() - l0) / 12
+        assert per_call == int(per_call) and per_call >= 4, "replays count the kernels they launch"
+        for i in range(12):                               # two shapes alternating: capture happens on a repeat only
+            gi, gd = ivf.search_refine(queries[i:i + 1], 8, 50, k)
+            assert np.array_equal(gi[0], ri[i]) and np.array_equal(gd[0], rd[i]), i
+            gi, gd = ivf.search_refine(queries[i:i + 1], 8, 50, k)
+            assert np.array_equal(gi[0], ri[i]) and np.array_equal(gd[0], rd[i]), i
+            gi, _ = ivf.search(queries[i:i + 4], 8, 50, return_dist=False)
+            assert np.array_equal(gi, bi[i:i + 4]), i
+            gi, _ = ivf.search(queries[i:i + 4], 8, 50, return_dist=False)
+            assert np.array_equal(gi, bi[i:i + 4]), i
+        big_i, _ = ivf.search(np.tile(queries, (8, 1)), 8, 200)   # regrows the workspaces: cached graphs are stale now
+        assert np.array_equal(big_i[:40, :50], bi)
+        for i in range(4):
+            gi, gd = ivf.search_refine(queries[i:i + 1], 8, 50, k)
+            assert np.array_equal(gi[0], ri[i]) and np.array_equal(gd[0], rd[i]), i
+    os.environ["NVDB_B200_IVF_GRAPH"] = "0"
+    try:
+        base, rows, ivf = build(nv, x, F16, nlist=nlist, pq_m=M, ntrain=10_000, niter=6, seed=5)
+        with base, ivf:
+            for i in range(4):
+                gi, gd = ivf.search_refine(queries[i:i + 1], 8, 50, k)
+                assert np.array_equal(gi[0], ri[i]) and np.array_equal(gd[0], rd[i]), i
+    finally:
+        del os.environ["NVDB_B200_IVF_GRAPH"]
+
+
 def test_argument_errors(nv):
     x = clustered(3000, 32, 10, 1)
     with nv.FlatIndexCuda.from_host(x, None, F32) as base:
