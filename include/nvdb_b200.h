@@ -200,7 +200,7 @@ enum {
   NVDB_B200_TUNE_FUSED_MERGE = 4, /* final merge inside the streaming scan's last CTA: 0 never, 1 auto (default), 2 always */
   NVDB_B200_TUNE_MMA_RESIDENT = 5, /* i8 tensor scan, query limbs resident in shared memory: 0 none, 1 the first (default), 2 both when they fit (CTA pairs) */
   NVDB_B200_TUNE_EXACT_TIER2 = 6, /* exact path: queries whose certificate failed get a second tensor-core pass with wider candidate lists before the streaming scan: 0 off, 1 on (default), > 1 that many list entries (A/B measurements); env NVDB_B200_EXACT_TIER2 */
-  NVDB_B200_TUNE_ROWS = 7, /* exact path, small batches: row-tile tensor kernel (base rows on M, the whole batch resident in shared memory; scan_rows.cu): 0 never, 1 auto (default: int8 bases whenever the batch and its candidate lists fit — measured faster there — f16 never), 2 whenever it fits; env NVDB_B200_ROWS */
+  NVDB_B200_TUNE_ROWS = 7, /* exact path, small batches: row-tile tensor kernel (base rows on M, the whole batch resident in shared memory; scan_rows.cu): 0 never, 1 auto (default: int8 bases whenever the batch and its candidate lists fit, f16 bases up to 32 queries — where it measured faster), 2 whenever it fits; env NVDB_B200_ROWS */
   NVDB_B200_TUNE_ROWS_SEED = 8, /* its cross-CTA threshold seeding: 0 off, 1 auto (default: from 40 queries), 2 always; env NVDB_B200_ROWS_SEED */
   NVDB_B200_TUNE_MMA_2CTA = 3   /* CTA-pair (cta_group::2) tensor-core scan (f16, i8): 0 never, 1 (default) / 2 whenever the batch has an even number of 128-query tiles */
 };

@@ -673,7 +673,16 @@ int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) 
     const uint32_t fixed = scan_gemv_smem_bytes(true, 0, t, idx->dim, p->cap);
     if (fixed + 3u * 32768u > (uint32_t)idx->max_smem) continue;
     int st = (int)(((uint32_t)idx->max_smem - fixed) / (32768u + 16u));
-    if (st > 6) st = 6;
+    // Ring depth: FP16 rows run fastest with 4 x 32 KB in flight per SM (batch 1, 2.9 M x 768: 6 stages 0.68-0.70 ms,
+    // 5 0.67, 4 0.64-0.65, 3 0.65-0.67; profiles/r2_ring_depth_sweep.jsonl) - a deeper ring spreads the requests of
+    // 148 SMs over more DRAM pages at a time. INT8 (issue-bound) and FP32 do not care / prefer 5-6.
+    // NVDB_B200_GEMV_MAX_STAGES=3..6 overrides (A/B).
+    int st_cap = idx->dtype == NVDB_B200_F16 ? 4 : 6;
+    if (const char* e = getenv("NVDB_B200_GEMV_MAX_STAGES")) {
+      const int v = atoi(e);
+      if (v >= 3 && v <= 6) st_cap = v;
+    }
+    if (st > st_cap) st = st_cap;
     // single-query passes may run two CTAs per SM (more consumer warps to cover the int8 conversion chain); each CTA
     // then gets half of the shared memory. Tuning knob NVDB_B200_TUNE_GEMV_CTAS (default 1).
     if (t == 1 && gemv_ctas(idx) == 2) {
@@ -971,10 +980,11 @@ int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
 // operand) — one HBM pass, tensor work proportional to the batch. false = the batch / k' does not fit, use scan_mma*.
 bool rows_kernel_fits(const nvdb_b200_index* idx, const float* d_queries, uint32_t nq, uint32_t kp, RowsPlan* plan) {
   if (!idx->mma_ok || !idx->tune_rows) return false;
-  // measured (profiles/r2_probe_rows_ab.jsonl, interleaved on one box): int8 0.37-0.42 ms against 0.49-0.57 ms of the
-  // query-tile kernels for 1..32 queries (0.51-0.57 against 0.58-0.59 at 48..64); f16 is the other way round (0.69-0.73
-  // against 0.70-0.80: its one-limb query tile is cheap to re-stream and 256-row tiles need half the MMA issues)
-  if (idx->tune_rows == 1 && idx->dtype != kDtI8) return false;
+  // measured (profiles/r2_probe_rows_ab_v2.jsonl, interleaved on one box, 4-stage ring): int8 0.36-0.43 ms against
+  // 0.51-0.59 ms of the query-tile kernels for 1..32 queries (0.52-0.65 against 0.59-0.67 at 48..128); f16 0.66-0.68
+  // against 0.69-0.71 up to 16 queries, 0.76 / 0.78 at 32, and the other way round from 48 on (0.80 against 0.76: the
+  // one-limb query tile is cheap to re-stream and 256-row tiles need half the MMA issues)
+  if (idx->tune_rows == 1 && idx->dtype != kDtI8 && nq > 32u) return false;
   if ((reinterpret_cast<uintptr_t>(d_queries) & 15u) || (idx->dim % 4u)) return false;  // float4 reads of the queries
   return scan_rows_plan((int)idx->dtype, nq, kp, idx->dim, idx->max_smem, plan);
 }

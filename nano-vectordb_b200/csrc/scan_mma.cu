@@ -25,6 +25,7 @@
 //     int32; score = fmaf(s2, I2, s1*I1) * scale_row in a fixed FP32 order -> bit-exact against the CPU
 //     restatement of this scheme (oracle/nvdb_oracle.c orc_dot_i8_limbs), ~3e-6 relative to the AVX2 kernel.
 #include "common.cuh"
+#include <cstdlib>
 #include "scan.h"
 #include "tc_common.cuh"
 #include "scan_mma_common.cuh"
@@ -396,7 +397,12 @@ bool scan_mma_plan(int dtype, int limbs, uint32_t k, int max_smem, uint32_t* blo
   const uint32_t cand[2] = {dtype == kDtF16 ? 256u : 128u, 128u};
   for (int c = 0; c < 2; ++c) {
     const int min_stages = (c == 0 && cand[0] != cand[1]) ? 3 : 2;
-    for (int st = 6; st >= min_stages; --st)
+    int st_max = 6;
+    if (const char* e = getenv("NVDB_B200_MMA_MAX_STAGES")) {  // diagnostic: ring depth experiments
+      const int v = atoi(e);
+      if (v >= 3 && v < st_max) st_max = v;
+    }
+    for (int st = st_max; st >= min_stages; --st)
       if (mma_layout(cand[c], limbs, st, k <= (uint32_t)kMmaRegK ? 0u : k).total <= (uint32_t)max_smem) {
         *block_n = cand[c];
         *stages = st;

@@ -26,6 +26,7 @@
 // Numerics are those of scan_mma.cu (same limb schemes, same FP32 epilogue order), so the candidates carry the same
 // approximate scores and the exact path's certificate (rescore.cu) holds unchanged.
 #include "common.cuh"
+#include <cstdlib>
 #include "scan.h"
 #include "scan_mma_common.cuh"
 #include "tc_common.cuh"
@@ -608,7 +609,15 @@ bool scan_rows_plan(int dtype, uint32_t nq, uint32_t kp, uint32_t dim, int max_s
   while (cap < 4u * kp) cap <<= 1;  // a list is compacted when half full: at least k' free slots afterwards
   if (cap > 4096u) return false;
   const uint32_t kchunks = (dim * es + 127u) / 128u;
-  for (int st = (int)kRowsMaxStages; st >= 3; --st) {
+  // Ring depth: 4 x 32 KB in flight per SM already covers the HBM latency, and a deeper ring is SLOWER (FP16 8 queries:
+  // 6 stages 0.721 ms, 5 0.697, 4 0.665, 3 0.674; INT8 0.376 / 0.373 / 0.365 / 0.375: profiles/r2_ring_depth_sweep.jsonl) -
+  // the requests of 148 SMs then spread over more DRAM pages at a time. NVDB_B200_ROWS_MAX_STAGES=3..6 overrides (A/B).
+  int st_max = 4;
+  if (const char* e = getenv("NVDB_B200_ROWS_MAX_STAGES")) {
+    const int v = atoi(e);
+    if (v >= 3 && v <= (int)kRowsMaxStages) st_max = v;
+  }
+  for (int st = st_max; st >= 3; --st) {
     if (rows_layout(nb, bp, cap, kchunks, st).total <= (uint32_t)max_smem) {
       out->bp = bp;
       out->nb = nb;
