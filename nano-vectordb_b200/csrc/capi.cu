@@ -1010,7 +1010,8 @@ int rows_candidate_scan(nvdb_b200_index* idx, const RowsPlan& plan, const float*
   // (pays from ~40 queries on: below that its publish / poll / select steps cost more than the appends they save)
   const bool seed = idx->tune_rows_seed == 2 || (idx->tune_rows_seed == 1 && nq >= 40u);
   if (seed && (uint32_t)grid >= kp && grid <= 256) {  // the kernel's own condition: every CTA publishes or none
-    if ((rc = ensure_ws(idx, WS_ROWS_SEED, 64u + (size_t)idx->num_sms * 2u * 128u * 4u))) return rc;
+    // 4 rounds of [grid][bp <= 128] words after the 64-byte header of counters; one size, so it is never re-allocated
+    if ((rc = ensure_ws(idx, WS_ROWS_SEED, 64u + 4u * 256u * 128u * 4u))) return rc;
     if (idx->rows_seed_seen != idx->d_ws[WS_ROWS_SEED]) {
       CK(cudaMemsetAsync(idx->d_ws[WS_ROWS_SEED], 0, 64, stream), "memset seeding counter");
       idx->rows_seed_seen = idx->d_ws[WS_ROWS_SEED];
@@ -1018,6 +1019,10 @@ int rows_candidate_scan(nvdb_b200_index* idx, const RowsPlan& plan, const float*
     }
     a.seed_ws = (uint32_t*)idx->d_ws[WS_ROWS_SEED];
     a.seed_target = ++idx->rows_launches * (uint32_t)grid;
+    // one round (after the first tile): a second and third one (tiles 8, 64) cut the appends further but measured no
+    // faster (64 int8 queries 0.461 / 0.465 ms with 1 / 3 rounds, 0.482 without seeding: profiles/r2_rows_startup.jsonl)
+    a.seed_rounds = 1;
+    if (const char* e = getenv("NVDB_B200_ROWS_ROUNDS")) a.seed_rounds = (uint32_t)atoi(e) > 3u ? 3u : (uint32_t)atoi(e) < 1u ? 1u : (uint32_t)atoi(e);
   }
   a.n_rows = (uint32_t)idx->n;
   a.dim = idx->dim;

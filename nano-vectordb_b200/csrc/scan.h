@@ -121,6 +121,7 @@ struct RowsArgs {
   uint32_t* seed_ws;      // cross-CTA threshold seeding: [0] arrival counter, [16 + cta * bp + q] best ordered score of
                           // CTA cta for query q after its first tile; null = off
   uint32_t seed_target;   // counter value that means "every CTA of THIS launch has published" (launch number * grid)
+  uint32_t seed_rounds;   // publication rounds (after tile 0, 8, 64 of every CTA), <= 3; every launch on a workspace uses the same
   uint32_t n_rows, dim, kp, nq;
   uint32_t num_tiles;     // ceil(n_rows / 128)
   uint32_t kchunks;       // ceil(dim * elem_size / 128)

@@ -18,10 +18,11 @@
 //   warp 1      : tcgen05.mma issuer (one elected lane), 4 MMAs per K chunk
 //   warps 2..5  : epilogue, ONE THREAD PER BASE ROW: tcgen05.ld of its lane (its row's scores against every query), compare
 //                 with the query's threshold (a broadcast shared-memory word) and — rarely — append an ordered key to the
-//                 query's candidate list in shared memory (atomic slot). A list is compacted by one warp (bitonic sort, keep
-//                 the best k', raise the threshold) when it is half full. An append that finds its list full is kept as a
-//                 pending bit and retried after the compaction from the accumulators, which stay in TMEM until the tile is
-//                 done: nothing is ever dropped, whatever the data (first tile: every row qualifies for every query).
+//                 query's candidate list in shared memory (atomic slot). An append that finds its list full is kept as a
+//                 pending bit and starts a maintenance round: every list that is at least half full is compacted by one
+//                 warp (bitonic sort, keep the best k', raise the threshold), then the pending appends are retried from
+//                 the accumulators, which stay in TMEM until the tile is done: nothing is ever dropped, whatever the
+//                 data (first tile: every row qualifies for every query).
 //
 // Numerics are those of scan_mma.cu (same limb schemes, same FP32 epilogue order), so the candidates carry the same
 // approximate scores and the exact path's certificate (rescore.cu) holds unchanged.
@@ -64,8 +65,8 @@ __host__ __device__ inline RowsSmem rows_layout(uint32_t nb, uint32_t bp, uint32
   L.wl_off = off;    // compaction work lists: [2][4] {count, head, -, -} then [2][bp] query numbers
   off += 32u + 2u * bp * 4u;
   off = (off + 7u) & ~7u;
-  L.bars_off = off;  // full[stages], empty[stages], tfull[2], tempty[2]
-  off += (2u * (uint32_t)stages + 4u) * 8u;
+  L.bars_off = off;  // full[stages], empty[stages], tfull[8], tempty[8]
+  off += (2u * (uint32_t)stages + 16u) * 8u;
   L.tmem_off = off;
   off += 16u;
   L.total = off + 1024u;  // slack for the 1024-byte alignment of the swizzled regions
@@ -142,7 +143,13 @@ __device__ __noinline__ void warp_compact(uint32_t keys_q, uint32_t cap, uint32_
     const uint32_t nc = c < kp ? c : kp;
     sts_u32(cnt_addr, nc);
     // admission is `>=` so that rows tying with the k'-th best reach the exact (score, id) ordering of the next sort
-    sts_f32(thr_addr, nc == kp ? key_score(lds_u64(keys_q + (kp - 1u) * 8u)) : -INFINITY);
+    // (never lowered: a bound adopted from the other CTAs - threshold seeding - stays in force)
+    if (nc == kp) {
+      const float t = key_score(lds_u64(keys_q + (kp - 1u) * 8u));
+      float cur;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(cur) : "r"(thr_addr));
+      if (t > cur) sts_f32(thr_addr, t);
+    }
   }
   __syncwarp();
 }
@@ -183,7 +190,12 @@ __device__ __noinline__ void warp_compact64(uint32_t keys_q, uint32_t c, uint32_
   const uint64_t kth = __shfl_sync(0xffffffffu, (uint32_t)(k0 >> 32), kp - 1u);
   if (lane == 0) {
     sts_u32(cnt_addr, nc);
-    sts_f32(thr_addr, nc == kp ? ordered_to_float((uint32_t)kth) : -INFINITY);
+    if (nc == kp) {  // never lowered (see warp_compact)
+      const float t = ordered_to_float((uint32_t)kth);
+      float cur;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(cur) : "r"(thr_addr));
+      if (t > cur) sts_f32(thr_addr, t);
+    }
   }
   __syncwarp();
 }
@@ -198,7 +210,13 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars_off);
   uint64_t* empty = full + a.stages;
   uint64_t* tfull = empty + a.stages;
-  uint64_t* tempty = tfull + 2;
+  uint64_t* tempty = tfull + 8;
+  // Accumulator buffers in TMEM: as many as 512 columns hold (2 for 256 accumulator columns ... 8 from 64 down), a power
+  // of two. The MMA warp may run that many tiles ahead of the epilogue, which hides a maintenance round of the candidate
+  // lists (a few microseconds during which no epilogue warp releases a buffer) from the HBM stream.
+  uint32_t nbuf_log2 = 1;
+  while (nbuf_log2 < 3u && (a.nb << (nbuf_log2 + 1u)) <= kTmemCols) ++nbuf_log2;
+  const uint32_t nbuf = 1u << nbuf_log2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
   const uint32_t b_u32 = smem_u32(smem + L.b_off), keys_u32 = smem_u32(smem + L.keys_off);
   const uint32_t par_u32 = smem_u32(smem + L.par_off), cnt_u32 = smem_u32(smem + L.cnt_off);
@@ -213,7 +231,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (uint32_t b = 0; b < nbuf; ++b) {
       mbar_init(&tfull[b], 1);
       mbar_init(&tempty[b], kRowsEpiWarps);  // one arrival per epilogue warp
     }
@@ -225,6 +243,10 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
   {
     const uint32_t pieces = a.kchunks * L.b_chunk_bytes / 16u;
     for (uint32_t i = tid; i < pieces; i += kRowsThreads) sts_v4(b_u32 + i * 16u, make_uint4(0u, 0u, 0u, 0u));
+    // the candidate lists too: a slot that was never written must read as "no key" (threshold seeding looks at slots that
+    // another warp may have reserved but not yet written)
+    const uint32_t kpieces = a.bp * a.cap / 2u;
+    for (uint32_t i = tid; i < kpieces; i += kRowsThreads) sts_v4(keys_u32 + i * 16u, make_uint4(0u, 0u, 0u, 0u));
   }
   tc::fence_before_thread_sync();
   __syncthreads();
@@ -262,14 +284,42 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
 
   // ---- query preparation: FP32 queries -> limb rows of the B operand (swizzled, K-major) + per-query scales. Same
   // arithmetic as scan_mma.cu's prep kernels (oracle/nvdb_oracle.c: orc_query_limbs_f16 / _i8 restate it).
+  // The MMA cannot start before every query is converted, so this loop is pure start-up latency (20 us for 64 queries
+  // when every query cost two dependent global round trips). dim <= 1024: a lane keeps its share of the query in registers
+  // (8 float4: the pieces it converts) and the NEXT query of the warp is loaded while the current one is converted.
+  constexpr uint32_t kEPP = kI8 ? 16u : 8u;  // FP32 elements per 16-byte operand piece
+  constexpr uint32_t kF4P = kEPP / 4u;       // float4 loads per piece
+  auto load_query = [&](uint32_t q, float4 (&r)[8]) {
+    const float* src = a.queries + (size_t)q * a.dim;
+#pragma unroll
+    for (uint32_t c = 0; c < 8u; ++c) {
+      const uint32_t e = ((c / kF4P) * 32u + lane) * kEPP + (c % kF4P) * 4u;
+      r[c] = (q < a.nq && e < a.dim) ? *reinterpret_cast<const float4*>(src + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  const bool in_regs = a.dim <= 1024u;
+  float4 nxt[8];
+  if (in_regs) load_query(warp, nxt);
   for (uint32_t q = warp; q < a.bp; q += kRowsThreads / 32) {
     float qs1 = 0.f, qs2 = 0.f, thr0 = INFINITY;  // padding columns: zero rows, nothing is ever admitted
+    float4 cur[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) cur[c] = nxt[c];
+    if (in_regs && q + kRowsThreads / 32 < a.nq) load_query(q + kRowsThreads / 32, nxt);
     if (q < a.nq) {
       const float* src = a.queries + (size_t)q * a.dim;
       float amax = 0.f;
-      for (uint32_t i = lane * 4u; i < a.dim; i += 128u) {
-        const float4 v = *reinterpret_cast<const float4*>(src + i);
-        amax = fmaxf(fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+      if (in_regs) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4 v = cur[c];
+          amax = fmaxf(fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+        }
+      } else {
+        for (uint32_t i = lane * 4u; i < a.dim; i += 128u) {
+          const float4 v = *reinterpret_cast<const float4*>(src + i);
+          amax = fmaxf(fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+        }
       }
 #pragma unroll
       for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
@@ -281,9 +331,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
           e = e > 100 ? 100 : (e < -100 ? -100 : e);
         }
         qs1 = scalbnf(1.0f, -e);
-        for (uint32_t p8 = lane; p8 * 8u < a.dim; p8 += 32u) {  // 8 elements = one 16-byte piece of the fp16 row
-          const float4 v0 = *reinterpret_cast<const float4*>(src + p8 * 8u);
-          const float4 v1 = *reinterpret_cast<const float4*>(src + p8 * 8u + 4u);
+        auto piece = [&](uint32_t p8, const float4& v0, const float4& v1) {  // 8 elements = one 16-byte piece of the fp16 row
           const __half2 h0 = __floats2half2_rn(scalbnf(v0.x, e), scalbnf(v0.y, e));
           const __half2 h1 = __floats2half2_rn(scalbnf(v0.z, e), scalbnf(v0.w, e));
           const __half2 h2 = __floats2half2_rn(scalbnf(v1.x, e), scalbnf(v1.y, e));
@@ -295,6 +343,16 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
           w.w = *reinterpret_cast<const uint32_t*>(&h3);
           const uint32_t byte = p8 * 16u, kc = byte >> 7, c = byte & 127u;
           sts_v4(b_u32 + kc * L.b_chunk_bytes + swz128(q, c), w);
+        };
+        if (in_regs) {
+#pragma unroll
+          for (uint32_t pc = 0; pc < 4u; ++pc) {
+            const uint32_t p8 = pc * 32u + lane;
+            if (p8 * 8u < a.dim) piece(p8, cur[(pc * 2u) & 7u], cur[(pc * 2u + 1u) & 7u]);
+          }
+        } else {
+          for (uint32_t p8 = lane; p8 * 8u < a.dim; p8 += 32u)
+            piece(p8, *reinterpret_cast<const float4*>(src + p8 * 8u), *reinterpret_cast<const float4*>(src + p8 * 8u + 4u));
         }
       } else {
         const float s1 = (amax > 0.f && amax < INFINITY) ? __fdiv_rn(amax, 127.f) : 1.f;
@@ -303,12 +361,11 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
         const float inv2 = __fdiv_rn(1.f, s2);
         qs1 = s1;
         qs2 = s2;
-        for (uint32_t p16 = lane; p16 * 16u < a.dim; p16 += 32u) {  // 16 elements = one 16-byte piece of each int8 limb row
+        auto piece = [&](uint32_t p16, const float4 (&vv4)[4]) {  // 16 elements = one 16-byte piece of each int8 limb row
           uint32_t w1[4], w2[4];
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            const float4 v = *reinterpret_cast<const float4*>(src + p16 * 16u + g * 4);
-            const float vv[4] = {v.x, v.y, v.z, v.w};
+            const float vv[4] = {vv4[g].x, vv4[g].y, vv4[g].z, vv4[g].w};
             uint32_t b1 = 0, b2 = 0;
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -326,6 +383,20 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
           const uint32_t byte = p16 * 16u, kc = byte >> 7, c = byte & 127u;
           sts_v4(b_u32 + kc * L.b_chunk_bytes + swz128(q, c), make_uint4(w1[0], w1[1], w1[2], w1[3]));
           sts_v4(b_u32 + kc * L.b_chunk_bytes + swz128(a.bp + q, c), make_uint4(w2[0], w2[1], w2[2], w2[3]));
+        };
+        if (in_regs) {
+#pragma unroll
+          for (uint32_t pc = 0; pc < 2u; ++pc) {
+            const uint32_t p16 = pc * 32u + lane;
+            const float4 vv4[4] = {cur[(pc * 4u) & 7u], cur[(pc * 4u + 1u) & 7u], cur[(pc * 4u + 2u) & 7u], cur[(pc * 4u + 3u) & 7u]};
+            if (p16 * 16u < a.dim) piece(p16, vv4);
+          }
+        } else {
+          for (uint32_t p16 = lane; p16 * 16u < a.dim; p16 += 32u) {
+            const float4 vv4[4] = {*reinterpret_cast<const float4*>(src + p16 * 16u), *reinterpret_cast<const float4*>(src + p16 * 16u + 4u),
+                                   *reinterpret_cast<const float4*>(src + p16 * 16u + 8u), *reinterpret_cast<const float4*>(src + p16 * 16u + 12u)};
+            piece(p16, vv4);
+          }
         }
       }
     }
@@ -349,10 +420,10 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     const uint32_t idesc = kI8 ? tc::idesc_s8_s32(kRowsTile, a.nb) : tc::idesc_f16_f32(kRowsTile, a.nb);
     uint32_t stage = 0, phase = 0, it = 0;
     for (uint32_t tile = j; tile < a.num_tiles; tile += P, ++it) {
-      const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
+      const uint32_t buf = it & (nbuf - 1u), bphase = (it >> nbuf_log2) & 1;
       mbar_wait(&tempty[buf], bphase ^ 1);
       tc::fence_after_thread_sync();
-      const uint32_t acc = tmem_base + buf * kAccColsPerBuf;
+      const uint32_t acc = tmem_base + buf * a.nb;
       for (uint32_t sg = 0; sg < nsg; ++sg) {
         const uint32_t c0 = sg * kRowsCps;
         const uint32_t nch = a.kchunks - c0 < kRowsCps ? a.kchunks - c0 : kRowsCps;
@@ -391,10 +462,17 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     const uint32_t lane_addr = tmem_base + ((qd * 32u) << 16);
     const uint32_t ngroups = a.bp >> 4;          // groups of 16 queries
     const uint32_t half_cap = a.cap >> 1;
-    uint32_t rp = 0;                             // parity of the compaction work list appends go to
-    // cross-CTA threshold seeding (see below): off when there is no workspace or fewer CTAs than list entries
-    bool seeded = a.seed_ws == nullptr || P < a.kp || P > 256u;
-    uint32_t next_poll = 1;                      // tile count after which the arrival counter is looked at next
+    // cross-CTA threshold seeding (see below): off when there is no workspace or fewer CTAs than list entries; round r is
+    // published after tile 0 / 8 / 64 when every CTA has at least 2 more tiles after it
+    uint32_t nrounds = 0;
+    if (a.seed_ws != nullptr && P >= a.kp && P <= 256u) {
+      const uint32_t tiles_min = a.num_tiles / P;
+      for (uint32_t pit = 0; nrounds < a.seed_rounds && pit + 2u < tiles_min; pit = pit == 0u ? 8u : pit * 8u) ++nrounds;
+      if (nrounds == 0) nrounds = 1;  // the single early round of small bases
+    }
+    uint32_t my_round = 0, pub_round = 0, pub_it = 0;  // rounds adopted by this warp / published by it; tile of the next one
+    uint32_t arrived_round = 0, pcur = 0;             // thread 64 only: rounds whose P publications it has seen
+    bool polled = false;
 
     // score of (this row, query q) from the raw accumulators, in scan_mma.cu's fixed FP32 order
     auto score_of = [&](const float4& p, uint32_t v, uint32_t w, float rs) -> float {
@@ -415,34 +493,40 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
     };
 
     uint32_t it = 0;
+    float rs_next = 0.f;
+    if constexpr (kI8) {
+      const uint32_t r0 = j * kRowsTile + rl;
+      rs_next = (j < a.num_tiles && r0 < a.n_rows) ? __ldg(a.scales + r0) : 0.f;
+    }
     for (uint32_t tile = j; tile < a.num_tiles; tile += P, ++it) {
-      const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
+      const uint32_t buf = it & (nbuf - 1u), bphase = (it >> nbuf_log2) & 1;
       const uint32_t row = tile * kRowsTile + rl;
       const bool row_ok = row < a.n_rows;
+      if (tid == 64u && arrived_round < pub_round) {  // poll issued here, looked at after the tile: its latency is hidden
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(pcur) : "l"(a.seed_ws + arrived_round) : "memory");
+        polled = true;
+      }
+      // int8 row scale: loaded one tile ahead (under a saturated HBM stream a global load takes ~1000 cycles, which the
+      // first multiply of the tile's offers would otherwise wait for)
       float rs = 1.f;
-      if constexpr (kI8) rs = row_ok ? __ldg(a.scales + row) : 0.f;
+      if constexpr (kI8) {
+        rs = rs_next;
+        const uint32_t nrow = row + P * kRowsTile;
+        rs_next = (tile + P < a.num_tiles && nrow < a.n_rows) ? __ldg(a.scales + nrow) : 0.f;
+      }
       mbar_wait(&tfull[buf], bphase);
       tc::fence_after_thread_sync();
-      const uint32_t acc = lane_addr + buf * kAccColsPerBuf;
+      const uint32_t acc = lane_addr + buf * a.nb;
       uint64_t pend_lo = 0ull, pend_hi = 0ull;  // queries whose append found the list full (bit q)
-      bool enq = false;                         // this thread queued a list for compaction in this round
 
-      // An append takes a slot of the query's list; the one that makes the list half full queues it for compaction;
-      // one that finds the list full stays pending.
+      // An append takes a slot of the query's list (one shared-memory atomic per admitted row; a warp-aggregated variant -
+      // one atomic per warp and query, slots handed out by ballot - measured 20 % slower at 64 queries, interleaved on
+      // one box); one that finds the list full stays pending and triggers a maintenance round (below).
       auto append = [&](uint32_t q, float s) {
         const uint32_t slot = atom_add_shared(cnt_u32 + q * 4u, 1u);
-        if (slot < a.cap) {
-          sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
-          if (slot + 1u == half_cap) {
-            const uint32_t e = atom_add_shared(wl_u32 + rp * 16u, 1u);
-            sts_u32(wl_u32 + 32u + (rp * a.bp + e) * 4u, q);
-            enq = true;
-          }
-        } else if (q < 64u) {
-          pend_lo |= 1ull << q;
-        } else {
-          pend_hi |= 1ull << (q - 64u);
-        }
+        if (slot < a.cap) sts_u64(keys_u32 + (q * a.cap + slot) * 8u, make_key(s, row));
+        else if (q < 64u) pend_lo |= 1ull << q;
+        else pend_hi |= 1ull << (q - 64u);
       };
 
       // ---- offers. Fast path, branch free: thresholds / scales of 8 queries at a time come from shared memory with
@@ -475,26 +559,17 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
         }
       }
 
-      // ---- list maintenance, only when a list became half full or an append is pending: the queued lists are compacted
-      // (any warp takes the next one), pending appends are retried from TMEM against the raised thresholds.
+      // ---- list maintenance, only when an append is pending (its list was full). A round costs every epilogue warp two
+      // barriers, so it must be rare and do parallel work: ALL lists that are at least half full are compacted in it (warp
+      // w takes lists w, w + 8, ...), which raises their thresholds; then the pending appends are retried from TMEM.
+      // (Queueing every list for a round of its own as soon as it was half full made a round nearly every tile from 48
+      // queries on - one warp compacting one list, seven waiting: INT8 64 queries 0.60 ms against 0.35 ms with the appends
+      // switched off.)
       for (;;) {
-        if (epi_bar_count(enq || (pend_lo | pend_hi) != 0ull) == 0u) break;
-        if (tid == 64u) {  // the other work list: last read before the previous round's second barrier
-          sts_u32(wl_u32 + (rp ^ 1u) * 16u, 0u);
-          sts_u32(wl_u32 + (rp ^ 1u) * 16u + 4u, 0u);
-        }
-        const uint32_t nwork = lds_u32(wl_u32 + rp * 16u);
-        for (;;) {
-          uint32_t idx = 0;
-          if (lane == 0) idx = atom_add_shared(wl_u32 + rp * 16u + 4u, 1u);
-          idx = __shfl_sync(0xffffffffu, idx, 0);
-          if (idx >= nwork) break;
-          compact(lds_u32(wl_u32 + 32u + (rp * a.bp + idx) * 4u));
-        }
-        const uint32_t npend = epi_bar_count((pend_lo | pend_hi) != 0ull);  // compactions visible
-        rp ^= 1u;
-        enq = false;
-        if (npend == 0u) break;
+        if (epi_bar_count((pend_lo | pend_hi) != 0ull) == 0u) break;
+        for (uint32_t q = ew; q < a.nq; q += kRowsEpiWarps)
+          if (lds_u32(cnt_u32 + q * 4u) >= half_cap) compact(q);
+        named_bar_sync(1, kRowsEpiThreads);  // compactions visible
 #pragma unroll 1
         for (uint32_t g = hf; g < ngroups; g += 2) {
           const uint32_t bits = (uint32_t)(((g < 4u) ? (pend_lo >> (g * 16u)) : (pend_hi >> ((g - 4u) * 16u))) & 0xFFFFull);
@@ -521,13 +596,19 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
       if (lane == 0) mbar_arrive(&tempty[buf]);
 
       // ---- threshold seeding across the CTAs. A CTA sees 1/P of the rows, so its own k'-th best stays far below the
-      // final one and (k' ln) rows per query keep passing it. After its FIRST tile every CTA publishes, per query, the best
-      // score it has seen; the k'-th largest of the P published values is a lower bound of the final k'-th best (k'
-      // distinct rows reach it) that is as tight as if one CTA had seen all P first tiles (~rank 17 of 128 P rows).
-      // Nobody waits: the arrival counter is polled at a few tile boundaries and the bound is adopted once all P CTAs
-      // have published; until then the local thresholds apply. Epochs make the counter reusable without a memset.
-      if (!seeded) {
-        if (it == 0) {
+      // final one and (k' ln) rows per query keep passing it. In round r (after tile 0, 8, 64 of the CTA) every CTA
+      // publishes, per query, the best score it has seen so far; a bound computed from the P published values (below) is a
+      // lower bound of the final k'-th best, about as tight as the k'-th best of ALL rows the grid has seen by then. Each
+      // round cuts the admission rate ~8x: after the first tile a query admits ~1 row per CTA instead of ~k' ln(rows).
+      // Nobody waits and there is no CTA barrier in it: a warp publishes its own queries (the lists are stable below their
+      // counts between maintenance rounds; a slot another warp has reserved but not yet written holds an older key of the
+      // same query or zero, both harmless for a maximum that only has to be reached by one real row), the eighth warp
+      // to finish bumps the round's arrival counter, thread 64 polls it with a load issued at the top of the next tiles,
+      // and every warp adopts the bound for its own queries when it sees the flag. Epochs (seed_target) make the counters
+      // reusable without a memset.
+      if (nrounds != 0u) {
+        if (pub_round < nrounds && it == pub_it) {
+          uint32_t* ws_val = a.seed_ws + 16u + pub_round * (P * a.bp);
           for (uint32_t q = ew; q < a.nq; q += kRowsEpiWarps) {
             const uint32_t c0 = lds_u32(cnt_u32 + q * 4u), c = c0 < a.cap ? c0 : a.cap;
             uint32_t best = 0u;
@@ -536,45 +617,69 @@ __global__ void __launch_bounds__(kRowsThreads, 1) scan_rows_kernel(const __grid
               best = h > best ? h : best;
             }
             best = __reduce_max_sync(0xffffffffu, best);
-            if (lane == 0) a.seed_ws[16u + j * a.bp + q] = best;
+            if (lane == 0) ws_val[j * a.bp + q] = best;
           }
-          __threadfence();
-          named_bar_sync(1, kRowsEpiThreads);
-          if (tid == 64u) atomicAdd(a.seed_ws, 1u);
-        } else if (it == next_poll) {
-          next_poll += next_poll < 4u ? 1u : next_poll >> 1;
-          if (tid == 64u) {
-            uint32_t cur;
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(cur) : "l"(a.seed_ws) : "memory");
-            sts_u32(wl_u32 + 8u, (int32_t)(cur - a.seed_target) >= 0 ? 1u : 0u);
+          if (lane == 0) {
+            __threadfence();
+            if (atom_add_shared(wl_u32 + 12u, 1u) + 1u == kRowsEpiWarps * (pub_round + 1u)) atomicAdd(a.seed_ws + pub_round, 1u);
           }
-          named_bar_sync(1, kRowsEpiThreads);
-          if (lds_u32(wl_u32 + 8u)) {
-            for (uint32_t q = ew; q < a.nq; q += kRowsEpiWarps) {
-              uint32_t h[8];
+          ++pub_round;
+          pub_it = pub_it == 0u ? 8u : pub_it * 8u;
+        }
+        if (tid == 64u && polled) {
+          polled = false;
+          if ((int32_t)(pcur - a.seed_target) >= 0) sts_u32(wl_u32 + 8u, ++arrived_round);
+        }
+        const uint32_t avail = __shfl_sync(0xffffffffu, lds_u32(wl_u32 + 8u), 0);
+        if (my_round < avail) {
+          const uint32_t* ws_val = a.seed_ws + 16u + my_round * (P * a.bp);
+          ++my_round;
+          // bound of query q from the P published maxima. k' <= 32 (the usual case): the CTAs form 16 or 32 groups (CTA
+          // c -> group c mod 16 / 32 = its lane mod 16 / 32), the smallest group maximum is reached by one row of every
+          // group, i.e. by >= k' distinct rows: one shuffle and one warp reduction per query. Larger k': the exact k'-th
+          // largest of the P values by a 32-step bit search. Four queries per pass so that their L2 loads overlap.
+          for (uint32_t q0 = ew * 4u; q0 < a.nq; q0 += kRowsEpiWarps * 4u) {
+            uint32_t h[4][8];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const uint32_t q = q0 + (uint32_t)u < a.nq ? q0 + (uint32_t)u : a.nq - 1u;
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 const uint32_t l = lane + 32u * (uint32_t)i;
-                h[i] = l < P ? __ldcg(a.seed_ws + 16u + l * a.bp + q) : 0u;
+                h[u][i] = l < P ? __ldcg(ws_val + l * a.bp + q) : 0u;
               }
-              uint32_t ans = 0u;  // the largest v with at least kp published values >= v: the kp-th largest of them
-#pragma unroll 1
-              for (int bit = 31; bit >= 0; --bit) {
-                const uint32_t cand = ans | (1u << bit);
-                uint32_t n = 0;
+            }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) n += h[i] >= cand ? 1u : 0u;
-                if (__reduce_add_sync(0xffffffffu, n) >= a.kp) ans = cand;
+            for (int u = 0; u < 4; ++u) {
+              const uint32_t q = q0 + (uint32_t)u;
+              if (q >= a.nq) break;  // warp-uniform
+              uint32_t ans = 0u;
+              if (a.kp <= 32u && P >= 32u) {
+                uint32_t m = 0u;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) m = h[u][i] > m ? h[u][i] : m;
+                if (a.kp <= 16u) {
+                  const uint32_t o = __shfl_xor_sync(0xffffffffu, m, 16);
+                  m = o > m ? o : m;
+                }
+                ans = __reduce_min_sync(0xffffffffu, m);
+              } else {  // the largest v with at least kp published values >= v: the kp-th largest of them
+#pragma unroll 1
+                for (int bit = 31; bit >= 0; --bit) {
+                  const uint32_t cand = ans | (1u << bit);
+                  uint32_t n = 0;
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) n += h[u][i] >= cand ? 1u : 0u;
+                  if (__reduce_add_sync(0xffffffffu, n) >= a.kp) ans = cand;
+                }
               }
-              if (lane == 0 && ans != 0u) {
+              if (lane == 0 && ans != 0u) {  // this warp is the only one that adopts for q; a compaction only raises too
                 const float t = ordered_to_float(ans);
                 float cur;
                 asm volatile("ld.shared.f32 %0, [%1];" : "=f"(cur) : "r"(par_u32 + q * 16u + 8u));
                 if (t > cur) sts_f32(par_u32 + q * 16u + 8u, t);
               }
             }
-            seeded = true;
-            named_bar_sync(1, kRowsEpiThreads);  // the raised thresholds are visible before the next tile's offers
           }
         }
       }

@@ -231,6 +231,72 @@ def depth3():
             print(json.dumps(rec), flush=True)
 
 
+def rounds():
+    """threshold seeding rounds 0 (off) / 1 / 2 / 3 (NVDB_B200_ROWS_ROUNDS), scan kernel ms"""
+    import os
+    st = torch.cuda.Stream(device=dev)
+    n = 2_903_054
+    for dt, name in ((nv.I8, "i8"), (nv.F16, "f16")):
+        with nv.FlatIndexCuda.synthetic(dt, n, DIM, SEED) as idx:
+            q = queries(n, DIM, 128, st)
+            out_ids = torch.empty((128, 10), dtype=torch.int64, device=dev)
+            out_sc = torch.empty((128, 10), dtype=torch.float32, device=dev)
+            idx.set_tuning(7, 2)
+            idx.set_path(nv.PATH_MMA_EXACT)
+            for b in (8, 16, 32, 48, 64):
+                rec = {"dtype": name, "batch": b}
+                for rep in range(3):
+                    for r in (0, 1, 2, 3):
+                        os.environ["NVDB_B200_ROWS_ROUNDS"] = str(max(r, 1))
+                        idx.set_tuning(8, 2 if r else 0)
+                        for _ in range(3):
+                            idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                        st.synchronize()
+                        idx.profile(True)
+                        for _ in range(20):
+                            idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                        st.synchronize()
+                        scan_ms, merge_ms, calls = idx.profile_read()
+                        idx.profile(False)
+                        k = f"rounds{r}"
+                        rec[k] = min(rec.get(k, 9e9), round(scan_ms / max(calls, 1), 4))
+                os.environ.pop("NVDB_B200_ROWS_ROUNDS")
+                print(json.dumps(rec), flush=True)
+
+
+def slope():
+    """scan kernel ms against the number of rows: slope = steady-state cost per tile, intercept = start-up phase"""
+    import os
+    st = torch.cuda.Stream(device=dev)
+    for dt, name in ((nv.I8, "i8"),):
+        for n in (2_903_054, 1_451_527, 725_763, 362_881):
+            with nv.FlatIndexCuda.synthetic(dt, n, DIM, SEED) as idx:
+                q = queries(n, DIM, 128, st)
+                out_ids = torch.empty((128, 10), dtype=torch.int64, device=dev)
+                out_sc = torch.empty((128, 10), dtype=torch.float32, device=dev)
+                idx.set_tuning(7, 2)
+                idx.set_path(nv.PATH_MMA_EXACT)
+                for b in (8, 32, 64):
+                    rec = {"dtype": name, "rows": n, "tiles_per_cta": round(n / 128 / 148, 1), "batch": b}
+                    for rep in range(3):
+                        for r in (0, 1, 3):
+                            os.environ["NVDB_B200_ROWS_ROUNDS"] = str(max(r, 1))
+                            idx.set_tuning(8, 2 if r else 0)
+                            for _ in range(3):
+                                idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                            st.synchronize()
+                            idx.profile(True)
+                            for _ in range(20):
+                                idx.search_device(q.data_ptr(), b, 10, out_ids.data_ptr(), out_sc.data_ptr(), st.cuda_stream)
+                            st.synchronize()
+                            scan_ms, merge_ms, calls = idx.profile_read()
+                            idx.profile(False)
+                            k = f"rounds{r}"
+                            rec[k] = min(rec.get(k, 9e9), round(scan_ms / max(calls, 1), 4))
+                    os.environ.pop("NVDB_B200_ROWS_ROUNDS")
+                    print(json.dumps(rec), flush=True)
+
+
 if __name__ == "__main__":
     for w in sys.argv[1:] or ["small"]:
         globals()[w]()
