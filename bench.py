@@ -542,16 +542,17 @@ def roofline_configs(cx, idx16, q_dev, args):
     # K3: INT8 (+scale), 2.9M x 768: batch 1 (bit-exact streaming scan), small batches and batch 1024 (exact tensor path)
     with nv.FlatIndexCuda.synthetic(I8, n, DIM, SEED, device=cx.local_rank) as idx8:
         hbm_rec("int8_b1", idx8, I8, n, 1, TOPK, nv.PATH_GEMV, "scan_gemv_tma_kernel<i8,1>", 100)
+        hbm_rec("int8_b1_auto", idx8, I8, n, 1, TOPK, nv.PATH_AUTO, "device call: scan_gemv_tma_kernel<i8,1>; host call (e2e): scan_rows_kernel<i8> + rescore_exact_kernel", 50)
         hbm_rec("int8_b2", idx8, I8, n, 2, TOPK, nv.PATH_AUTO, "scan_rows_kernel<i8> + rescore_exact_kernel (AUTO)", 50)
         for b in (8, 32, 64, 128):
-            hbm_rec(f"int8_b{b}_exact", idx8, I8, n, b, TOPK, nv.PATH_MMA_EXACT, "scan_rows_kernel<i8> (b <= 64) / scan_mma_kernel<i8> + rescore_exact_kernel", 30)
+            hbm_rec(f"int8_b{b}_exact", idx8, I8, n, b, TOPK, nv.PATH_MMA_EXACT, "scan_rows_kernel<i8> (b <= 64) / scan_mma2_kernel<i8> + rescore_exact_kernel", 30)
         time.sleep(0.3)
         tensor_rec("int8_b1024_exact", idx8, I8, 1024, TOPK, "scan_mma2_kernel<i8> + rescore_exact_kernel", 8)
     time.sleep(0.5)
     # K2: FP16 batch sweep (BASELINE.json configs[1]): streaming scan -> tcgen05 crossover
-    hbm_rec("fp16_b2", idx16, F16, n, 2, TOPK, nv.PATH_AUTO, "scan_gemv_tma_kernel<f16,2>", 50)
+    hbm_rec("fp16_b2", idx16, F16, n, 2, TOPK, nv.PATH_AUTO, "scan_rows_kernel<f16> + rescore_exact_kernel (AUTO)", 50)
     for b in (8, 64, 128):
-        hbm_rec(f"fp16_b{b}_exact", idx16, F16, n, b, TOPK, nv.PATH_MMA_EXACT, "tensor-core candidate scan (kind::f16) + rescore_exact_kernel", 30)
+        hbm_rec(f"fp16_b{b}_exact", idx16, F16, n, b, TOPK, nv.PATH_MMA_EXACT, "scan_rows_kernel<f16> (b <= 32) / scan_mma_kernel<f16> + rescore_exact_kernel", 30)
     time.sleep(0.3)
     tensor_rec("fp16_b256_exact", idx16, F16, 256, TOPK, "scan_mma2_kernel<f16,1 limb> + rescore_exact_kernel", 10)
     tensor_rec("fp16_b1024_exact", idx16, F16, 1024, TOPK, "scan_mma2_kernel<f16,1 limb> + rescore_exact_kernel", 8)

@@ -1292,8 +1292,11 @@ int mma_exact_finish(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
 constexpr uint32_t kMmaCrossover = 3;
 // From how many queries AUTO leaves the streaming scan: int8 with the row-tile kernel already at 2 (0.38 ms against the
 // streaming scan's 0.50 ms for two queries: 41 instructions per 16 bytes and query make it issue-bound), else 3.
-static uint32_t auto_crossover(const nvdb_b200_index* idx, uint32_t k, bool exchange) {
-  if (idx->dtype == kDtI8 && idx->tune_rows) return 2u;
+// A host-buffer call (nvdb_b200_search: synchronises anyway) with an int8 base takes the row-tile kernel from ONE query
+// on: device time is the same (0.357 against 0.363 ms), but the issue-bound streaming scan runs at the ramping clock of
+// a GPU that idled between two calls (0.422 ms per call against 0.372, profiles/r2_bench_n1_v5.json).
+static uint32_t auto_crossover(const nvdb_b200_index* idx, uint32_t k, bool exchange, bool host_call = false) {
+  if (idx->dtype == kDtI8 && idx->tune_rows) return (host_call && !exchange && k <= 12u) ? 1u : 2u;
   // f16, two queries, small k: the one-limb query-tile kernel streams the base at 6.9 TB/s, the streaming scan with two
   // queries per pass at 6.2 (0.692 against 0.726 ms per step, profiles/r2_probe_rows_ab.jsonl). Row-sharded searches keep
   // the streaming scan there: its last CTA runs the exchange in the same launch.
@@ -1306,7 +1309,8 @@ int search_device_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq
                        bool* deferred = nullptr) {
   int path = idx->path;
   if (path == NVDB_B200_PATH_AUTO)
-    path = (nq >= auto_crossover(idx, k, false) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT : NVDB_B200_PATH_GEMV;
+    path = (nq >= auto_crossover(idx, k, false, deferred != nullptr) && mma_exact_supported(idx, k)) ? NVDB_B200_PATH_MMA_EXACT
+                                                                                                    : NVDB_B200_PATH_GEMV;
   if (path_used) *path_used = (uint32_t)path;
   if (path == NVDB_B200_PATH_GEMV) return gemv_search_impl(idx, d_queries, nq, k, d_out_ids, d_out_scores, stream, launches);
   if (path == NVDB_B200_PATH_MMA_EXACT)

@@ -128,9 +128,11 @@ def test_auto_path_crossover_and_timing_path(nv, oracle):
         idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 3, rng), 100, t)
         assert t.path == nv.PATH_MMA_EXACT
     b8, s8 = oracle.synth(I8, 2, 0, n, d)
-    with nv.FlatIndexCuda.from_host(b8, s8, I8) as idx:       # int8: the row-tile kernel already wins at two queries
+    with nv.FlatIndexCuda.from_host(b8, s8, I8) as idx:       # int8: the row-tile kernel from one query on (host calls)
         t = nv.Timing()
         idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 1, rng), 10, t)
+        assert t.path == nv.PATH_MMA_EXACT
+        idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 1, rng), 100, t)
         assert t.path == nv.PATH_GEMV
         idx.search_topk_dot_batch(make_queries(oracle, 2, n, d, 2, rng), 10, t)
         assert t.path == nv.PATH_MMA_EXACT
