@@ -68,6 +68,119 @@ __device__ __forceinline__ void l2_piece(const uint4 v, const float* __restrict_
 // Loads in flight per thread = rows in flight (U) x pieces per lane (unrolled up to 4): U = 2 for long rows (3+ pieces per
 // lane), 4 for short ones — enough to cover the HBM latency at 5-6 resident CTAs per SM without the register count
 // cutting the occupancy (4 rows x 3 pieces measured 0.73 of the copy peak at D = 768, 2 x 3 0.89).
+// K <= 16: a tournament instead of the counting step of the selection. floor(32 / K) chunks' best K fit one warp sort;
+// their best K become one chunk of the next round (written to the other buffer, so a round needs one barrier). R = 500,
+// K = 10: 16 chunks -> 6 -> 2 -> 1 in three warp sorts instead of 160 x 160 key compares (16 K cycles of a 100 K-cycle CTA).
+// Not inlined: inlined, the two unrolled sorts changed the code of the distance loop (85 K -> 101 K cycles per CTA).
+__device__ __noinline__ void select_tournament(uint64_t* skeys, uint64_t* sbuf, uint32_t nchunks, uint32_t K, uint32_t* out_ids,
+                                               float* out_dist) {
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const uint32_t G = 32u / K;
+  uint64_t* src = skeys;
+  uint64_t* dst = sbuf;
+  uint32_t nch = nchunks;
+  while (nch > 1u) {
+    __syncthreads();
+    const uint32_t ngr = (nch + G - 1u) / G;
+    for (uint32_t gr = warp; gr < ngr; gr += kRefineThreads / 32) {
+      const uint32_t c = gr * G + lane / K;
+      uint64_t key = (lane < G * K && c < nch) ? src[c * 32u + lane % K] : 0ull;
+#pragma unroll
+      for (uint32_t size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+          const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)key, stride);
+          const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(key >> 32), stride);
+          const uint64_t o = ((uint64_t)hi << 32) | lo;
+          const bool lower = (lane & stride) == 0, desc = (lane & size) == 0 || size == 32;
+          key = (lower == desc) ? (key > o ? key : o) : (key < o ? key : o);
+        }
+      }
+      if (lane < K) dst[gr * 32u + lane] = key;
+    }
+    uint64_t* t = src;
+    src = dst;
+    dst = t;
+    nch = ngr;
+  }
+  __syncthreads();
+  for (uint32_t j = tid; j < K; j += kRefineThreads) {
+    const uint64_t sk = src[j];
+    const bool ok = sk != 0ull;
+    const uint64_t key = ~sk;
+    out_ids[j] = ok ? (uint32_t)key : 0xFFFFFFFFu;
+    if (out_dist) out_dist[j] = ok ? __uint_as_float((uint32_t)(key >> 32)) : 1e30f;
+  }
+}
+
+// Selection of the K best of the R keys in skeys (descending; 0 = empty) and their output. Not inlined into the kernel:
+// inlined, its unrolled warp sorts changed the code of the distance loop (85 K -> 101 K cycles per CTA at K5).
+__device__ __noinline__ void select_and_write(uint64_t* skeys, uint64_t* sbuf, uint32_t R, uint32_t K, uint32_t sortn,
+                                              uint32_t* out_ids, float* out_dist) {
+  const uint32_t tid = threadIdx.x;
+  if (K <= 32u) {
+    // Selection in two barrier-light steps instead of a full block sort (36+ barrier-separated stages for 256 keys):
+    //   1. every warp sorts chunks of 32 keys in registers (bitonic over shuffles) and leaves each chunk's best
+    //      min(K, 32) at the front of the chunk — the final K best are among them;
+    //   2. those few keys are ranked by counting (keys are unique per (distance, id); equal keys — the same id listed
+    //      twice — take consecutive ranks by position) and a key of rank < K goes straight to its output slot.
+    const uint32_t lane = tid & 31u, warp = tid >> 5;
+    const uint32_t nchunks = (R + 31u) >> 5;
+    for (uint32_t ch = warp; ch < nchunks; ch += kRefineThreads / 32) {
+      const uint32_t pos = ch * 32u + lane;
+      uint64_t key = pos < R ? skeys[pos] : 0ull;
+#pragma unroll
+      for (uint32_t size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+          const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)key, stride);
+          const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(key >> 32), stride);
+          const uint64_t o = ((uint64_t)hi << 32) | lo;
+          const bool lower = (lane & stride) == 0, desc = (lane & size) == 0 || size == 32;
+          key = (lower == desc) ? (key > o ? key : o) : (key < o ? key : o);
+        }
+      }
+      skeys[pos] = key;   // sortn >= 32 * nchunks (the host rounds it up to a power of two >= 32)
+    }
+    if (K <= 16u) {
+      select_tournament(skeys, sbuf, nchunks, K, out_ids, out_dist);
+      return;
+    }
+    for (uint32_t j = tid; j < K; j += kRefineThreads) {
+      out_ids[j] = 0xFFFFFFFFu;
+      if (out_dist) out_dist[j] = 1e30f;
+    }
+    __syncthreads();
+    const uint32_t ncand = nchunks * K;
+    for (uint32_t i = tid; i < ncand; i += kRefineThreads) {
+      const uint32_t pi = (i / K) * 32u + (i % K);
+      const uint64_t mine = skeys[pi];
+      if (mine == 0ull) continue;
+      uint32_t rank = 0;
+      for (uint32_t m = 0; m < ncand; ++m) {
+        const uint32_t pm = (m / K) * 32u + (m % K);
+        const uint64_t o = skeys[pm];
+        rank += (o > mine || (o == mine && pm < pi)) ? 1u : 0u;
+      }
+      if (rank < K) {
+        const uint64_t key = ~mine;
+        out_ids[rank] = (uint32_t)key;
+        if (out_dist) out_dist[rank] = __uint_as_float((uint32_t)(key >> 32));
+      }
+    }
+    return;
+  }
+  auto sync = [] { __syncthreads(); };
+  bitonic_sort_desc(skeys, sortn, tid, kRefineThreads, sync);
+  for (uint32_t j = tid; j < K; j += kRefineThreads) {
+    const uint64_t sk = (j < sortn) ? skeys[j] : 0ull;
+    const bool ok = sk != 0ull;
+    const uint64_t key = ~sk;
+    out_ids[j] = ok ? (uint32_t)key : 0xFFFFFFFFu;
+    if (out_dist) out_dist[j] = ok ? __uint_as_float((uint32_t)(key >> 32)) : 1e30f;
+  }
+}
+
 template <int DT, int LPR, int kRowsInFlight, int PPL>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ scales, uint64_t n, uint32_t dim,
@@ -83,6 +196,7 @@ refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ sca
   if (sample) tq0 = clock64();
   uint64_t* skeys = smem64;                                  // [sortn]
   float* sq = reinterpret_cast<float*>(smem64 + sortn);      // [dim]
+  uint64_t* sbuf = smem64 + sortn + (dim + 1u) / 2u;         // [sortn / 2]: the other side of the selection tournament
   constexpr int ES = (DT == kDtF32) ? 4 : (DT == kDtF16 ? 2 : 1);
   constexpr int P16 = 16 / ES;
   constexpr uint32_t kGroups = kRefineThreads / LPR;
@@ -153,68 +267,11 @@ refine_l2_kernel(const uint8_t* __restrict__ base, const float* __restrict__ sca
     dbg[(size_t)q * 3 + 0] = (unsigned long long)(tq1 - tq0);
     dbg[(size_t)q * 3 + 1] = (unsigned long long)(tq2 - tq1);
   }
-  if (K <= 32u) {
-    // Selection in two barrier-light steps instead of a full block sort (36+ barrier-separated stages for 256 keys):
-    //   1. every warp sorts chunks of 32 keys in registers (bitonic over shuffles) and leaves each chunk's best
-    //      min(K, 32) at the front of the chunk — the final K best are among them;
-    //   2. those few keys are ranked by counting (keys are unique per (distance, id); equal keys — the same id listed
-    //      twice — take consecutive ranks by position) and a key of rank < K goes straight to its output slot.
-    const uint32_t lane = tid & 31u, warp = tid >> 5;
-    const uint32_t nchunks = (R + 31u) >> 5;
-    for (uint32_t ch = warp; ch < nchunks; ch += kRefineThreads / 32) {
-      const uint32_t pos = ch * 32u + lane;
-      uint64_t key = pos < R ? skeys[pos] : 0ull;
-#pragma unroll
-      for (uint32_t size = 2; size <= 32; size <<= 1) {
-#pragma unroll
-        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-          const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)key, stride);
-          const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(key >> 32), stride);
-          const uint64_t o = ((uint64_t)hi << 32) | lo;
-          const bool lower = (lane & stride) == 0, desc = (lane & size) == 0 || size == 32;
-          key = (lower == desc) ? (key > o ? key : o) : (key < o ? key : o);
-        }
-      }
-      skeys[pos] = key;   // sortn >= 32 * nchunks (the host rounds it up to a power of two >= 32)
-    }
-    for (uint32_t j = tid; j < K; j += kRefineThreads) {
-      out_ids[(size_t)q * K + j] = 0xFFFFFFFFu;
-      if (out_dist) out_dist[(size_t)q * K + j] = 1e30f;
-    }
+  select_and_write(skeys, sbuf, R, K, sortn, out_ids + (size_t)q * K, out_dist ? out_dist + (size_t)q * K : nullptr);
+  if (dbg != nullptr && blockIdx.x < dbg_q) {  // the selection phase ends when the slowest thread is done
     __syncthreads();
-    const uint32_t ncand = nchunks * K;
-    for (uint32_t i = tid; i < ncand; i += kRefineThreads) {
-      const uint32_t pi = (i / K) * 32u + (i % K);
-      const uint64_t mine = skeys[pi];
-      if (mine == 0ull) continue;
-      uint32_t rank = 0;
-      for (uint32_t m = 0; m < ncand; ++m) {
-        const uint32_t pm = (m / K) * 32u + (m % K);
-        const uint64_t o = skeys[pm];
-        rank += (o > mine || (o == mine && pm < pi)) ? 1u : 0u;
-      }
-      if (rank < K) {
-        const uint64_t key = ~mine;
-        out_ids[(size_t)q * K + rank] = (uint32_t)key;
-        if (out_dist) out_dist[(size_t)q * K + rank] = __uint_as_float((uint32_t)(key >> 32));
-      }
-    }
-    if (dbg != nullptr && blockIdx.x < dbg_q) {  // the selection phase ends when the slowest thread is done
-      __syncthreads();
-      if (sample) dbg[(size_t)q * 3 + 2] = (unsigned long long)(clock64() - tq2);
-    }
-    return;
+    if (sample) dbg[(size_t)q * 3 + 2] = (unsigned long long)(clock64() - tq2);
   }
-  auto sync = [] { __syncthreads(); };
-  bitonic_sort_desc(skeys, sortn, tid, kRefineThreads, sync);
-  for (uint32_t j = tid; j < K; j += kRefineThreads) {
-    const uint64_t sk = (j < sortn) ? skeys[j] : 0ull;
-    const bool ok = sk != 0ull;
-    const uint64_t key = ~sk;
-    out_ids[(size_t)q * K + j] = ok ? (uint32_t)key : 0xFFFFFFFFu;
-    if (out_dist) out_dist[(size_t)q * K + j] = ok ? __uint_as_float((uint32_t)(key >> 32)) : 1e30f;
-  }
-  if (sample) dbg[(size_t)q * 3 + 2] = (unsigned long long)(clock64() - tq2);
 }
 
 }  // namespace
@@ -225,7 +282,7 @@ cudaError_t refine_l2_launch(int dtype, const void* base, const float* scales, u
                              uint32_t dbg_q, uint32_t* smem_bytes_out) {
   if (Q == 0 || K == 0) return cudaSuccess;
   const uint32_t sortn = next_pow2(R < 32 ? 32 : R);
-  const size_t smem = (size_t)sortn * 8u + (size_t)dim * 4u;
+  const size_t smem = (size_t)sortn * 12u + (size_t)((dim + 1u) / 2u) * 8u;  // keys + query + the tournament's second buffer (sortn / 2)
   if (smem > 220u * 1024u) return cudaErrorInvalidValue;
   if (smem_bytes_out) *smem_bytes_out = (uint32_t)smem;
   auto go = [&](auto kern) -> cudaError_t {
