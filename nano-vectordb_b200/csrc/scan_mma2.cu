@@ -340,7 +340,13 @@ cudaError_t launch_mma2_k(const CUtensorMap* ta, const CUtensorMap* tb, const Mm
 
 // deepest ring that fits; 0 when not even `min_stages` do
 int mma2_fit_stages(uint32_t half_n, int limbs, uint32_t k, int res_limbs, uint32_t kchunks, int max_smem, int min_stages) {
-  for (int st = 8; st >= min_stages; --st)
+  int st_max = 8;
+  if (const char* e = getenv("NVDB_B200_PAIR_MAX_STAGES")) {  // ring depth experiments (A/B)
+    const int v = atoi(e);
+    if (v >= 2 && v < st_max) st_max = v;
+  }
+  if (st_max < min_stages) st_max = min_stages;
+  for (int st = st_max; st >= min_stages; --st)
     if (mma2_layout(half_n, limbs, st, k <= (uint32_t)kMmaRegK ? 0u : k, res_limbs, kchunks).total <= (uint32_t)max_smem)
       return st;
   return 0;
