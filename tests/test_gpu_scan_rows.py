@@ -115,3 +115,46 @@ def test_rows_kernel_is_what_auto_runs_for_small_batches(nv, oracle):
         l0 = nv.launch_count()
         idx.search_topk_dot_batch(queries, k)
         assert nv.launch_count() - l0 == 4
+
+
+@pytest.mark.parametrize("dt", ["f16", "i8"])
+@pytest.mark.parametrize("rounds,depth", [(1, 4), (3, 3), (2, 6)])
+def test_rows_kernel_seeding_rounds_and_ring_depth_do_not_change_results(nv, dt, rounds, depth):
+    """A base with enough tiles per CTA for all three seeding rounds (after tiles 0, 8 and 64) and the ring-depth
+    overrides: results are those of the streaming scan bit for bit whatever NVDB_B200_ROWS_ROUNDS /
+    NVDB_B200_ROWS_MAX_STAGES / NVDB_B200_GEMV_MAX_STAGES say (they are A/B aids)."""
+    import os
+    torch = pytest.importorskip("torch")
+    dtype = F16 if dt == "f16" else I8
+    n, d, k, nq = 1_300_000, 64, 10, 48            # 10157 tiles of 128 rows: 68 per CTA on 148 SMs
+    dev = torch.device("cuda", 0)
+    st = torch.cuda.Stream(device=dev)
+    env = {"NVDB_B200_ROWS_ROUNDS": str(rounds), "NVDB_B200_ROWS_MAX_STAGES": str(depth), "NVDB_B200_GEMV_MAX_STAGES": str(depth)}
+    old = {key: os.environ.get(key) for key in env}
+    os.environ.update(env)
+    try:
+        with nv.FlatIndexCuda.synthetic(dtype, n, d, 77) as idx:
+            q = torch.empty((nq, d), dtype=torch.float32, device=dev)
+            for i in range(nq):
+                nv.synth_fill_device(0, nv.F32, 1, d, 77, (i * 7919) % n, q[i].data_ptr(), None, st.cuda_stream)
+            st.synchronize()
+            q += 0.01 * torch.randn(q.shape, device=dev, generator=torch.Generator(device=dev).manual_seed(3))
+            res = []
+            for path, rows in ((nv.PATH_MMA_EXACT, ROWS_ALWAYS), (nv.PATH_GEMV, 1)):
+                idx.set_tuning(TUNE_ROWS, rows)
+                idx.set_tuning(TUNE_ROWS_SEED, 2)
+                idx.set_path(path)
+                ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+                sc = torch.empty((nq, k), dtype=torch.float32, device=dev)
+                for _ in range(2):                  # the second launch reuses the seeding counters (epochs)
+                    idx.search_device(q.data_ptr(), nq, k, ids.data_ptr(), sc.data_ptr(), st.cuda_stream)
+                st.synchronize()
+                res.append((ids.cpu().numpy(), sc.cpu().numpy().view(np.uint32)))
+            assert idx.exact_stats()[0] == 2 * nq
+        assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1])
+    finally:
+        for key, v in old.items():
+            if v is None:
+                os.environ.pop(key, None)
+            else:
+                os.environ[key] = v
