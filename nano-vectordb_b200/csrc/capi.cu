@@ -887,8 +887,11 @@ int gemv_search_impl(nvdb_b200_index* idx, const float* d_queries, uint32_t nq, 
   // (auto: up to 4096 keys per query — beyond that one CTA sorting alone is slower than the 512-thread merge kernel:
   // k = 100, 148 lists: 0.95 vs 0.86 ms, profiles/r1_ab_fused_merge.jsonl; 2 = whenever the buffer fits)
   const size_t merge_keys = (size_t)next_pow2((uint32_t)plan.grid * k);
+  // (round 2: with the rank-counting merge the last CTA keeps only ~k of the keys, so it also takes k = 100 - 14,800 keys
+  // - whenever the keys and the lists' j-th entries fit the ring)
   const bool fused = idx->tma_ok && idx->tune_fused_merge && merge_keys * 8u <= (size_t)plan.stages * 32768u &&
-                     (idx->tune_fused_merge == 2 || merge_keys <= 4096u);
+                     (idx->tune_fused_merge == 2 || merge_keys <= 4096u ||
+                      ((size_t)plan.grid * k + (size_t)plan.grid) * 8u <= (size_t)plan.stages * 32768u);
   a.done_counter = nullptr;
   a.out_ids = nullptr;
   a.out_scores = nullptr;

@@ -209,17 +209,22 @@ scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a)
   const uint32_t nlists = gridDim.x, total = nlists * a.k;
   for (uint32_t qi = 0; qi < a.nq; ++qi) {
     const uint64_t* in = a.partial + (size_t)qi * total;
-    // All nlists x k keys come into the ring with ONE round of L2 loads (when they fit twice: keys + survivors); the
-    // floors and the survivors are then computed from shared memory.
     // Every list is sorted descending, so the final k-th best is (a) >= the best of the lists' own k-th entries and
-    // (b) >= the k-th largest of the lists' BEST entries (k distinct rows reach it), which is far tighter: ~k survivors
-    // instead of hundreds (631 of 1480 keys at 148 lists, whose 1024-key bitonic sort took 10 us of a 635 us step).
+    // (b) >= the m-th largest of the lists' j-th entries whenever m * j >= k (m lists hold j rows each that reach it):
+    // with j = ceil(k / nlists) (1 when there are at least k lists) and m = ceil(k / j) this is far tighter than (a):
+    // ~k survivors instead of hundreds (631 of 1480 keys at 148 lists and k = 10, whose 1024-key bitonic sort took 10 us
+    // of a 635 us step; k = 100: ~170 of 14,800). The j-th entries are ranked by counting in the idle ring. When the
+    // keys fit the ring twice they are staged there with ONE round of L2 loads and everything else reads shared memory.
     if (tid == 0) {
       s_floor = 0ull;
       s_cnt = 0u;
     }
-    const bool staged = (size_t)total * 16u <= (size_t)a.stages * kStageBytes;
+    const size_t ring_bytes = (size_t)a.stages * kStageBytes;
+    const bool staged = (size_t)total * 16u <= ring_bytes;
+    const bool heads_fit = (size_t)(total + nlists) * 8u <= ring_bytes;
     uint64_t* all = buf + total;  // staged copy of the lists (survivors go to buf[0 .. total))
+    uint64_t* heads = staged ? buf : buf + total;  // the lists' j-th entries (read before the survivors are written)
+    const uint32_t jth = (a.k + nlists - 1u) / nlists, mth = (a.k + jth - 1u) / jth;
     if (staged)
       for (uint32_t i = tid; i < total; i += kConsumers) all[i] = __ldcg(in + i);
     csync();
@@ -227,18 +232,21 @@ scan_gemv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanArgs a)
     for (uint32_t l = tid; l < nlists; l += kConsumers) {
       const uint64_t v = staged ? all[(size_t)l * a.k + (a.k - 1)] : __ldcg(in + (size_t)l * a.k + (a.k - 1));
       fl = v > fl ? v : fl;
+      if (heads_fit) heads[l] = staged ? all[(size_t)l * a.k + (jth - 1u)] : __ldcg(in + (size_t)l * a.k + (jth - 1u));
     }
-    if (staged && nlists >= a.k) {  // (b): heads ranked by counting
+    csync();
+    if (heads_fit) {  // (b)
       for (uint32_t l = tid; l < nlists; l += kConsumers) {
-        const uint64_t mine = all[(size_t)l * a.k];
+        const uint64_t mine = heads[l];
         uint32_t r = 0;
         for (uint32_t m = 0; m < nlists; ++m) {
-          const uint64_t o = all[(size_t)m * a.k];
-          r += (o > mine || (o == mine && m < l)) ? 1u : 0u;  // empty lists: equal zero heads, ranked by position
+          const uint64_t o = heads[m];
+          r += (o > mine || (o == mine && m < l)) ? 1u : 0u;  // empty lists: equal zero entries, ranked by position
         }
-        if (r == a.k - 1u && mine > fl) fl = mine;
+        if (r == mth - 1u && mine > fl) fl = mine;
       }
     }
+    csync();  // the j-th entries have been read: their place may take survivors
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
       const uint64_t o = __shfl_xor_sync(0xffffffffu, fl, off);
