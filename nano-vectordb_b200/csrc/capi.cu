@@ -123,9 +123,13 @@ int fail_cuda(const nvdb_b200_index* idx, cudaError_t e, const char* what) {
 // blocks are split over a few short-lived threads (>= 2 MB per thread).
 void par_memcpy(void* dst, const void* src, size_t bytes, size_t max_threads = 6) {
   const size_t per_thread = (size_t)2 << 20;
-  unsigned hw = std::thread::hardware_concurrency();
   size_t T = bytes / per_thread;
   if (T > max_threads) T = max_threads;
+  if (T <= 1) {  // the per-query path: no thread, no look at the machine
+    std::memcpy(dst, src, bytes);
+    return;
+  }
+  static const unsigned hw = std::thread::hardware_concurrency();
   if (hw && T > hw) T = hw;
   if (T <= 1) {
     std::memcpy(dst, src, bytes);
