@@ -655,6 +655,14 @@ int gemv_ctas(const nvdb_b200_index* idx) {
   return idx->tune_gemv_ctas == 2 ? 2 : 1;
 }
 
+// NVDB_B200_GEMV_MAX_STAGES=3..6 (0 = unset); read per call: the A/B probes and a test flip it inside one process
+static int gemv_max_stages_override() {
+  const char* e = getenv("NVDB_B200_GEMV_MAX_STAGES");
+  if (!e) return 0;
+  const int v = atoi(e);
+  return (v >= 3 && v <= 6) ? v : 0;
+}
+
 int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) {
   const uint64_t need = (uint64_t)k + kScanRowsPerTile;
   if (need > 8192) return fail(idx, NVDB_B200_ERR_UNSUPPORTED, "k too large for the fused selector (k <= 7936)");
@@ -682,10 +690,7 @@ int plan_scan(const nvdb_b200_index* idx, uint32_t nq, uint32_t k, ScanPlan* p) 
     // 148 SMs over more DRAM pages at a time. INT8 (issue-bound) and FP32 do not care / prefer 5-6.
     // NVDB_B200_GEMV_MAX_STAGES=3..6 overrides (A/B).
     int st_cap = idx->dtype == NVDB_B200_F16 ? 4 : 6;
-    if (const char* e = getenv("NVDB_B200_GEMV_MAX_STAGES")) {
-      const int v = atoi(e);
-      if (v >= 3 && v <= 6) st_cap = v;
-    }
+    if (const int v = gemv_max_stages_override()) st_cap = v;
     if (st > st_cap) st = st_cap;
     // single-query passes may run two CTAs per SM (more consumer warps to cover the int8 conversion chain); each CTA
     // then gets half of the shared memory. Tuning knob NVDB_B200_TUNE_GEMV_CTAS (default 1).

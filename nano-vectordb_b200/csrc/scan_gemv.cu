@@ -19,6 +19,7 @@
 //     gridDim.x * k keys to the final k.
 //
 // HBM traffic = the base payload once per pass (plus 4 B/row of scales for int8): the roofline of this kernel.
+#include <atomic>
 #include "common.cuh"
 #include "exchange.cuh"
 #include "scan.h"
@@ -391,8 +392,16 @@ cudaError_t launch_one(const ScanLaunch& l, const ScanArgs& a) {
   if (l.use_tma) {
     const SmemLayout L = make_layout(a.stages, NQ, a.dim, a.cap);
     auto kern = scan_gemv_tma_kernel<DT, NQ>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+    // the attribute is per device and sticky: set it only when this launch needs more than any before (1 us per call)
+    static std::atomic<uint32_t> smem_set[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || smem_set[dev].load(std::memory_order_relaxed) < L.total) {
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+      if (e != cudaSuccess) return e;
+      if (dev >= 0 && dev < 64) smem_set[dev].store(L.total, std::memory_order_relaxed);
+    }
     kern<<<l.grid, kThreads, L.total, l.stream>>>(*l.tmap, a);
   } else {
     const SmemLayout L = make_layout(0, NQ, a.dim, a.cap);
