@@ -1122,9 +1122,11 @@ int mma_exact_enqueue(nvdb_b200_index* idx, const float* d_queries, uint32_t nq,
   r.rel_err = idx->dtype == kDtF16
                   ? (float)(D * 2.0 * u24 + (D / 8.0 + 4.0) * u24)  // + |delta|_2 of the limb split, added per query
                   : (float)((D / 8.0 + 16.0) * u24);
+  // the verdict (number of flagged queries) is stored into the pinned word by the kernel's last CTA
+  r.done_ctr = ws_flags + 3;
+  r.host_nflag = (uint32_t*)idx->h_pin[2];
   CK(rescore_exact_launch((int)idx->dtype, r, nq, stream), "rescore launch");
   if (launches) ++*launches;
-  CK(cudaMemcpyAsync(idx->h_pin[2], nflag, 4, cudaMemcpyDeviceToHost, stream), "D2H flag count");
   return NVDB_B200_OK;
 }
 

@@ -294,6 +294,15 @@ rescore_exact_kernel(const RescoreArgs a) {
     a.flags[q] = pass ? 0u : 1u;
     if (!pass) atomicAdd(a.nflag, 1u);
     if (q == 0 && a.nflag_next) *a.nflag_next = 0u;  // the counter of the NEXT call on this stream (no memset launch)
+    if (a.host_nflag) {  // the last CTA hands the verdict to the host itself: no copy-engine round trip behind the kernel
+      __threadfence();
+      if (atomicAdd(a.done_ctr, 1u) == gridDim.x - 1u) {
+        __threadfence();
+        const uint32_t c = atomicAdd(a.nflag, 0u);
+        *a.done_ctr = 0u;
+        *reinterpret_cast<volatile uint32_t*>(a.host_nflag) = c;
+      }
+    }
   }
 }
 

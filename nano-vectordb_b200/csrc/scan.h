@@ -154,6 +154,8 @@ struct RescoreArgs {
   const uint64_t* partial;
   uint32_t nlists;
   uint32_t* nflag_next;      // optional: zeroed by the kernel (the flag counter of the next call on the stream)
+  uint32_t* done_ctr;        // optional pair: device word (zero between launches) counting finished CTAs, and a
+  uint32_t* host_nflag;      // device-visible pinned host word that the LAST CTA stores the final flag count to (no D2H copy)
   uint32_t sel_off;          // set by rescore_exact_launch
   int stage_rows;            // set by rescore_exact_launch: candidate rows staged in shared memory, 8 lanes per candidate
 };
