@@ -1136,13 +1136,19 @@ int nvdb_b200_ivfpq_search(nvdb_b200_ivfpq* h, const float* queries_host, uint32
   if ((rc = pin(h, qb + 2 * ob))) return rc;
   memcpy(h->h_pin, queries_host, qb);  // pinned staging: asynchronous copies, one sync per call
   uint8_t* hp = (uint8_t*)h->h_pin + qb;
+  // small results are written by the last kernel straight into the pinned buffer (device-addressable): a copy-engine
+  // round trip behind the kernels costs ~6 us of a 50-90 us call
+  const bool direct = 2 * ob <= 4096u;
   auto enqueue = [&]() -> int {
     ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
-    if (int rc2 = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND],
-                                     out_dist ? (float*)h->ws[IWS_OUT] : nullptr, h->stream))
+    if (int rc2 = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R,
+                                     direct ? (uint32_t*)hp : (uint32_t*)h->ws[IWS_CAND],
+                                     out_dist ? (direct ? (float*)(hp + ob) : (float*)h->ws[IWS_OUT]) : nullptr, h->stream))
       return rc2;
-    ICK(cudaMemcpyAsync(hp, h->ws[IWS_CAND], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate ids");
-    if (out_dist) ICK(cudaMemcpyAsync(hp + ob, h->ws[IWS_OUT], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate distances");
+    if (!direct) {
+      ICK(cudaMemcpyAsync(hp, h->ws[IWS_CAND], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate ids");
+      if (out_dist) ICK(cudaMemcpyAsync(hp + ob, h->ws[IWS_OUT], ob, cudaMemcpyDeviceToHost, h->stream), "D2H candidate distances");
+    }
     return NVDB_B200_OK;
   };
   const uint64_t key[8] = {out_dist ? 3u : 1u, nq, nprobe, R, 0, 0, 0, 0};
@@ -1184,13 +1190,15 @@ int nvdb_b200_ivfpq_search_refine(nvdb_b200_ivfpq* h, nvdb_b200_index* base, con
     ICK(cudaMemcpyAsync(h->ws[IWS_Q], h->h_pin, qb, cudaMemcpyHostToDevice, h->stream), "H2D queries");
     if (int rc2 = search_device_impl(h, (const float*)h->ws[IWS_Q], nq, nprobe, R, (uint32_t*)h->ws[IWS_CAND], nullptr, h->stream))
       return rc2;
-    uint32_t* o_ids = (uint32_t*)h->ws[IWS_OUT];
-    float* o_dist = (float*)((uint8_t*)h->ws[IWS_OUT] + ob);
+    // small results: the refine kernel writes straight into the pinned buffer (no copy-engine round trip behind it)
+    const bool direct = 2 * ob <= 4096u;
+    uint32_t* o_ids = direct ? (uint32_t*)hp : (uint32_t*)h->ws[IWS_OUT];
+    float* o_dist = direct ? (float*)(hp + ob) : (float*)((uint8_t*)h->ws[IWS_OUT] + ob);
     // candidates never leave the device (the reference copies them to the host and back: src/cuda_refine.cu:926-929)
     if (nvdb_b200_refine_l2_device(base, (const float*)h->ws[IWS_Q], (const uint32_t*)h->ws[IWS_CAND], nq, R, k, o_ids, o_dist,
                                    h->stream) != NVDB_B200_OK)
       return ifail(h, NVDB_B200_ERR_CUDA, std::string("refine: ") + nvdb_b200_last_error(base));
-    ICK(cudaMemcpyAsync(hp, h->ws[IWS_OUT], 2 * ob, cudaMemcpyDeviceToHost, h->stream), "D2H results");
+    if (!direct) ICK(cudaMemcpyAsync(hp, h->ws[IWS_OUT], 2 * ob, cudaMemcpyDeviceToHost, h->stream), "D2H results");
     return NVDB_B200_OK;
   };
   // the graph bakes the base's device pointers in: they are part of the key
