@@ -1514,7 +1514,7 @@ int nvdb_b200_search(nvdb_b200_index* idx, const float* queries_host, uint32_t n
   // device addresses directly (unified addressing): no device-to-host copy is enqueued, the stream synchronisation
   // below makes the stores visible. Larger results go through device memory and one copy.
   char* hp = (char*)idx->h_pin[1];
-  const bool direct_out = ibytes + sbytes <= 4096u;
+  const bool direct_out = ibytes + sbytes <= 16384u;  // up to 128 queries x top-10
   uint64_t* d_ids = direct_out ? (uint64_t*)hp : (uint64_t*)idx->d_ws[WS_OUT_IDS];
   float* d_scores = direct_out ? (float*)(hp + ibytes) : (float*)((char*)idx->d_ws[WS_OUT_IDS] + ibytes);
   par_memcpy(idx->h_pin[0], queries_host, qbytes);
